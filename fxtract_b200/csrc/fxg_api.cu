@@ -1,0 +1,690 @@
+// fxg_api.cu -- context, pattern tables and the C ABI of libfxgpu.so (include/fxgpu.h).
+#include "fxg_common.cuh"
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <string>
+#include <vector>
+
+namespace fxg {
+
+static std::string g_last_error;
+
+struct Slot {
+    void *pinned = nullptr;             // input staging (host path)
+    ScanCounters *h_ctr = nullptr;      // pinned result staging
+    unsigned long long *h_counts = nullptr;   // [2]: n_runs, n_selected (K6)
+    fxg_run *h_runs = nullptr; size_t h_runs_cap = 0;
+    fxg_run *d_runs = nullptr; size_t d_runs_cap = 0;
+    uint8_t *h_flags = nullptr; int *h_pid = nullptr; uint32_t *h_off = nullptr; size_t fields_cap = 0;
+    cudaEvent_t done = nullptr;
+    int state = 0;                      // 0 free, 1 lent to caller, 2 submitted
+    int kind = 0;                       // 0 raw, 1 fields
+    size_t nbytes = 0; uint32_t nrec = 0; int is_last = 0;
+    size_t runs_copied = 0;
+};
+
+}  // namespace fxg
+
+struct fxg_ctx {
+    fxg_config cfg;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    // patterns
+    std::vector<uint8_t> blob; std::vector<uint32_t> off; uint32_t npat = 0;
+    bool have_patterns = false;
+    fxg::LiteralTable h_lit;
+    fxg::LiteralTable *d_lit = nullptr;
+    uint8_t *d_pat = nullptr; uint32_t *d_patoff = nullptr;
+    uint8_t *d_cls = nullptr; int *d_next = nullptr; int *d_out = nullptr; int ac_ncls = 0, ac_nstates = 0;
+    unsigned long long *d_slot_hash = nullptr; int *d_slot_pat = nullptr; unsigned int exact_mask = 0;
+    // scan resources (shared; everything is ordered on one stream)
+    size_t cap_bytes = 0; size_t rec_cap = 0; size_t ntiles_cap = 0; size_t nblocks_cap = 0;
+    fxg::TileDesc *d_desc = nullptr; fxg::ScanCounters *d_ctr = nullptr; unsigned int *d_hitbits = nullptr;
+    unsigned long long *d_rec_start = nullptr, *d_fld_off = nullptr, *d_block_sums = nullptr, *d_counts = nullptr;
+    unsigned int *d_fld_len = nullptr;
+    // host path
+    uint8_t *d_in = nullptr; size_t d_in_cap = 0;
+    uint8_t *d_flags = nullptr; int *d_pid = nullptr; uint32_t *d_off32 = nullptr; size_t d_fields_cap = 0;
+    fxg::Slot slots[3];                 // 0,1: host path; 2: device-resident path
+    std::deque<int> inflight;
+    uint64_t total_selected = 0;
+    int last_launches = 0;
+};
+
+namespace fxg {
+
+int set_error(fxg_ctx *ctx, int code, const std::string &msg)
+{
+    g_last_error = msg;
+    if (ctx) ctx->err = msg;
+    return code;
+}
+int set_cuda_error(fxg_ctx *ctx, cudaError_t e, const char *what)
+{
+    return set_error(ctx, FXG_ERR_CUDA, std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what);
+}
+
+template <typename T> static cudaError_t dev_realloc(T *&p, size_t n)
+{
+    if (p) { cudaFree(p); p = nullptr; }
+    if (n == 0) return cudaSuccess;
+    return cudaMalloc((void **)&p, n * sizeof(T));
+}
+template <typename T> static cudaError_t host_realloc(T *&p, size_t n)
+{
+    if (p) { cudaFreeHost(p); p = nullptr; }
+    if (n == 0) return cudaSuccess;
+    return cudaHostAlloc((void **)&p, n * sizeof(T), cudaHostAllocDefault);
+}
+
+// ---------------------------------------------------------------- literal table (host)
+static void build_literal_table(fxg_ctx *ctx)
+{
+    LiteralTable &T = ctx->h_lit;
+    memset(&T, 0, sizeof T);
+    T.n_patterns = (int)ctx->npat;
+    int minlen = 1 << 30;
+    bool any_valid = false;
+    for (uint32_t q = 0; q < ctx->npat && q < 2; ++q) {
+        int len = (int)(ctx->off[q + 1] - ctx->off[q]);
+        T.pat_len[q] = len; T.pat_off[q] = (int)ctx->off[q];
+        if (len == 0) T.all_match = 1;
+        bool has_nl = memchr(ctx->blob.data() + ctx->off[q], '\n', (size_t)len) != nullptr;
+        if (has_nl) { T.pat_len[q] = -1; continue; }      // can never occur inside a field
+        any_valid = true;
+        if (len < minlen) minlen = len;
+    }
+    if (!any_valid) { T.never = 1; T.unit = 8; return; }
+    if (T.all_match) { T.unit = 8; return; }
+    T.unit = minlen >= 15 ? 8 : (minlen >= 7 ? 4 : (minlen >= 3 ? 2 : 1));
+    const int U = T.unit;
+    std::vector<unsigned long long> keys; std::vector<unsigned short> masks;
+    for (uint32_t q = 0; q < ctx->npat && q < 2; ++q) {
+        if (T.pat_len[q] < 0) continue;
+        const uint8_t *p = ctx->blob.data() + ctx->off[q];
+        for (int s = 0; s < U; ++s) {
+            unsigned long long k = 0;
+            for (int b = 0; b < U; ++b) k |= (unsigned long long)p[s + b] << (8 * b);
+            size_t i = 0;
+            for (; i < keys.size(); ++i) if (keys[i] == k) break;
+            if (i == keys.size()) { keys.push_back(k); masks.push_back(0); }
+            masks[i] |= (unsigned short)(1u << (q * 8 + s));
+        }
+    }
+    T.n_keys = (int)keys.size();
+    if (U == 8) {
+        unsigned long long rng = 0x243F6A8885A308D3ull;
+        for (int attempt = 0; attempt < 100000; ++attempt) {
+            rng = rng * 6364136223846793005ull + 1442695040888963407ull;
+            unsigned int m1 = (unsigned int)(rng >> 32) | 1u;
+            rng = rng * 6364136223846793005ull + 1442695040888963407ull;
+            unsigned int m2 = (unsigned int)(rng >> 32) | 1u;
+            bool used[64] = {false}; bool ok = true;
+            for (size_t i = 0; i < keys.size() && ok; ++i) {
+                unsigned int lo = (unsigned int)keys[i], hi = (unsigned int)(keys[i] >> 32);
+                unsigned int h = ((lo * m1) ^ (hi * m2)) >> 26;
+                if (used[h]) ok = false; else used[h] = true;
+            }
+            if (ok) { T.mul1 = m1; T.mul2 = m2; break; }
+        }
+        for (size_t i = 0; i < keys.size(); ++i) {
+            unsigned int lo = (unsigned int)keys[i], hi = (unsigned int)(keys[i] >> 32);
+            unsigned int h = ((lo * T.mul1) ^ (hi * T.mul2)) >> 26;
+            T.keys[h] = keys[i]; T.masks[h] = masks[i];
+        }
+    } else {
+        for (size_t i = 0; i < keys.size() && i < 64; ++i) { T.keys[i] = keys[i]; T.masks[i] = masks[i]; }
+    }
+    // patterns that cannot match keep pat_len -1: verification skips them (no key bits set)
+}
+
+// ---------------------------------------------------------------- Aho-Corasick DFA (host build)
+static int build_ac(fxg_ctx *ctx)
+{
+    const uint32_t n = ctx->npat;
+    std::vector<uint8_t> cls(256, 0);
+    int ncls = 1;
+    {
+        bool used[256] = {false};
+        for (size_t i = 0; i < ctx->blob.size(); ++i) used[ctx->blob[i]] = true;
+        for (int b = 0; b < 256; ++b) if (used[b]) cls[b] = (uint8_t)(ncls++);
+    }
+    size_t max_states = ctx->blob.size() + 1;
+    if ((double)max_states * ncls * 4.0 > 24e9) return set_error(ctx, FXG_ERR_UNSUPPORTED, "pattern set too large for the DFA engine");
+    std::vector<int> next(max_states * (size_t)ncls, -1), term(max_states, -1);
+    size_t ns = 1;
+    for (uint32_t i = 0; i < n; ++i) {
+        size_t s = 0;
+        for (uint32_t j = ctx->off[i]; j < ctx->off[i + 1]; ++j) {
+            int c = cls[ctx->blob[j]];
+            int t = next[s * ncls + c];
+            if (t < 0) { t = (int)ns++; next[s * ncls + c] = t; }
+            s = (size_t)t;
+        }
+        if (term[s] < 0) term[s] = (int)i;
+    }
+    next.resize(ns * (size_t)ncls); term.resize(ns);
+    std::vector<int> fail(ns, 0), out(ns, -1), queue; queue.reserve(ns);
+    out[0] = term[0];
+    for (int c = 0; c < ncls; ++c) {
+        int t = next[c];
+        if (t < 0) next[c] = 0; else { fail[t] = 0; queue.push_back(t); }
+    }
+    for (size_t qh = 0; qh < queue.size(); ++qh) {
+        int s = queue[qh], f = fail[s];
+        out[s] = term[s] >= 0 ? term[s] : out[f];     // longest pattern that is a suffix of this state
+        for (int c = 0; c < ncls; ++c) {
+            int t = next[(size_t)s * ncls + c];
+            if (t < 0) next[(size_t)s * ncls + c] = next[(size_t)f * ncls + c];
+            else { fail[t] = next[(size_t)f * ncls + c]; queue.push_back(t); }
+        }
+    }
+    cudaError_t e;
+    if ((e = dev_realloc(ctx->d_cls, 256)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc cls");
+    if ((e = dev_realloc(ctx->d_next, next.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc dfa");
+    if ((e = dev_realloc(ctx->d_out, out.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc dfa out");
+    cudaMemcpy(ctx->d_cls, cls.data(), 256, cudaMemcpyHostToDevice);
+    cudaMemcpy(ctx->d_next, next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice);
+    e = cudaMemcpy(ctx->d_out, out.data(), out.size() * sizeof(int), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa");
+    ctx->ac_ncls = ncls; ctx->ac_nstates = (int)ns;
+    return FXG_OK;
+}
+
+// ---------------------------------------------------------------- exact table (host build)
+static int build_exact(fxg_ctx *ctx)
+{
+    const uint32_t n = ctx->npat;
+    size_t nslots = 16;
+    while (nslots < (size_t)n * 2) nslots <<= 1;
+    std::vector<unsigned long long> sh(nslots, 0); std::vector<int> sp(nslots, -1);
+    unsigned int mask = (unsigned int)(nslots - 1);
+    for (uint32_t i = 0; i < n; ++i) {
+        unsigned long long h = fxg_hash_bytes(ctx->blob.data() + ctx->off[i], ctx->off[i + 1] - ctx->off[i]);
+        unsigned int slot = (unsigned int)(h >> 20) & mask;
+        while (sh[slot] != 0) slot = (slot + 1) & mask;
+        sh[slot] = h; sp[slot] = (int)i;
+    }
+    cudaError_t e;
+    if ((e = dev_realloc(ctx->d_slot_hash, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
+    if ((e = dev_realloc(ctx->d_slot_pat, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
+    cudaMemcpy(ctx->d_slot_hash, sh.data(), nslots * 8, cudaMemcpyHostToDevice);
+    e = cudaMemcpy(ctx->d_slot_pat, sp.data(), nslots * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
+    ctx->exact_mask = mask;
+    return FXG_OK;
+}
+
+// ---------------------------------------------------------------- resources
+static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
+{
+    if (nbytes <= ctx->cap_bytes && ctx->d_desc) return FXG_OK;
+    size_t cap = std::max(nbytes, (size_t)1 << 20);
+    size_t ntiles = (cap + kTileBytes - 1) / kTileBytes;
+    size_t rec_cap = cap / 48 + 64;
+    size_t words = (rec_cap + 31) / 32;
+    size_t nblocks = (words + 1023) / 1024 + 1;
+    cudaError_t e;
+    if ((e = dev_realloc(ctx->d_desc, ntiles)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile descriptors");
+    if ((e = dev_realloc(ctx->d_hitbits, words + 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc hit bitset");
+    if (!ctx->d_ctr && (e = dev_realloc(ctx->d_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counters");
+    if (!ctx->d_counts && (e = dev_realloc(ctx->d_counts, 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counts");
+    if (!ctx->cfg.count_only) {
+        if ((e = dev_realloc(ctx->d_rec_start, rec_cap + 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc record starts");
+        if ((e = dev_realloc(ctx->d_block_sums, nblocks)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc block sums");
+    }
+    if (ctx->cfg.mode != FXG_MODE_LITERAL) {
+        if ((e = dev_realloc(ctx->d_fld_off, rec_cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc field table");
+        if ((e = dev_realloc(ctx->d_fld_len, rec_cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc field table");
+    }
+    ctx->cap_bytes = cap; ctx->ntiles_cap = ntiles; ctx->rec_cap = rec_cap; ctx->nblocks_cap = nblocks;
+    return FXG_OK;
+}
+
+static int ensure_slot_result(fxg_ctx *ctx, Slot &s)
+{
+    cudaError_t e;
+    if (!s.h_ctr && (e = host_realloc(s.h_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned counters");
+    if (!s.h_counts && (e = host_realloc(s.h_counts, 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned counts");
+    if (!s.done && (e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)) != cudaSuccess) return set_cuda_error(ctx, e, "event");
+    return FXG_OK;
+}
+
+static int ensure_slot_runs(fxg_ctx *ctx, Slot &s)
+{
+    size_t want = std::min<size_t>(ctx->rec_cap / 2 + 2, (size_t)1 << 26);
+    cudaError_t e;
+    if (s.d_runs_cap < want) {
+        if ((e = dev_realloc(s.d_runs, want)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc runs");
+        s.d_runs_cap = want;
+    }
+    if (s.h_runs_cap < 65536) {
+        if ((e = host_realloc(s.h_runs, 65536)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned runs");
+        s.h_runs_cap = 65536;
+    }
+    return FXG_OK;
+}
+
+// Enqueue the whole raw pipeline for one batch that is already in device memory.
+static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &s)
+{
+    int rc;
+    if (!ctx->have_patterns) return set_error(ctx, FXG_ERR_STATE, "fxg_set_patterns has not been called");
+    if ((rc = ensure_scan_capacity(ctx, nbytes)) != FXG_OK) return rc;
+    if ((rc = ensure_slot_result(ctx, s)) != FXG_OK) return rc;
+    const bool emit = !ctx->cfg.count_only;
+    if (emit && (rc = ensure_slot_runs(ctx, s)) != FXG_OK) return rc;
+    cudaStream_t st = ctx->stream;
+    ctx->last_launches = 0;
+    s.nbytes = nbytes; s.kind = 0; s.runs_copied = 0;
+    memset(s.h_ctr, 0, sizeof(ScanCounters)); s.h_counts[0] = s.h_counts[1] = 0;
+    if (nbytes == 0) { FXG_CUDA_OK(cudaEventRecord(s.done, st)); return FXG_OK; }
+
+    size_t ntiles = (nbytes + kTileBytes - 1) / kTileBytes;
+    size_t rec_cap = std::min(ctx->rec_cap, nbytes / 48 + 64);
+    size_t words = (rec_cap + 31) / 32;
+    FXG_CUDA_OK(cudaMemsetAsync(ctx->d_desc, 0, ntiles * sizeof(TileDesc), st));
+    FXG_CUDA_OK(cudaMemsetAsync(ctx->d_hitbits, 0, (words + 4) * sizeof(unsigned int), st));
+    FXG_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, sizeof(ScanCounters), st));
+    FXG_CUDA_OK(cudaMemsetAsync(ctx->d_counts, 0, 2 * sizeof(unsigned long long), st));
+    FXG_CUDA_OK(cudaMemsetAsync(&ctx->d_ctr->first_bad, 0xff, 8, st));      // min-reduced by the kernel
+    ScanParams P;
+    memset(&P, 0, sizeof P);
+    P.buf = d_buf; P.nbytes = nbytes; P.desc = ctx->d_desc; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
+    P.rec_start = emit ? ctx->d_rec_start : nullptr; P.rec_cap = rec_cap;
+    P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
+    const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
+    P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;
+    if (!literal) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
+    FXG_CUDA_OK(launch_scan_raw(P, st));
+    ctx->last_launches += 1;
+    if (!literal) {
+        FieldSrc src; memset(&src, 0, sizeof src);
+        src.base = d_buf; src.off64 = ctx->d_fld_off; src.len32 = ctx->d_fld_len; src.n_lines_dev = &ctx->d_ctr->n_lines;
+        FieldOut O; memset(&O, 0, sizeof O);
+        O.hitbits = ctx->d_hitbits; O.n_hits = &ctx->d_ctr->n_hits;
+        if (ctx->cfg.mode == FXG_MODE_MULTI) {
+            AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
+            FXG_CUDA_OK(launch_fields_ac(src, rec_cap, A, O, st));
+        } else {
+            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask};
+            FXG_CUDA_OK(launch_fields_exact(src, rec_cap, E, O, st));
+        }
+        ctx->last_launches += 1;
+    }
+    if (emit) {
+        int inv = ctx->cfg.invert ? 1 : 0;
+        if (literal && ctx->h_lit.all_match) inv ^= 1;     // every record matches: hit bits stay 0
+        FXG_CUDA_OK(launch_compact(ctx->d_hitbits, ctx->d_rec_start, ctx->d_ctr, rec_cap, ctx->d_block_sums, ctx->d_counts,
+                                   s.d_runs, s.d_runs_cap, inv, st, &ctx->last_launches));
+        FXG_CUDA_OK(cudaMemcpyAsync(s.h_counts, ctx->d_counts, 16, cudaMemcpyDeviceToHost, st));
+        FXG_CUDA_OK(cudaMemcpyAsync(s.h_runs, s.d_runs, std::min<size_t>(s.h_runs_cap, s.d_runs_cap) * sizeof(fxg_run),
+                                    cudaMemcpyDeviceToHost, st));
+        s.runs_copied = std::min<size_t>(s.h_runs_cap, s.d_runs_cap);
+    }
+    FXG_CUDA_OK(cudaMemcpyAsync(s.h_ctr, ctx->d_ctr, sizeof(ScanCounters), cudaMemcpyDeviceToHost, st));
+    FXG_CUDA_OK(cudaEventRecord(s.done, st));
+    return FXG_OK;
+}
+
+static int finish_raw(fxg_ctx *ctx, Slot &s, fxg_result *res)
+{
+    FXG_CUDA_OK(cudaEventSynchronize(s.done));
+    memset(res, 0, sizeof *res);
+    const ScanCounters &c = *s.h_ctr;
+    res->n_lines = c.n_lines;
+    res->n_records = c.n_lines >> 2;
+    unsigned int viol = c.violation;
+    if (s.nbytes && (c.last_byte != '\n' || (c.n_lines & 3))) viol |= FXG_V_TRUNCATED;
+    res->violation = viol;
+    res->canonical_ok = viol == 0;
+    res->first_bad_offset = c.first_bad;
+    res->consumed_bytes = viol == 0 ? s.nbytes : 0;
+    const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
+    res->n_matched = (literal && ctx->h_lit.all_match) ? res->n_records : c.n_hits;
+    res->n_selected = ctx->cfg.invert ? res->n_records - res->n_matched : res->n_matched;
+    if (!ctx->cfg.count_only && s.nbytes) {
+        unsigned long long nr = s.h_counts[0];
+        if (nr > s.d_runs_cap) return set_error(ctx, FXG_ERR_NOMEM, "selected-run list overflow; use smaller batches");
+        if (nr > s.runs_copied) {
+            cudaError_t e;
+            if (s.h_runs_cap < nr) {
+                if ((e = host_realloc(s.h_runs, (size_t)nr)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned runs");
+                s.h_runs_cap = (size_t)nr;
+            }
+            // d_runs of this slot is not touched again until the slot is resubmitted
+            FXG_CUDA_OK(cudaMemcpy(s.h_runs, s.d_runs, (size_t)nr * sizeof(fxg_run), cudaMemcpyDeviceToHost));
+        }
+        res->n_runs = nr; res->runs = s.h_runs;
+    }
+    return FXG_OK;
+}
+
+}  // namespace fxg
+
+using namespace fxg;
+
+// ================================================================= C ABI
+extern "C" int fxg_device_count(int *n)
+{
+    if (!n) return FXG_ERR_ARG;
+    cudaError_t e = cudaGetDeviceCount(n);
+    if (e != cudaSuccess) { *n = 0; return set_cuda_error(nullptr, e, "cudaGetDeviceCount"); }
+    return FXG_OK;
+}
+
+extern "C" const char *fxg_last_error(const fxg_ctx *ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+extern "C" int fxg_create(const fxg_config *cfg, fxg_ctx **out)
+{
+    if (!cfg || !out) return set_error(nullptr, FXG_ERR_ARG, "null argument");
+    if (cfg->mode < 0 || cfg->mode > 2 || cfg->target < 0 || cfg->target > 3) return set_error(nullptr, FXG_ERR_ARG, "bad mode/target");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0)
+        return set_error(nullptr, FXG_ERR_CUDA, std::string("no usable CUDA device (there is no CPU fallback): ") +
+                                                    (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    if (cfg->device < 0 || cfg->device >= ndev) return set_error(nullptr, FXG_ERR_ARG, "bad device ordinal");
+    if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) return set_cuda_error(nullptr, e, "cudaSetDevice");
+    fxg_ctx *ctx = new (std::nothrow) fxg_ctx();
+    if (!ctx) return set_error(nullptr, FXG_ERR_NOMEM, "out of memory");
+    ctx->cfg = *cfg;
+    if (ctx->cfg.batch_bytes == 0) ctx->cfg.batch_bytes = 256ull << 20;
+    if (cfg->stream) ctx->stream = (cudaStream_t)cfg->stream;
+    else {
+        if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { delete ctx; return set_cuda_error(nullptr, e, "stream"); }
+        ctx->own_stream = true;
+    }
+    *out = ctx;
+    return FXG_OK;
+}
+
+extern "C" void fxg_destroy(fxg_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->cfg.device);
+    cudaStreamSynchronize(ctx->stream);
+    for (Slot &s : ctx->slots) {
+        if (s.pinned) cudaFreeHost(s.pinned);
+        if (s.h_ctr) cudaFreeHost(s.h_ctr);
+        if (s.h_counts) cudaFreeHost(s.h_counts);
+        if (s.h_runs) cudaFreeHost(s.h_runs);
+        if (s.h_flags) cudaFreeHost(s.h_flags);
+        if (s.h_pid) cudaFreeHost(s.h_pid);
+        if (s.h_off) cudaFreeHost(s.h_off);
+        if (s.d_runs) cudaFree(s.d_runs);
+        if (s.done) cudaEventDestroy(s.done);
+    }
+    void *dev[] = {ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat,
+                   ctx->d_desc, ctx->d_ctr, ctx->d_hitbits, ctx->d_rec_start, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
+                   ctx->d_fld_len, ctx->d_in, ctx->d_flags, ctx->d_pid, ctx->d_off32};
+    for (void *p : dev) if (p) cudaFree(p);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" int fxg_set_patterns(fxg_ctx *ctx, const uint8_t *blob, const uint32_t *off, uint32_t n)
+{
+    if (!ctx || !off || (n && !blob && off[n])) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    if (n == 0) return set_error(ctx, FXG_ERR_ARG, "empty pattern set");
+    if (ctx->cfg.mode == FXG_MODE_LITERAL && n > 2) return set_error(ctx, FXG_ERR_ARG, "literal mode takes 1 or 2 patterns");
+    cudaSetDevice(ctx->cfg.device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->npat = n;
+    ctx->off.assign(off, off + n + 1);
+    ctx->blob.assign(blob, blob + off[n]);
+    cudaError_t e;
+    if ((e = dev_realloc(ctx->d_pat, ctx->blob.size() + 16)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc patterns");
+    if ((e = dev_realloc(ctx->d_patoff, (size_t)n + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc patterns");
+    if (!ctx->blob.empty()) cudaMemcpy(ctx->d_pat, ctx->blob.data(), ctx->blob.size(), cudaMemcpyHostToDevice);
+    if ((e = cudaMemcpy(ctx->d_patoff, ctx->off.data(), ((size_t)n + 1) * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
+        return set_cuda_error(ctx, e, "upload patterns");
+    int rc = FXG_OK;
+    if (ctx->cfg.mode == FXG_MODE_LITERAL) {
+        build_literal_table(ctx);
+        if (!ctx->d_lit && (e = dev_realloc(ctx->d_lit, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc literal table");
+        if ((e = cudaMemcpy(ctx->d_lit, &ctx->h_lit, sizeof(LiteralTable), cudaMemcpyHostToDevice)) != cudaSuccess)
+            return set_cuda_error(ctx, e, "upload literal table");
+    } else if (ctx->cfg.mode == FXG_MODE_MULTI) rc = build_ac(ctx);
+    else rc = build_exact(ctx);
+    if (rc == FXG_OK) ctx->have_patterns = true;
+    return rc;
+}
+
+// ---------------------------------------------------------------- host path
+static int free_slot(fxg_ctx *ctx)
+{
+    for (int i = 0; i < 2; ++i) if (ctx->slots[i].state == 0) return i;
+    return -1;
+}
+
+extern "C" int fxg_acquire_buffer(fxg_ctx *ctx, void **pinned, size_t *cap)
+{
+    if (!ctx || !pinned || !cap) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    for (int i = 0; i < 2; ++i) if (ctx->slots[i].state == 1) return set_error(ctx, FXG_ERR_STATE, "a buffer is already lent out");
+    int i = free_slot(ctx);
+    if (i < 0) return set_error(ctx, FXG_ERR_STATE, "both buffers are in flight: call fxg_collect first");
+    Slot &s = ctx->slots[i];
+    if (!s.pinned) {
+        cudaError_t e = cudaHostAlloc(&s.pinned, ctx->cfg.batch_bytes + 64, cudaHostAllocDefault);
+        if (e != cudaSuccess) return set_cuda_error(ctx, e, "cudaHostAlloc(staging)");
+    }
+    s.state = 1;
+    *pinned = s.pinned; *cap = ctx->cfg.batch_bytes;
+    return FXG_OK;
+}
+
+static int ensure_d_in(fxg_ctx *ctx, size_t n)
+{
+    if (ctx->d_in_cap >= n + 64) return FXG_OK;
+    size_t cap = std::max<size_t>(n, ctx->cfg.batch_bytes) + 64;
+    cudaError_t e = dev_realloc(ctx->d_in, cap);
+    if (e != cudaSuccess) return set_cuda_error(ctx, e, "alloc device input buffer");
+    ctx->d_in_cap = cap;
+    return FXG_OK;
+}
+
+static int submit_raw_common(fxg_ctx *ctx, int si, const void *src, size_t nbytes, int is_last)
+{
+    Slot &s = ctx->slots[si];
+    int rc;
+    if (nbytes > ctx->cfg.batch_bytes) return set_error(ctx, FXG_ERR_ARG, "batch larger than batch_bytes");
+    if ((rc = ensure_d_in(ctx, nbytes)) != FXG_OK) return rc;
+    if (nbytes) FXG_CUDA_OK(cudaMemcpyAsync(ctx->d_in, src, nbytes, cudaMemcpyHostToDevice, ctx->stream));
+    s.is_last = is_last;
+    if ((rc = enqueue_raw(ctx, ctx->d_in, nbytes, s)) != FXG_OK) return rc;
+    s.state = 2;
+    ctx->inflight.push_back(si);
+    return FXG_OK;
+}
+
+extern "C" int fxg_submit_raw(fxg_ctx *ctx, size_t nbytes, int is_last)
+{
+    if (!ctx) return set_error(ctx, FXG_ERR_ARG, "null ctx");
+    cudaSetDevice(ctx->cfg.device);
+    int si = -1;
+    for (int i = 0; i < 2; ++i) if (ctx->slots[i].state == 1) si = i;
+    if (si < 0) return set_error(ctx, FXG_ERR_STATE, "no acquired buffer");
+    return submit_raw_common(ctx, si, ctx->slots[si].pinned, nbytes, is_last);
+}
+
+extern "C" int fxg_submit_raw_from(fxg_ctx *ctx, const void *host_buf, size_t nbytes, int is_last)
+{
+    if (!ctx || (!host_buf && nbytes)) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    for (int i = 0; i < 2; ++i) if (ctx->slots[i].state == 1) return set_error(ctx, FXG_ERR_STATE, "a buffer is lent out");
+    int si = free_slot(ctx);
+    if (si < 0) return set_error(ctx, FXG_ERR_STATE, "both slots are in flight: call fxg_collect first");
+    return submit_raw_common(ctx, si, host_buf, nbytes, is_last);
+}
+
+extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *off, uint32_t nrec)
+{
+    if (!ctx || (!off && nrec)) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    if (!ctx->have_patterns) return set_error(ctx, FXG_ERR_STATE, "fxg_set_patterns has not been called");
+    int si = -1;
+    for (int i = 0; i < 2; ++i) if (ctx->slots[i].state == 1) si = i;
+    if (si < 0) return set_error(ctx, FXG_ERR_STATE, "no acquired buffer");
+    if (nbytes > ctx->cfg.batch_bytes) return set_error(ctx, FXG_ERR_ARG, "batch larger than batch_bytes");
+    Slot &s = ctx->slots[si];
+    int rc;
+    cudaError_t e;
+    if ((rc = ensure_slot_result(ctx, s)) != FXG_OK) return rc;
+    if ((rc = ensure_d_in(ctx, nbytes)) != FXG_OK) return rc;
+    if (s.fields_cap < (size_t)nrec + 1) {
+        size_t cap = std::max<size_t>((size_t)nrec + 1, 1 << 16);
+        if ((e = host_realloc(s.h_flags, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned flags");
+        if ((e = host_realloc(s.h_pid, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned ids");
+        if ((e = host_realloc(s.h_off, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned offsets");
+        s.fields_cap = cap;
+    }
+    if (ctx->d_fields_cap < (size_t)nrec + 1) {
+        size_t cap = std::max<size_t>((size_t)nrec + 1, 1 << 16);
+        if ((e = dev_realloc(ctx->d_flags, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc flags");
+        if ((e = dev_realloc(ctx->d_pid, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc ids");
+        if ((e = dev_realloc(ctx->d_off32, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc offsets");
+        ctx->d_fields_cap = cap;
+    }
+    if (!ctx->d_ctr && (e = dev_realloc(ctx->d_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counters");
+    cudaStream_t st = ctx->stream;
+    ctx->last_launches = 0;
+    s.kind = 1; s.nrec = nrec; s.nbytes = nbytes;
+    memset(s.h_ctr, 0, sizeof(ScanCounters));
+    if (nrec) {
+        memcpy(s.h_off, off, ((size_t)nrec + 1) * 4);
+        if (nbytes) FXG_CUDA_OK(cudaMemcpyAsync(ctx->d_in, s.pinned, nbytes, cudaMemcpyHostToDevice, st));
+        FXG_CUDA_OK(cudaMemcpyAsync(ctx->d_off32, s.h_off, ((size_t)nrec + 1) * 4, cudaMemcpyHostToDevice, st));
+        FXG_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, sizeof(ScanCounters), st));
+        FieldSrc src; memset(&src, 0, sizeof src);
+        src.base = ctx->d_in; src.off32 = ctx->d_off32;
+        FieldOut O; memset(&O, 0, sizeof O);
+        O.flags = ctx->d_flags; O.pattern_id = ctx->cfg.want_pattern_id ? ctx->d_pid : nullptr; O.n_hits = &ctx->d_ctr->n_hits;
+        if (ctx->cfg.mode == FXG_MODE_LITERAL) {
+            LiteralFieldParams L; memset(&L, 0, sizeof L);
+            L.n_patterns = (int)std::min<uint32_t>(ctx->npat, 2);
+            for (int q = 0; q < L.n_patterns; ++q) { L.pat[q] = ctx->d_pat + ctx->off[q]; L.len[q] = (int)(ctx->off[q + 1] - ctx->off[q]); }
+            FXG_CUDA_OK(launch_fields_literal(src, nrec, L, O, st));
+        } else if (ctx->cfg.mode == FXG_MODE_MULTI) {
+            AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
+            FXG_CUDA_OK(launch_fields_ac(src, nrec, A, O, st));
+        } else {
+            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask};
+            FXG_CUDA_OK(launch_fields_exact(src, nrec, E, O, st));
+        }
+        ctx->last_launches = 1;
+        FXG_CUDA_OK(cudaMemcpyAsync(s.h_flags, ctx->d_flags, nrec, cudaMemcpyDeviceToHost, st));
+        if (ctx->cfg.want_pattern_id) FXG_CUDA_OK(cudaMemcpyAsync(s.h_pid, ctx->d_pid, (size_t)nrec * 4, cudaMemcpyDeviceToHost, st));
+        FXG_CUDA_OK(cudaMemcpyAsync(s.h_ctr, ctx->d_ctr, sizeof(ScanCounters), cudaMemcpyDeviceToHost, st));
+    }
+    FXG_CUDA_OK(cudaEventRecord(s.done, st));
+    s.state = 2;
+    ctx->inflight.push_back(si);
+    return FXG_OK;
+}
+
+extern "C" int fxg_collect(fxg_ctx *ctx, fxg_result *res)
+{
+    if (!ctx || !res) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    if (ctx->inflight.empty()) return set_error(ctx, FXG_ERR_STATE, "nothing submitted");
+    int si = ctx->inflight.front();
+    ctx->inflight.pop_front();
+    Slot &s = ctx->slots[si];
+    int rc = FXG_OK;
+    if (s.kind == 0) rc = finish_raw(ctx, s, res);
+    else {
+        FXG_CUDA_OK(cudaEventSynchronize(s.done));
+        memset(res, 0, sizeof *res);
+        res->n_records = s.nrec;
+        res->n_matched = res->n_selected = s.h_ctr->n_hits;
+        res->canonical_ok = 1;
+        res->flags = s.h_flags;
+        res->pattern_id = ctx->cfg.want_pattern_id ? s.h_pid : nullptr;
+    }
+    s.state = 0;
+    if (rc == FXG_OK) ctx->total_selected += res->n_selected;
+    return rc;
+}
+
+extern "C" int fxg_count(fxg_ctx *ctx, uint64_t *total)
+{
+    if (!ctx || !total) return FXG_ERR_ARG;
+    *total = ctx->total_selected;
+    return FXG_OK;
+}
+
+extern "C" size_t fxg_find_record_cut(const uint8_t *buf, size_t n)
+{
+    // A record starts at c iff buf[c]=='@' at a line start and the line after next starts
+    // with '+'.  For canonical FASTQ this is exact (a quality line may start with '@', but
+    // then the line two below it is a sequence line, which cannot start with '+'); for
+    // anything else the GPU predicate rejects the batch and the caller re-routes it.
+    if (!buf || n == 0) return 0;
+    size_t pos = n;
+    for (int tries = 0; tries < 64 && pos > 0; ++tries) {
+        // line start at or before pos-1
+        size_t c = pos - 1;
+        while (c > 0 && buf[c - 1] != '\n') --c;
+        if (buf[c] == '@') {
+            const uint8_t *e1 = (const uint8_t *)memchr(buf + c, '\n', n - c);
+            if (e1) {
+                const uint8_t *e2 = (const uint8_t *)memchr(e1 + 1, '\n', n - (size_t)(e1 + 1 - buf));
+                if (e2 && (size_t)(e2 + 1 - buf) < n && e2[1] == '+') return c;
+            }
+        }
+        pos = c;        // continue with the previous line
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------- device-resident path
+extern "C" int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes)
+{
+    if (!ctx || (!d_buf && nbytes)) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    Slot &s = ctx->slots[2];
+    int rc = enqueue_raw(ctx, (const uint8_t *)d_buf, (size_t)nbytes, s);
+    if (rc == FXG_OK) s.state = 2;
+    return rc;
+}
+
+extern "C" int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res)
+{
+    if (!ctx || !res) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    Slot &s = ctx->slots[2];
+    if (s.state != 2) return set_error(ctx, FXG_ERR_STATE, "no device scan in flight");
+    int rc = finish_raw(ctx, s, res);
+    s.state = 0;
+    return rc;
+}
+
+extern "C" int fxg_last_launch_count(const fxg_ctx *ctx) { return ctx ? ctx->last_launches : 0; }
+
+extern "C" int fxg_synth_device(fxg_ctx *ctx, const fxg_synth_spec *s, void *d_out)
+{
+    if (!ctx || !s || !d_out) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    FXG_CUDA_OK(launch_synth(*s, (uint8_t *)d_out, ctx->stream));
+    FXG_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    return FXG_OK;
+}
+
+extern "C" int fxg_host_alloc(void **p, size_t n)
+{
+    if (!p) return FXG_ERR_ARG;
+    cudaError_t e = cudaHostAlloc(p, n, cudaHostAllocDefault);
+    if (e != cudaSuccess) { *p = nullptr; return set_cuda_error(nullptr, e, "cudaHostAlloc"); }
+    return FXG_OK;
+}
+extern "C" int fxg_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+    return FXG_OK;
+}

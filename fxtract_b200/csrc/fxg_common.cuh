@@ -1,0 +1,154 @@
+// fxg_common.cuh -- shared device/host declarations of libfxgpu (sm_100a only).
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <cuda_runtime.h>
+#include "../../include/fxgpu.h"
+
+struct fxg_ctx;
+
+namespace fxg {
+
+int set_cuda_error(fxg_ctx *ctx, cudaError_t e, const char *what);
+
+// ---------------------------------------------------------------- geometry
+constexpr int kTileBytes = 32768;              // bytes of input one CTA scans
+constexpr int kThreads = 256;                  // threads per CTA (8 warps)
+constexpr int kChunks = kTileBytes / 16;       // 16-byte chunks per tile (2048)
+constexpr int kChunksPerThread = kChunks / kThreads;   // 8
+constexpr int kMaxTileLines = 4096;            // newline-table capacity per tile
+constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
+
+// ---------------------------------------------------------------- lookback
+// One descriptor per tile for the single-pass (decoupled look-back) prefix sum of
+// newline counts.  Besides the count it carries the tile's own last three newline
+// positions, so a tile can check record structure (|qual| == |seq|, "+" line, '@')
+// for records that straddle its left edge without re-reading its predecessor.
+struct __align__(32) TileDesc {
+    unsigned long long status;   // [63:62] flag (0 none, 1 aggregate, 2 inclusive) [61:60] min(own count,3) [59:0] value
+    long long p1, p2, p3;        // own last / 2nd last / 3rd last newline (global offsets)
+};
+constexpr unsigned long long kFlagAgg = 1ull << 62;
+constexpr unsigned long long kFlagInc = 2ull << 62;
+constexpr unsigned long long kValMask = (1ull << 60) - 1;
+constexpr long long kNoPos = -(1ll << 62);
+
+// ---------------------------------------------------------------- counters
+struct ScanCounters {
+    unsigned long long n_lines;
+    unsigned long long n_hits;        // records with >= 1 hit (deduplicated through the hit bitset)
+    unsigned long long first_bad;     // min offset of a violation
+    unsigned int violation;           // FXG_V_* bitmask
+    unsigned int last_byte;           // last byte of the batch (must be '\n')
+    unsigned int ticket;              // dynamic tile ticket
+    unsigned int pad;
+};
+
+// ---------------------------------------------------------------- literal matcher tables
+// Aligned-unit filter: an occurrence of a pattern of length >= 2U-1 at offset p
+// fully contains the U-byte unit at ceil_U(p); the table holds, for every pattern
+// and every shift s in [0,U), the U bytes pat[s..s+U).  One lookup per aligned
+// unit of text replaces one comparison per text position.
+struct LiteralTable {
+    int n_patterns;              // 1 or 2
+    int unit;                    // 8, 4, 2 or 1 bytes
+    int n_keys;                  // unique keys
+    int all_match;               // empty pattern: every record matches (strstr(hay,"") != NULL)
+    int never;                   // pattern contains '\n': can never match a field
+    unsigned int mul1, mul2;     // perfect-hash multipliers (unit == 8)
+    int pat_len[2];
+    int pat_off[2];              // offsets into pat_bytes
+    unsigned long long keys[64]; // unit==8: 64-slot perfect hash; else first n_keys entries
+    unsigned short masks[64];    // bit (pattern*8 + shift) set if keys[i] == pat[shift..shift+U)
+};
+
+struct ScanParams {
+    const uint8_t *buf;
+    unsigned long long nbytes;
+    TileDesc *desc;
+    ScanCounters *ctr;
+    unsigned int *hitbits;            // 1 bit per record
+    unsigned long long *rec_start;    // [rec_cap + 1] or nullptr (count-only)
+    unsigned long long rec_cap;
+    const LiteralTable *lit;          // device copy
+    const uint8_t *pat_bytes;         // device copy of pattern bytes
+    int target;
+    int match_enabled;                // 0: index/validate only (multi / exact use the field table)
+    // field table for the second-stage matchers (multi / exact): target field of record k
+    unsigned long long *fld_off;      // [rec_cap] or nullptr
+    unsigned int *fld_len;            // [rec_cap]
+};
+
+// ---------------------------------------------------------------- field engine
+struct AcDevice {              // byte-class compressed Aho-Corasick DFA
+    const uint8_t *cls;        // [256]
+    const int *next;           // [nstates * ncls]
+    const int *out;            // [nstates] longest pattern ending here or -1
+    int ncls;
+    int nstates;
+};
+struct ExactDevice {           // open-addressing table over whole-field keys
+    const unsigned long long *slot_hash;   // [nslots] 0 = empty
+    const int *slot_pat;                   // [nslots] pattern id
+    const uint8_t *blob;                   // pattern bytes
+    const unsigned int *off;               // [n+1]
+    unsigned int mask;                     // nslots - 1
+};
+
+// 64-bit FNV-1a style hash with a final mix; identical on host and device.
+__host__ __device__ inline unsigned long long fxg_hash_bytes(const uint8_t *p, unsigned int n)
+{
+    unsigned long long h = 0xcbf29ce484222325ull;
+    for (unsigned int i = 0; i < n; ++i) { h ^= p[i]; h *= 0x100000001b3ull; }
+    h ^= h >> 32; h *= 0x9e3779b97f4a7c15ull; h ^= h >> 29;
+    return h ? h : 1ull;
+}
+
+struct FieldSrc {
+    const uint8_t *base;
+    const unsigned int *off32;           // packed layout: [n+1] offsets, or
+    const unsigned long long *off64;     // table layout: start offsets ...
+    const unsigned int *len32;           // ... and lengths
+    const unsigned long long *n_lines_dev; // raw path: field count = *n_lines_dev / 4 (capped by the launch's n)
+    __device__ __forceinline__ unsigned long long count(unsigned long long cap) const
+    {
+        if (!n_lines_dev) return cap;
+        unsigned long long v = *n_lines_dev >> 2;
+        return v < cap ? v : cap;
+    }
+    __device__ __forceinline__ void get(unsigned long long k, const uint8_t *&p, unsigned int &len) const
+    {
+        if (off32) { unsigned int a = off32[k]; p = base + a; len = off32[k + 1] - a; }
+        else { p = base + off64[k]; len = len32[k]; }
+    }
+};
+
+struct FieldOut {
+    uint8_t *flags;            // 1 byte per field or nullptr
+    int *pattern_id;           // first-hit pattern id per field or nullptr
+    unsigned int *hitbits;     // 1 bit per field (raw path) or nullptr
+    unsigned long long *n_hits;
+};
+
+struct LiteralFieldParams {
+    const uint8_t *pat[2];
+    int len[2];
+    int n_patterns;
+};
+
+
+// launchers (fxg_scan.cu / fxg_fields.cu / fxg_synth.cu)
+size_t scan_smem_bytes();
+cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream);
+cudaError_t launch_compact(const unsigned int *hitbits, const unsigned long long *rec_start, const ScanCounters *ctr,
+                           unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
+                           fxg_run *runs, unsigned long long run_cap, int invert, cudaStream_t stream, int *launches);
+cudaError_t launch_fields_literal(const FieldSrc &src, unsigned long long n, const LiteralFieldParams &L,
+                                  const FieldOut &O, cudaStream_t st);
+cudaError_t launch_fields_ac(const FieldSrc &src, unsigned long long n, const AcDevice &A, const FieldOut &O, cudaStream_t st);
+cudaError_t launch_fields_exact(const FieldSrc &src, unsigned long long n, const ExactDevice &E, const FieldOut &O, cudaStream_t st);
+cudaError_t launch_synth(const fxg_synth_spec &s, uint8_t *d_out, cudaStream_t st);
+
+#define FXG_CUDA_OK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return fxg::set_cuda_error(ctx, e__, #expr); } while (0)
+
+}  // namespace fxg

@@ -1,0 +1,181 @@
+// fxg_synth.cu -- deterministic synthetic FASTQ, generated
+// identically by a host loop and by a CUDA kernel from a counter-based RNG keyed by
+// (seed, global record index, word), so 30-200 GB inputs can exist in HBM without
+// host I/O and any shard of the stream can be regenerated anywhere.
+//
+// Record i (global index g):
+//   @SYN:1:FC:<lane>:<tile>:<x>:<g> 1:N:0:ACGT\n     lane 1 digit, tile 4, x 5, g unpadded decimal
+//   <read_len bases, uniform ACGT, optionally with a planted pattern>\n
+//   +\n
+//   <read_len quality bytes, uniform in [33,73], so '@' can open a quality line>\n
+#include "fxg_common.cuh"
+
+namespace fxg {
+
+__host__ __device__ inline unsigned long long mix64(unsigned long long z)
+{
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__host__ __device__ inline unsigned long long rnd(unsigned long long seed, unsigned long long g, unsigned int j)
+{
+    return mix64(seed + g * 0x9E3779B97F4A7C15ull + (unsigned long long)(j + 1) * 0xD1B54A32D192ED03ull);
+}
+__host__ __device__ inline int dec_digits(unsigned long long g)
+{
+    int d = 1;
+    while (g >= 10) { g /= 10; ++d; }
+    return d;
+}
+// sum of dec_digits(x) for x in [0, n)
+__host__ __device__ inline unsigned long long digit_sum_below(unsigned long long n)
+{
+    unsigned long long s = n, p = 10;
+    for (int k = 0; k < 19; ++k) {
+        if (n > p) s += n - p; else break;
+        p *= 10;
+    }
+    return s;
+}
+__host__ __device__ inline unsigned long long rec_fixed_bytes(const fxg_synth_spec &s)
+{
+    return 39ull + 2ull * s.read_len;   // everything except the decimal index
+}
+__host__ __device__ inline unsigned long long rec_offset(const fxg_synth_spec &s, unsigned long long i)
+{
+    return i * rec_fixed_bytes(s) + digit_sum_below(s.first_record + i) - digit_sum_below(s.first_record);
+}
+__host__ __device__ inline unsigned int base_char(unsigned int code)
+{
+    return code == 0 ? 'A' : (code == 1 ? 'C' : (code == 2 ? 'G' : 'T'));
+}
+__host__ __device__ inline unsigned int pattern_base(const fxg_synth_spec &s, unsigned int p, unsigned int k)
+{
+    unsigned long long w = rnd(s.pattern_seed, p, k >> 5);
+    return (unsigned int)(w >> ((k & 31) * 2)) & 3u;
+}
+// sequence base k of global record g (2-bit code)
+__host__ __device__ inline unsigned int seq_code(const fxg_synth_spec &s, unsigned long long g, unsigned int k)
+{
+    if (s.plant_mode && s.n_patterns && s.pattern_len && s.pattern_len <= s.read_len) {
+        if ((rnd(s.seed, g, 200) % 1000000ull) < s.plant_per_million) {
+            unsigned int p = (unsigned int)(rnd(s.seed, g, 201) % s.n_patterns);
+            unsigned int o = (unsigned int)(rnd(s.seed, g, 202) % (s.read_len - s.pattern_len + 1));
+            if (k >= o && k < o + s.pattern_len) {
+                bool rc = s.plant_revcomp && (rnd(s.seed, g, 203) & 1ull);
+                unsigned int q = k - o;
+                if (!rc) return pattern_base(s, p, q);
+                return 3u - pattern_base(s, p, s.pattern_len - 1 - q);    // A<->T, C<->G with codes A0 C1 G2 T3
+            }
+        }
+    }
+    unsigned long long w = rnd(s.seed, g, k >> 5);
+    return (unsigned int)(w >> ((k & 31) * 2)) & 3u;
+}
+// byte b of the record with global index g whose index has d decimal digits
+__host__ __device__ inline unsigned int rec_byte(const fxg_synth_spec &s, unsigned long long g, int d, unsigned int b)
+{
+    const unsigned int R = s.read_len;
+    const unsigned int hl = 35u + (unsigned int)d;      // header line incl. '\n'
+    if (b < hl) {
+        unsigned long long h = rnd(s.seed, g, 100);
+        if (b < 10) { const char *pre = "@SYN:1:FC:"; return (unsigned int)pre[b]; }
+        if (b == 10) return '1' + (unsigned int)(h % 8);
+        if (b == 11) return ':';
+        if (b < 16) {
+            unsigned int tile = 1101u + (unsigned int)((h >> 8) % 1000);
+            unsigned int div = b == 12 ? 1000u : (b == 13 ? 100u : (b == 14 ? 10u : 1u));
+            return '0' + (tile / div) % 10;
+        }
+        if (b == 16) return ':';
+        if (b < 22) {
+            unsigned int x = 10000u + (unsigned int)((h >> 24) % 90000);
+            unsigned int div = 1;
+            for (unsigned int q = b; q < 21; ++q) div *= 10;
+            return '0' + (x / div) % 10;
+        }
+        if (b == 22) return ':';
+        if (b < 23u + (unsigned int)d) {
+            unsigned long long div = 1;
+            for (unsigned int q = b; q < 22u + (unsigned int)d; ++q) div *= 10;
+            return '0' + (unsigned int)((g / div) % 10);
+        }
+        unsigned int t = b - (23u + (unsigned int)d);
+        const char *suf = " 1:N:0:ACGT\n";
+        return (unsigned int)suf[t];
+    }
+    b -= hl;
+    if (b < R) return base_char(seq_code(s, g, b));
+    if (b == R) return '\n';
+    if (b == R + 1) return '+';
+    if (b == R + 2) return '\n';
+    b -= R + 3;
+    if (b < R) {
+        unsigned long long w = rnd(s.seed, g, 8 + (b >> 3));
+        unsigned int by = (unsigned int)(w >> ((b & 7) * 8)) & 0xffu;
+        return 33u + ((by * 41u) >> 8);
+    }
+    return '\n';
+}
+
+__global__ void __launch_bounds__(256) synth_kernel(fxg_synth_spec s, uint8_t *out)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned long long warp0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long i = warp0; i < s.n_records; i += nwarps) {
+        unsigned long long g = s.first_record + i;
+        int d = dec_digits(g);
+        unsigned long long off = rec_offset(s, i);
+        unsigned int len = (unsigned int)rec_fixed_bytes(s) + (unsigned int)d;
+        for (unsigned int b = lane; b < len; b += 32) out[off + b] = (uint8_t)rec_byte(s, g, d, b);
+    }
+}
+
+cudaError_t launch_synth(const fxg_synth_spec &s, uint8_t *d_out, cudaStream_t st)
+{
+    if (s.n_records == 0) return cudaSuccess;
+    unsigned long long blocks = (s.n_records + 7) / 8;
+    if (blocks > 148ull * 64) blocks = 148ull * 64;
+    synth_kernel<<<(unsigned int)blocks, 256, 0, st>>>(s, d_out);
+    return cudaGetLastError();
+}
+
+}  // namespace fxg
+
+using namespace fxg;
+
+extern "C" uint64_t fxg_synth_bytes(const fxg_synth_spec *s) { return rec_offset(*s, s->n_records); }
+extern "C" uint64_t fxg_synth_record_offset(const fxg_synth_spec *s, uint64_t i) { return rec_offset(*s, i); }
+
+extern "C" int fxg_synth_host(const fxg_synth_spec *s, uint8_t *out)
+{
+    if (!s || !out) return FXG_ERR_ARG;
+    for (unsigned long long i = 0; i < s->n_records; ++i) {
+        unsigned long long g = s->first_record + i;
+        int d = dec_digits(g);
+        unsigned long long off = rec_offset(*s, i);
+        unsigned int len = (unsigned int)rec_fixed_bytes(*s) + (unsigned int)d;
+        for (unsigned int b = 0; b < len; ++b) out[off + b] = (uint8_t)rec_byte(*s, g, d, b);
+    }
+    return FXG_OK;
+}
+
+extern "C" int fxg_synth_pattern(const fxg_synth_spec *s, uint32_t p, uint8_t *out)
+{
+    if (!s || !out) return FXG_ERR_ARG;
+    for (unsigned int k = 0; k < s->pattern_len; ++k) out[k] = (uint8_t)base_char(pattern_base(*s, p, k));
+    return FXG_OK;
+}
+
+extern "C" int fxg_synth_name(const fxg_synth_spec *s, uint64_t i, uint8_t *out, uint32_t *len)
+{
+    if (!s || !out || !len) return FXG_ERR_ARG;
+    unsigned long long g = s->first_record + i;
+    int d = dec_digits(g);
+    unsigned int n = 22u + (unsigned int)d;       // bytes 1 .. 22+d of the header line
+    for (unsigned int b = 0; b < n; ++b) out[b] = (uint8_t)rec_byte(*s, g, d, b + 1);
+    *len = n;
+    return FXG_OK;
+}
