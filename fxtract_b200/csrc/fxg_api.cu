@@ -20,6 +20,8 @@ struct Slot {
     fxg_run *d_runs = nullptr; size_t d_runs_cap = 0;
     uint8_t *h_flags = nullptr; int *h_pid = nullptr; uint32_t *h_off = nullptr; size_t fields_cap = 0;
     cudaEvent_t done = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};   // profiling: pipeline begin, scan begin, scan end, pipeline end
+    bool timed = false;
     int state = 0;                      // 0 free, 1 lent to caller, 2 submitted
     int kind = 0;                       // 0 raw, 1 fields
     size_t nbytes = 0; uint32_t nrec = 0; int is_last = 0;
@@ -53,6 +55,8 @@ struct fxg_ctx {
     std::deque<int> inflight;
     uint64_t total_selected = 0;
     int last_launches = 0;
+    bool profiling = false;
+    float last_scan_ms = 0.f, last_pipeline_ms = 0.f;
 };
 
 namespace fxg {
@@ -282,7 +286,12 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     ctx->last_launches = 0;
     s.nbytes = nbytes; s.kind = 0; s.runs_copied = 0;
     memset(s.h_ctr, 0, sizeof(ScanCounters)); s.h_counts[0] = s.h_counts[1] = 0;
+    s.timed = false;
     if (nbytes == 0) { FXG_CUDA_OK(cudaEventRecord(s.done, st)); return FXG_OK; }
+    if (ctx->profiling) {
+        for (cudaEvent_t &e : s.ev) if (!e) FXG_CUDA_OK(cudaEventCreate(&e));
+        FXG_CUDA_OK(cudaEventRecord(s.ev[0], st));
+    }
 
     size_t ntiles = (nbytes + kTileBytes - 1) / kTileBytes;
     size_t rec_cap = std::min(ctx->rec_cap, nbytes / 48 + 64);
@@ -300,7 +309,9 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;
     if (!literal) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
+    if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[1], st));
     FXG_CUDA_OK(launch_scan_raw(P, st));
+    if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[2], st));
     ctx->last_launches += 1;
     if (!literal) {
         FieldSrc src; memset(&src, 0, sizeof src);
@@ -321,11 +332,13 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
         if (literal && ctx->h_lit.all_match) inv ^= 1;     // every record matches: hit bits stay 0
         FXG_CUDA_OK(launch_compact(ctx->d_hitbits, ctx->d_rec_start, ctx->d_ctr, rec_cap, ctx->d_block_sums, ctx->d_counts,
                                    s.d_runs, s.d_runs_cap, inv, st, &ctx->last_launches));
+        if (ctx->profiling) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
         FXG_CUDA_OK(cudaMemcpyAsync(s.h_counts, ctx->d_counts, 16, cudaMemcpyDeviceToHost, st));
         FXG_CUDA_OK(cudaMemcpyAsync(s.h_runs, s.d_runs, std::min<size_t>(s.h_runs_cap, s.d_runs_cap) * sizeof(fxg_run),
                                     cudaMemcpyDeviceToHost, st));
         s.runs_copied = std::min<size_t>(s.h_runs_cap, s.d_runs_cap);
     }
+    if (ctx->profiling && !s.timed) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
     FXG_CUDA_OK(cudaMemcpyAsync(s.h_ctr, ctx->d_ctr, sizeof(ScanCounters), cudaMemcpyDeviceToHost, st));
     FXG_CUDA_OK(cudaEventRecord(s.done, st));
     return FXG_OK;
@@ -334,6 +347,11 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
 static int finish_raw(fxg_ctx *ctx, Slot &s, fxg_result *res)
 {
     FXG_CUDA_OK(cudaEventSynchronize(s.done));
+    if (s.timed) {
+        FXG_CUDA_OK(cudaEventElapsedTime(&ctx->last_scan_ms, s.ev[1], s.ev[2]));
+        FXG_CUDA_OK(cudaEventElapsedTime(&ctx->last_pipeline_ms, s.ev[0], s.ev[3]));
+        s.timed = false;
+    }
     memset(res, 0, sizeof *res);
     const ScanCounters &c = *s.h_ctr;
     res->n_lines = c.n_lines;
@@ -418,6 +436,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h_off) cudaFreeHost(s.h_off);
         if (s.d_runs) cudaFree(s.d_runs);
         if (s.done) cudaEventDestroy(s.done);
+        for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
     void *dev[] = {ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat,
                    ctx->d_desc, ctx->d_ctr, ctx->d_hitbits, ctx->d_rec_start, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
@@ -667,6 +686,21 @@ extern "C" int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res)
 
 extern "C" int fxg_last_launch_count(const fxg_ctx *ctx) { return ctx ? ctx->last_launches : 0; }
 
+extern "C" int fxg_set_profiling(fxg_ctx *ctx, int enabled)
+{
+    if (!ctx) return FXG_ERR_ARG;
+    ctx->profiling = enabled != 0;
+    return FXG_OK;
+}
+
+extern "C" int fxg_last_kernel_ms(fxg_ctx *ctx, float *scan_ms, float *pipeline_ms)
+{
+    if (!ctx) return FXG_ERR_ARG;
+    if (scan_ms) *scan_ms = ctx->last_scan_ms;
+    if (pipeline_ms) *pipeline_ms = ctx->last_pipeline_ms;
+    return FXG_OK;
+}
+
 extern "C" int fxg_synth_device(fxg_ctx *ctx, const fxg_synth_spec *s, void *d_out)
 {
     if (!ctx || !s || !d_out) return set_error(ctx, FXG_ERR_ARG, "null argument");
@@ -686,5 +720,14 @@ extern "C" int fxg_host_alloc(void **p, size_t n)
 extern "C" int fxg_host_free(void *p)
 {
     if (p) cudaFreeHost(p);
+    return FXG_OK;
+}
+
+extern "C" int fxg_copy_to_host(fxg_ctx *ctx, void *host_dst, const void *d_src, size_t n)
+{
+    if (!ctx || !host_dst || !d_src) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    FXG_CUDA_OK(cudaMemcpyAsync(host_dst, d_src, n, cudaMemcpyDeviceToHost, ctx->stream));
+    FXG_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     return FXG_OK;
 }

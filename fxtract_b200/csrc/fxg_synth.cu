@@ -9,6 +9,9 @@
 //   +\n
 //   <read_len quality bytes, uniform in [33,73], so '@' can open a quality line>\n
 #include "fxg_common.cuh"
+#include <cstring>
+#include <thread>
+#include <vector>
 
 namespace fxg {
 
@@ -149,16 +152,62 @@ using namespace fxg;
 extern "C" uint64_t fxg_synth_bytes(const fxg_synth_spec *s) { return rec_offset(*s, s->n_records); }
 extern "C" uint64_t fxg_synth_record_offset(const fxg_synth_spec *s, uint64_t i) { return rec_offset(*s, i); }
 
+// Host generator: same bytes as rec_byte(), produced a record at a time (the
+// per-record random words are drawn once, not once per byte) and on all host threads.
+static void synth_host_record(const fxg_synth_spec &s, unsigned long long g, int d, uint8_t *o)
+{
+    const unsigned int R = s.read_len;
+    unsigned long long h = rnd(s.seed, g, 100);
+    memcpy(o, "@SYN:1:FC:", 10); o += 10;
+    *o++ = (uint8_t)('1' + (unsigned int)(h % 8)); *o++ = ':';
+    unsigned int tile = 1101u + (unsigned int)((h >> 8) % 1000);
+    o[0] = '0' + tile / 1000 % 10; o[1] = '0' + tile / 100 % 10; o[2] = '0' + tile / 10 % 10; o[3] = '0' + tile % 10; o += 4;
+    *o++ = ':';
+    unsigned int x = 10000u + (unsigned int)((h >> 24) % 90000);
+    for (int k = 4; k >= 0; --k) { o[k] = '0' + x % 10; x /= 10; }
+    o += 5; *o++ = ':';
+    { unsigned long long v = g; for (int k = d - 1; k >= 0; --k) { o[k] = (uint8_t)('0' + v % 10); v /= 10; } o += d; }
+    memcpy(o, " 1:N:0:ACGT\n", 12); o += 12;
+    for (unsigned int k = 0; k < R; k += 32) {
+        unsigned long long w = rnd(s.seed, g, k >> 5);
+        unsigned int n = R - k < 32 ? R - k : 32;
+        for (unsigned int q = 0; q < n; ++q) o[k + q] = (uint8_t)base_char((unsigned int)(w >> (q * 2)) & 3u);
+    }
+    if (s.plant_mode && s.n_patterns && s.pattern_len && s.pattern_len <= R &&
+        (rnd(s.seed, g, 200) % 1000000ull) < s.plant_per_million) {
+        unsigned int p = (unsigned int)(rnd(s.seed, g, 201) % s.n_patterns);
+        unsigned int off = (unsigned int)(rnd(s.seed, g, 202) % (R - s.pattern_len + 1));
+        bool rc = s.plant_revcomp && (rnd(s.seed, g, 203) & 1ull);
+        for (unsigned int q = 0; q < s.pattern_len; ++q)
+            o[off + q] = (uint8_t)base_char(rc ? 3u - pattern_base(s, p, s.pattern_len - 1 - q) : pattern_base(s, p, q));
+    }
+    o += R; *o++ = '\n'; *o++ = '+'; *o++ = '\n';
+    for (unsigned int b = 0; b < R; b += 8) {
+        unsigned long long w = rnd(s.seed, g, 8 + (b >> 3));
+        unsigned int n = R - b < 8 ? R - b : 8;
+        for (unsigned int q = 0; q < n; ++q) o[b + q] = (uint8_t)(33u + ((((unsigned int)(w >> (q * 8)) & 0xffu) * 41u) >> 8));
+    }
+    o[R] = '\n';
+}
+
 extern "C" int fxg_synth_host(const fxg_synth_spec *s, uint8_t *out)
 {
     if (!s || !out) return FXG_ERR_ARG;
-    for (unsigned long long i = 0; i < s->n_records; ++i) {
-        unsigned long long g = s->first_record + i;
-        int d = dec_digits(g);
-        unsigned long long off = rec_offset(*s, i);
-        unsigned int len = (unsigned int)rec_fixed_bytes(*s) + (unsigned int)d;
-        for (unsigned int b = 0; b < len; ++b) out[off + b] = (uint8_t)rec_byte(*s, g, d, b);
-    }
+    const unsigned long long n = s->n_records;
+    unsigned int nt = std::thread::hardware_concurrency();
+    if (nt == 0) nt = 1;
+    if (nt > 64) nt = 64;
+    if (n < 4096) nt = 1;
+    auto work = [&](unsigned long long lo, unsigned long long hi) {
+        for (unsigned long long i = lo; i < hi; ++i) {
+            unsigned long long g = s->first_record + i;
+            synth_host_record(*s, g, dec_digits(g), out + rec_offset(*s, i));
+        }
+    };
+    if (nt == 1) { work(0, n); return FXG_OK; }
+    std::vector<std::thread> th;
+    for (unsigned int t = 0; t < nt; ++t) th.emplace_back(work, n * t / nt, n * (t + 1) / nt);
+    for (auto &x : th) x.join();
     return FXG_OK;
 }
 

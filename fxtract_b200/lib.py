@@ -40,8 +40,8 @@ class SynthSpec(C.Structure):
 EXPORTS = ["fxg_device_count", "fxg_create", "fxg_destroy", "fxg_last_error", "fxg_set_patterns",
            "fxg_acquire_buffer", "fxg_submit_raw", "fxg_submit_raw_from", "fxg_submit_fields", "fxg_collect",
            "fxg_count", "fxg_find_record_cut", "fxg_scan_device_async", "fxg_scan_device_finish",
-           "fxg_last_launch_count", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
-           "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free"]
+           "fxg_last_launch_count", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
+           "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free", "fxg_copy_to_host"]
 
 _lib = None
 
@@ -71,6 +71,8 @@ def load_library():
     lib.fxg_scan_device_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.fxg_scan_device_finish.argtypes = [C.c_void_p, C.POINTER(Result)]
     lib.fxg_last_launch_count.argtypes = [C.c_void_p]
+    lib.fxg_set_profiling.argtypes = [C.c_void_p, C.c_int]
+    lib.fxg_last_kernel_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.fxg_synth_bytes.argtypes = [C.POINTER(SynthSpec)]
     lib.fxg_synth_bytes.restype = C.c_uint64
     lib.fxg_synth_record_offset.argtypes = [C.POINTER(SynthSpec), C.c_uint64]
@@ -81,6 +83,7 @@ def load_library():
     lib.fxg_synth_name.argtypes = [C.POINTER(SynthSpec), C.c_uint64, C.c_void_p, C.POINTER(C.c_uint32)]
     lib.fxg_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
     lib.fxg_host_free.argtypes = [C.c_void_p]
+    lib.fxg_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
     lib.fxg_device_count.argtypes = [C.POINTER(C.c_int)]
     _lib = lib
     return lib
@@ -90,6 +93,23 @@ def find_record_cut(buf):
     lib = load_library()
     b = bytes(buf)
     return lib.fxg_find_record_cut(b, len(b))
+
+
+def find_record_cut_ptr(ptr, n):
+    """Same, over n bytes of host memory at address ptr (no copy)."""
+    return load_library().fxg_find_record_cut(C.c_void_p(ptr), n)
+
+
+def host_alloc(n):
+    p = C.c_void_p()
+    rc = load_library().fxg_host_alloc(C.byref(p), n)
+    if rc != 0:
+        raise FxgError("fxg_host_alloc(%d) failed: %s" % (n, load_library().fxg_last_error(None).decode()))
+    return p.value
+
+
+def host_free(ptr):
+    load_library().fxg_host_free(C.c_void_p(ptr))
 
 
 def pack_patterns(patterns):
@@ -181,6 +201,17 @@ class Context:
 
     def last_launch_count(self):
         return self.lib.fxg_last_launch_count(self.h)
+
+    def set_profiling(self, on=True):
+        self._check(self.lib.fxg_set_profiling(self.h, int(on)))
+
+    def last_kernel_ms(self):
+        a, b = C.c_float(), C.c_float()
+        self._check(self.lib.fxg_last_kernel_ms(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def copy_to_host(self, host_ptr, dptr, n):
+        self._check(self.lib.fxg_copy_to_host(self.h, C.c_void_p(host_ptr), C.c_void_p(dptr), n))
 
     def synth_device(self, spec, dptr):
         self._check(self.lib.fxg_synth_device(self.h, C.byref(spec), C.c_void_p(dptr)))

@@ -128,6 +128,13 @@ int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes);
 int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res);
 /* Number of kernel launches the last *_async / submit_* call enqueued. */
 int fxg_last_launch_count(const fxg_ctx *ctx);
+/* Measurement aid: when enabled, every raw-path enqueue brackets its kernels with
+ * CUDA events on the context's stream.  After the batch has been collected /
+ * finished, fxg_last_kernel_ms() returns the device time of the dominant kernel
+ * (scan_ms: the fused scan kernel alone) and of the whole kernel pipeline of that
+ * batch (pipeline_ms: memsets + scan + second-stage matcher + compaction). */
+int fxg_set_profiling(fxg_ctx *ctx, int enabled);
+int fxg_last_kernel_ms(fxg_ctx *ctx, float *scan_ms, float *pipeline_ms);
 
 /* ---- synthetic workload (deterministic, counter-based) */
 typedef struct fxg_synth_spec {
@@ -152,6 +159,9 @@ int fxg_synth_name(const fxg_synth_spec *s, uint64_t i, uint8_t *out, uint32_t *
 /* pinned host allocation helpers (bench / tests) */
 int fxg_host_alloc(void **p, size_t n);
 int fxg_host_free(void *p);
+/* synchronous device -> host copy on the context's stream (bench / tests: materialise a
+ * device-generated synthetic shard in host memory) */
+int fxg_copy_to_host(fxg_ctx *ctx, void *host_dst, const void *d_src, size_t n);
 
 #ifdef __cplusplus
 }
