@@ -122,7 +122,7 @@ static void build_literal_table(fxg_ctx *ctx)
     T.n_keys = (int)keys.size();
     if (U == 8) {
         unsigned long long rng = 0x243F6A8885A308D3ull;
-        for (int attempt = 0; attempt < 100000; ++attempt) {
+        for (int attempt = 0; attempt < 1000000; ++attempt) {
             rng = rng * 6364136223846793005ull + 1442695040888963407ull;
             unsigned int m1 = (unsigned int)(rng >> 32) | 1u;
             rng = rng * 6364136223846793005ull + 1442695040888963407ull;
@@ -130,15 +130,16 @@ static void build_literal_table(fxg_ctx *ctx)
             bool used[64] = {false}; bool ok = true;
             for (size_t i = 0; i < keys.size() && ok; ++i) {
                 unsigned int lo = (unsigned int)keys[i], hi = (unsigned int)(keys[i] >> 32);
-                unsigned int h = ((lo * m1) ^ (hi * m2)) >> 26;
+                unsigned int h = (lo * m1 + hi * m2) >> 26;
                 if (used[h]) ok = false; else used[h] = true;
             }
             if (ok) { T.mul1 = m1; T.mul2 = m2; break; }
         }
+        for (unsigned int h = 0; h < 64; ++h) T.fp[h] = (h ^ 1u) << 26;      // top bits != h: can never match
         for (size_t i = 0; i < keys.size(); ++i) {
             unsigned int lo = (unsigned int)keys[i], hi = (unsigned int)(keys[i] >> 32);
-            unsigned int h = ((lo * T.mul1) ^ (hi * T.mul2)) >> 26;
-            T.keys[h] = keys[i]; T.masks[h] = masks[i];
+            unsigned int r = lo * T.mul1 + hi * T.mul2;
+            T.keys[r >> 26] = keys[i]; T.fp[r >> 26] = r; T.masks[r >> 26] = masks[i];
         }
     } else {
         for (size_t i = 0; i < keys.size() && i < 64; ++i) { T.keys[i] = keys[i]; T.masks[i] = masks[i]; }

@@ -48,7 +48,9 @@ struct ScanCounters {
 // Aligned-unit filter: an occurrence of a pattern of length >= 2U-1 at offset p
 // fully contains the U-byte unit at ceil_U(p); the table holds, for every pattern
 // and every shift s in [0,U), the U bytes pat[s..s+U).  One lookup per aligned
-// unit of text replaces one comparison per text position.
+// unit of text replaces one comparison per text position.  For U == 8 the lookup
+// is a 32-bit multiplicative fingerprint (two IMADs) whose top 6 bits index a
+// collision-free 64-slot table; every candidate is then verified byte by byte.
 struct LiteralTable {
     int n_patterns;              // 1 or 2
     int unit;                    // 8, 4, 2 or 1 bytes
@@ -59,6 +61,7 @@ struct LiteralTable {
     int pat_len[2];
     int pat_off[2];              // offsets into pat_bytes
     unsigned long long keys[64]; // unit==8: 64-slot perfect hash; else first n_keys entries
+    unsigned int fp[64];         // unit==8: fp[h] = lo*mul1 + hi*mul2 of the key in slot h = fp >> 26 (else unmatchable)
     unsigned short masks[64];    // bit (pattern*8 + shift) set if keys[i] == pat[shift..shift+U)
 };
 

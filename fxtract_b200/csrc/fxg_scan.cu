@@ -5,13 +5,24 @@
 //   prepare_data (main.cpp:291-304)   ->  target field
 //   strstr x1..2 (main.cpp:568-588)   ->  literal hit
 //   on_match (main.cpp:258-271)       ->  count / select
-// with a position-centric kernel: every CTA takes a 32 KiB tile, finds '\n' with
-// SWAR on 16-byte loads, turns the per-tile counts into global line numbers with a
-// single-pass decoupled look-back prefix sum (line phase = line# mod 4 decides
-// header / sequence / plus / quality), validates the canonical-FASTQ predicate
-// under which kseq-parse-then-print is the identity, and runs
-// the literal matcher over aligned 8-byte units.  Hits set one bit per record;
-// K6 (compact_*) turns bits + record starts into ordered byte runs.
+// with a position-centric kernel.  Every CTA takes a 32 KiB tile (ticket order),
+// pulls it into shared memory with one bulk async copy (TMA, mbarrier completion)
+// and then
+//   1. main pass, 16 bytes per lane per step, SWAR only: '\n' mask and count, byte
+//      range check, per-chunk class summaries ("has a byte < 0x41", "has a byte
+//      < 0x21") as ballot bit rows, and the literal filter over aligned 8-byte units;
+//   2. block scan of the per-chunk counts -> ordered table of '\n' positions;
+//   3. one thread per line: record structure and character classes, evaluated for
+//      ALL FOUR possible line phases of the tile at once (4-bit "hypothesis" mask),
+//      so nothing here waits for the global line number;
+//   4. meanwhile warp 0 turns the per-tile '\n' counts into the global line number
+//      of the tile with a single-pass decoupled look-back (line phase = line# mod 4
+//      decides header / sequence / plus / quality) and picks the hypothesis;
+//   5. outputs: hit bit per record (verified literal candidates), record starts
+//      (when records are emitted), target-field table (multi / exact second stage).
+// The canonical-FASTQ predicate is what makes
+// kseq-parse-then-print the identity on the record bytes; a batch that violates
+// it is reported (never silently mis-parsed) and the host re-routes it.
 //
 // HBM traffic: each input byte is read once; outputs are 1 bit/record (+ 8 B per
 // record of record starts only when records are emitted).
@@ -19,31 +30,55 @@
 
 namespace fxg {
 
-struct __align__(16) ScanSmem {
-    uint4 tile[kChunks];                      // staged tile bytes
-    unsigned char cnt[kChunks];               // low-byte ('\n') count per chunk
-    unsigned int pre8[kThreads];              // exclusive '\n' prefix per group of 8 chunks
+struct __align__(128) ScanSmem {
+    uint4 tile[kChunks];                      // staged tile bytes (bulk-copy destination)
+    unsigned char cnt[kChunks];               // bytes < 0x20 per chunk
+    unsigned int pre8[kThreads];              // exclusive prefix of cnt per group of 8 chunks
     unsigned short nlpos[kMaxTileLines];      // tile-relative '\n' positions, in order
-    unsigned short nlchunk[kChunks];          // chunks that contain a low byte
+    unsigned short nlc[kChunks];              // chunks that contain a byte < 0x20 (unordered)
+    unsigned int sbits[kChunks / 32];         // bit c: chunk c has a byte < 0x41 (not a sequence letter)
+    unsigned int qbits[kChunks / 32];         // bit c: chunk c has a byte < 0x21 (not a quality char)
+    unsigned long long lit_keys[64];
+    unsigned int lit_fp[64];
+    unsigned short lit_masks[64];
     int cand_off[kCandCap];                   // tile-relative offset of a candidate unit
     unsigned short cand_mask[kCandCap];       // (pattern,shift) bits to verify
-    unsigned long long lit_keys[64];
-    unsigned short lit_masks[64];
     unsigned int warp_sums[kThreads / 32];
-    unsigned int n_nlchunk, n_cand, tile_hits, viol;
-    unsigned int total;                       // low bytes in this tile
-    unsigned int tile_id;
+    unsigned long long mbar;                  // bulk-copy completion barrier
     unsigned long long lbase;                 // '\n' count before this tile
     unsigned long long first_bad;
     long long e[3];                           // last three '\n' positions before the tile
+    unsigned int n_nlc, n_cand, tile_hits, viol, hyp_bad, total, tile_id;
 };
 
-__device__ __forceinline__ uint4 ld_stream(const uint8_t *p)
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ unsigned int smem_u32(const void *p) { return (unsigned int)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *mbar, unsigned int count)
 {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(mbar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *mbar, unsigned int bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(bytes) : "memory");
+}
+// 1-D bulk async copy global -> shared (TMA engine), completion counted in bytes on the mbarrier
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned int bytes, unsigned long long *mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(mbar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *mbar, unsigned int parity)
+{
+    asm volatile("{\n"
+                 ".reg .pred P1;\n"
+                 "LAB_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+                 "@P1 bra DONE;\n"
+                 "bra LAB_WAIT;\n"
+                 "DONE:\n"
+                 "}" ::"r"(smem_u32(mbar)), "r"(parity) : "memory");
 }
 __device__ __forceinline__ unsigned long long ld_vol64(const unsigned long long *p)
 {
@@ -58,19 +93,20 @@ __device__ __forceinline__ long long ld_vol64s(const long long *p)
     return v;
 }
 
-// bit7 of each byte set iff the byte is < 0x20 (valid for bytes < 0x80)
-__device__ __forceinline__ unsigned int low_mask(unsigned int x)
+// ---------------------------------------------------------------- SWAR helpers (bytes < 0x80)
+constexpr unsigned int kHi = 0x80808080u;
+constexpr unsigned int kAdd20 = 0x60606060u;   // (w + kAdd20) has bit7 set per byte iff byte >= 0x20
+constexpr unsigned int kAdd21 = 0x5f5f5f5fu;   // ... iff byte >= 0x21
+constexpr unsigned int kAdd41 = 0x3f3f3f3fu;   // ... iff byte >= 0x41
+
+// 16-bit mask, bit b set iff byte b of the chunk is below the threshold encoded by `add`
+__device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int add)
 {
-    return ~(x + 0x60606060u) & ~x & 0x80808080u;
-}
-// nonzero bit7 somewhere iff some byte >= 0x7f
-__device__ __forceinline__ unsigned int high_bits(unsigned int x)
-{
-    return (x + 0x01010101u) | x;
-}
-__device__ __forceinline__ unsigned int has_zero_byte(unsigned int v)
-{
-    return (v - 0x01010101u) & ~v & 0x80808080u;
+    unsigned int n0 = ((~(x.x + add) & kHi) * 0x00204081u) >> 28;
+    unsigned int n1 = ((~(x.y + add) & kHi) * 0x00204081u) >> 28;
+    unsigned int n2 = ((~(x.z + add) & kHi) * 0x00204081u) >> 28;
+    unsigned int n3 = ((~(x.w + add) & kHi) * 0x00204081u) >> 28;
+    return n0 | (n1 << 4) | (n2 << 8) | (n3 << 12);
 }
 
 __device__ __forceinline__ void note_violation(ScanSmem &S, unsigned int bit, unsigned long long off)
@@ -106,10 +142,106 @@ __device__ __forceinline__ long long nl_global(const ScanSmem &S, unsigned long 
     return i >= 0 ? (long long)(base + S.nlpos[i]) : S.e[-i - 1];
 }
 
-// ---------------------------------------------------------------- verification of one literal candidate
-__device__ void verify_candidate(ScanSmem &S, const ScanParams &P, const LiteralTable *lit,
-                                 unsigned long long base, int n_tab, int unit_rel, unsigned int bits)
+// any bit set in rows[lo, hi) (chunk indices) of both class bit rows
+__device__ __forceinline__ void range_any2(const ScanSmem &S, int lo, int hi, unsigned int &anyS, unsigned int &anyQ)
 {
+    anyS = 0; anyQ = 0;
+    if (lo >= hi) return;
+    const int wl = lo >> 5, wh = (hi - 1) >> 5;
+    const unsigned int ml = 0xffffffffu << (lo & 31), mh = 0xffffffffu >> (31 - ((hi - 1) & 31));
+    if (wl == wh) { anyS = S.sbits[wl] & ml & mh; anyQ = S.qbits[wl] & ml & mh; return; }
+    anyS = (S.sbits[wl] & ml) | (S.sbits[wh] & mh);
+    anyQ = (S.qbits[wl] & ml) | (S.qbits[wh] & mh);
+    for (int w = wl + 1; w < wh; ++w) { anyS |= S.sbits[w]; anyQ |= S.qbits[w]; }
+}
+
+// ---------------------------------------------------------------- per-line checks (phase-free)
+// Flags of local line i (the line that ends at nlpos[i]) and class flags of the head of
+// line i+1 (the bytes after that '\n' inside the same 16-byte chunk).
+constexpr unsigned int kFA = 1, kFB = 2, kFC = 4, kFD = 8, kFS = 16, kFQ = 32, kFSP = 64;
+//  kFA  not a header line: empty or first byte != '@'          (FXG_V_HEADER_AT)
+//  kFSP ends with ' ' (separator would not round-trip)          (FXG_V_HEADER_SPACE)
+//  kFB  empty line (as a sequence: FXG_V_EMPTY_SEQ)
+//  kFC  not exactly "+"                                         (FXG_V_PLUS_LINE)
+//  kFD  length differs from the line two above                  (FXG_V_QUAL_LEN)
+//  kFS  has a byte outside [0x41,0x7e]                          (FXG_V_SEQ_CLASS)
+//  kFQ  has a byte outside [0x21,0x7e]                          (FXG_V_QUAL_CLASS)
+__device__ __forceinline__ void line_flags(const ScanSmem &S, int i, int n_tab, unsigned int &own, unsigned int &nxt,
+                                           unsigned int &tail)
+{
+    const unsigned char *tb = reinterpret_cast<const unsigned char *>(S.tile);
+    const int pos = S.nlpos[i];
+    const int prev = i > 0 ? (int)S.nlpos[i - 1] : -1;
+    const int next = i + 1 < n_tab ? (int)S.nlpos[i + 1] : kTileBytes;
+    const int c = pos >> 4, cb = c << 4, cp = prev >> 4;
+    const uint4 x = S.tile[c];
+    const unsigned int s16 = lin_mask(x, kAdd41), q16 = lin_mask(x, kAdd21);
+    const int pb = pos - cb;
+    const int lo = prev + 1 > cb ? prev + 1 - cb : 0;
+    const unsigned int r_tail = ((1u << pb) - 1u) & ~((1u << lo) - 1u);
+    const int hi = next - cb < 16 ? next - cb : 16;
+    const unsigned int r_head = ((1u << hi) - 1u) & ~((2u << pb) - 1u);
+    unsigned int ms, mq;
+    range_any2(S, cp + 1, c, ms, mq);
+    own = (((s16 & r_tail) | ms) ? kFS : 0u) | (((q16 & r_tail) | mq) ? kFQ : 0u);
+    nxt = ((s16 & r_head) ? kFS : 0u) | ((q16 & r_head) ? kFQ : 0u);
+    tail = 0;
+    if (i == n_tab - 1) {                      // bytes after the last '\n': an unterminated line of index n_tab
+        range_any2(S, c + 1, kChunks, ms, mq);
+        tail = (ms ? kFS : 0u) | (mq ? kFQ : 0u);
+    }
+    if (i >= 1) {                              // line starts inside the tile: structure is local
+        const int llen = pos - prev - 1;
+        const unsigned int fb = tb[prev + 1], lb = tb[pos - 1];
+        if (llen < 1) own |= kFA | kFB | kFC;
+        else {
+            if (fb != '@') own |= kFA;
+            if (lb == ' ') own |= kFSP;
+            if (llen != 1 || fb != '+') own |= kFC;
+        }
+        if (i >= 3 && llen != (int)S.nlpos[i - 2] - (int)S.nlpos[i - 3] - 1) own |= kFD;
+    }
+}
+
+// 4-bit hypothesis mask: bit r set iff a line with these flags and local index i is illegal
+// when the tile starts at global line number == r (mod 4), i.e. the line's role is (i + r) & 3.
+__device__ __forceinline__ unsigned int hyp_bits(unsigned int f, int i)
+{
+    unsigned int v = ((f & (kFA | kFSP)) ? 1u : 0u) | ((f & (kFB | kFS)) ? 2u : 0u) | ((f & kFC) ? 4u : 0u) |
+                     ((f & (kFD | kFQ)) ? 8u : 0u);
+    const int s = i & 3;
+    return ((v >> s) | (v << (4 - s))) & 0xfu;
+}
+
+// slow path, known phase: turn the flags of line i into FXG_V_* bits
+__device__ __noinline__ void diagnose_line(ScanSmem &S, unsigned long long base, int i, int n_tab, int r)
+{
+    unsigned int own, nxt, tail;
+    line_flags(S, i, n_tab, own, nxt, tail);
+    const unsigned long long at = base + S.nlpos[i];
+    const int role = (i + r) & 3;
+    if (role == 0) {
+        if (own & kFA) note_violation(S, FXG_V_HEADER_AT, at);
+        if (own & kFSP) note_violation(S, FXG_V_HEADER_SPACE, at);
+    } else if (role == 1) {
+        if (own & kFB) note_violation(S, FXG_V_EMPTY_SEQ, at);
+        if (own & kFS) note_violation(S, FXG_V_SEQ_CLASS, at);
+    } else if (role == 2) {
+        if (own & kFC) note_violation(S, FXG_V_PLUS_LINE, at);
+    } else {
+        if (own & kFD) note_violation(S, FXG_V_QUAL_LEN, at);
+        if (own & kFQ) note_violation(S, FXG_V_QUAL_CLASS, at);
+    }
+    const int role1 = (role + 1) & 3;
+    if (role1 == 1 && ((nxt | tail) & kFS)) note_violation(S, FXG_V_SEQ_CLASS, at + 1);
+    if (role1 == 3 && ((nxt | tail) & kFQ)) note_violation(S, FXG_V_QUAL_CLASS, at + 1);
+}
+
+// ---------------------------------------------------------------- verification of one literal candidate
+__device__ __noinline__ void verify_candidate(ScanSmem &S, const ScanParams &P, unsigned long long base, int n_tab,
+                                              int unit_rel, unsigned int bits)
+{
+    const LiteralTable *lit = P.lit;
     while (bits) {
         int b = __ffs(bits) - 1;
         bits &= bits - 1;
@@ -161,71 +293,170 @@ __device__ void verify_candidate(ScanSmem &S, const ScanParams &P, const Literal
     }
 }
 
-__device__ __forceinline__ void push_candidate(ScanSmem &S, const ScanParams &P, const LiteralTable *lit,
-                                               unsigned long long base, int n_tab, int unit_rel, unsigned int bits)
+__device__ __forceinline__ void push_candidate(ScanSmem &S, int unit_rel, unsigned int bits)
 {
     unsigned int slot = atomicAdd(&S.n_cand, 1u);
     if (slot < kCandCap) { S.cand_off[slot] = unit_rel; S.cand_mask[slot] = (unsigned short)bits; }
-    else verify_candidate(S, P, lit, base, n_tab, unit_rel, bits);   // queue full: verify in place
+}
+
+// generic (short-pattern) literal filter: units of 4, 2 or 1 bytes compared against every key
+__device__ __noinline__ void filter_small_units(ScanSmem &S, const uint4 &x, int off, int U, int nkeys)
+{
+    const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
+    for (int u = 0; u < 16; u += U) {
+        unsigned int word = wv[u >> 2];
+        unsigned int val = U == 4 ? word : (U == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu) : ((word >> ((u & 3) * 8)) & 0xffu));
+        for (int k = 0; k < nkeys; ++k)
+            if ((unsigned int)S.lit_keys[k] == val) push_candidate(S, off + u, S.lit_masks[k]);
+    }
+}
+
+// record / field table entries of local line i once the phase is known
+__device__ __forceinline__ void emit_line(const ScanSmem &S, const ScanParams &P, unsigned long long base, int i)
+{
+    const unsigned long long j = S.lbase + (unsigned long long)i;
+    const int ph = (int)(j & 3);
+    const unsigned long long rec = j >> 2;
+    const long long pos = (long long)base + S.nlpos[i];
+    if (ph == 3) {
+        if (P.rec_start && rec + 1 <= P.rec_cap) P.rec_start[rec + 1] = (unsigned long long)(pos + 1);
+        if (P.fld_off && P.target == FXG_TARGET_QUAL && rec < P.rec_cap) {
+            const long long prev = nl_global(S, base, i - 1);
+            P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
+        }
+    } else if (ph == 1) {
+        if (P.fld_off && P.target == FXG_TARGET_SEQ && rec < P.rec_cap) {
+            const long long prev = nl_global(S, base, i - 1);
+            P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
+        }
+    } else if (ph == 0) {
+        if (P.fld_off && (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT) && rec < P.rec_cap) {
+            const long long prev = nl_global(S, base, i - 1);
+            long long q = prev + 2, sp = -1;
+            for (; q < pos; ++q) if (text_byte(S, P, base, q) == ' ') { sp = q; break; }
+            if (P.target == FXG_TARGET_NAME) {
+                long long ne = sp >= 0 ? sp : pos;
+                P.fld_off[rec] = (unsigned long long)(prev + 2);
+                P.fld_len[rec] = (unsigned int)(ne > prev + 2 ? ne - (prev + 2) : 0);
+            } else {
+                P.fld_off[rec] = (unsigned long long)(sp >= 0 ? sp + 1 : pos);
+                P.fld_len[rec] = (unsigned int)(sp >= 0 ? pos - (sp + 1) : 0);
+            }
+        }
+    }
+}
+
+// structure checks of the first lines of a tile, whose predecessors lie in earlier tiles (phase known)
+__device__ __noinline__ void check_edge_line(ScanSmem &S, const ScanParams &P, unsigned long long base, int i)
+{
+    const int ph = (int)((S.lbase + (unsigned long long)i) & 3);
+    const long long pos = (long long)base + S.nlpos[i];
+    const long long prev = nl_global(S, base, i - 1);
+    const long long llen = pos - prev - 1;
+    if (i == 0) {
+        if (llen > 0 && text_byte(S, P, base, pos - 1) == ' ' && ph == 0) note_violation(S, FXG_V_HEADER_SPACE, (unsigned long long)pos);
+        if (ph == 0 && (llen < 1 || text_byte(S, P, base, prev + 1) != '@')) note_violation(S, FXG_V_HEADER_AT, (unsigned long long)(prev + 1));
+        if (ph == 1 && llen < 1) note_violation(S, FXG_V_EMPTY_SEQ, (unsigned long long)pos);
+        if (ph == 2 && (llen != 1 || text_byte(S, P, base, pos - 1) != '+')) note_violation(S, FXG_V_PLUS_LINE, (unsigned long long)pos);
+    }
+    if (ph == 3) {
+        const long long slen = nl_global(S, base, i - 2) - nl_global(S, base, i - 3) - 1;
+        if (llen != slen) note_violation(S, FXG_V_QUAL_LEN, (unsigned long long)pos);
+    }
 }
 
 // ---------------------------------------------------------------- the kernel
 __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams P)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem &S = *reinterpret_cast<ScanSmem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LiteralTable *lit = P.lit;
-    int lit_unit = 0, lit_nkeys = 0;
-    unsigned int lit_mul1 = 0, lit_mul2 = 0;
-    if (P.match_enabled) { lit_unit = lit->unit; lit_nkeys = lit->n_keys; lit_mul1 = lit->mul1; lit_mul2 = lit->mul2; }
 
     if (tid == 0) {
         S.tile_id = atomicAdd(&P.ctr->ticket, 1u);
-        S.n_nlchunk = 0; S.n_cand = 0; S.tile_hits = 0; S.viol = 0;
+        S.n_nlc = 0; S.n_cand = 0; S.tile_hits = 0; S.viol = 0; S.hyp_bad = 0;
         S.first_bad = ~0ull;
+        mbar_init(&S.mbar, 1);
     }
-    if (P.match_enabled && tid < 64) { S.lit_keys[tid] = lit->keys[tid]; S.lit_masks[tid] = lit->masks[tid]; }
     __syncthreads();
     const unsigned long long t = S.tile_id;
     const unsigned long long base = t * (unsigned long long)kTileBytes;
     const unsigned long long remain = P.nbytes - base;
     const int tile_len = remain < (unsigned long long)kTileBytes ? (int)remain : kTileBytes;
+    const int bulk = tile_len & ~15;
     unsigned char *tb = reinterpret_cast<unsigned char *>(S.tile);
 
-    // ---- A. coalesced 16-byte loads, stage in smem, SWAR '\n' / range classification
+    // ---- stage the tile: one bulk async copy; the ragged end of the batch is patched by hand
+    if (tid == 0 && bulk) {
+        mbar_expect_tx(&S.mbar, (unsigned int)bulk);
+        bulk_g2s(S.tile, P.buf + base, (unsigned int)bulk, &S.mbar);
+    }
+    int lit_unit = 0, lit_nkeys = 0;
+    unsigned int lit_mul1 = 0, lit_mul2 = 0;
+    if (P.match_enabled) {
+        lit_unit = lit->unit; lit_nkeys = lit->n_keys; lit_mul1 = lit->mul1; lit_mul2 = lit->mul2;
+        if (tid >= 64 && tid < 128) {
+            const int k = tid - 64;
+            S.lit_keys[k] = lit->keys[k]; S.lit_fp[k] = lit->fp[k]; S.lit_masks[k] = lit->masks[k];
+        }
+    }
+    if (tile_len < kTileBytes) {
+        for (int b = bulk + tid * 16; b < kTileBytes; b += kThreads * 16) {
+            unsigned int w[4] = {0x78787878u, 0x78787878u, 0x78787878u, 0x78787878u};   // neutral filler
+            for (int k = 0; k < 16 && b + k < tile_len; ++k) {
+                unsigned int by = P.buf[base + b + k];
+                w[k >> 2] = (w[k >> 2] & ~(0xffu << ((k & 3) * 8))) | (by << ((k & 3) * 8));
+            }
+            S.tile[b >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    }
+    if (bulk) mbar_wait(&S.mbar, 0);
+    __syncthreads();
+
+    // ---- 1. main pass: 16 bytes per lane per step
     {
-        uint4 v[kChunksPerThread];
+        unsigned int hi_acc = 0;
 #pragma unroll
         for (int j = 0; j < kChunksPerThread; ++j) {
-            int c = warp * (kChunks / 8) + j * 32 + lane;
-            int off = c << 4;
-            if (off + 16 <= tile_len) v[j] = ld_stream(P.buf + base + off);
-            else {
-                unsigned int w[4] = {0x78787878u, 0x78787878u, 0x78787878u, 0x78787878u};
-                for (int k = 0; k < 16 && off + k < tile_len; ++k) {
-                    unsigned int by = P.buf[base + off + k];
-                    w[k >> 2] = (w[k >> 2] & ~(0xffu << ((k & 3) * 8))) | (by << ((k & 3) * 8));
+            const int c = warp * (kChunks / 8) + j * 32 + lane;
+            const uint4 x = S.tile[c];
+            hi_acc |= x.x | x.y | x.z | x.w;
+            hi_acc |= (x.x + 0x01010101u) | (x.y + 0x01010101u) | (x.z + 0x01010101u) | (x.w + 0x01010101u);
+            const unsigned int m = (~(x.x + kAdd20) & kHi) | ((~(x.y + kAdd20) & kHi) >> 1) |
+                                   ((~(x.z + kAdd20) & kHi) >> 2) | ((~(x.w + kAdd20) & kHi) >> 3);
+            const unsigned int n = __popc(m);
+            const bool s_any = (((x.x + kAdd41) & (x.y + kAdd41) & (x.z + kAdd41) & (x.w + kAdd41)) & kHi) != kHi;
+            const bool q_any = (((x.x + kAdd21) & (x.y + kAdd21) & (x.z + kAdd21) & (x.w + kAdd21)) & kHi) != kHi;
+            const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
+            const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
+            const unsigned int nb = __ballot_sync(0xffffffffu, n != 0);
+            S.cnt[c] = (unsigned char)n;
+            unsigned int slot0 = 0;
+            if (lane == 0) {
+                S.sbits[c >> 5] = sb; S.qbits[c >> 5] = qb;
+                if (nb) slot0 = atomicAdd(&S.n_nlc, (unsigned int)__popc(nb));
+            }
+            if (nb) {
+                slot0 = __shfl_sync(0xffffffffu, slot0, 0);
+                if (n) S.nlc[slot0 + __popc(nb & ((1u << lane) - 1u))] = (unsigned short)c;
+            }
+            if (P.match_enabled) {
+                if (lit_unit == 8) {
+                    const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
+                    const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
+                    if (S.lit_fp[r0 >> 26] == r0) push_candidate(S, c << 4, S.lit_masks[r0 >> 26]);
+                    if (S.lit_fp[r1 >> 26] == r1) push_candidate(S, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                } else if ((c << 4) < tile_len) {
+                    filter_small_units(S, x, c << 4, lit_unit, lit_nkeys);
                 }
-                v[j] = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
-        unsigned int hi = 0;
-#pragma unroll
-        for (int j = 0; j < kChunksPerThread; ++j) {
-            int c = warp * (kChunks / 8) + j * 32 + lane;
-            S.tile[c] = v[j];
-            unsigned int m = low_mask(v[j].x) | (low_mask(v[j].y) >> 1) | (low_mask(v[j].z) >> 2) | (low_mask(v[j].w) >> 3);
-            hi |= high_bits(v[j].x) | high_bits(v[j].y) | high_bits(v[j].z) | high_bits(v[j].w);
-            unsigned int n = __popc(m);
-            S.cnt[c] = (unsigned char)n;
-            if (n) { unsigned int slot = atomicAdd(&S.n_nlchunk, 1u); S.nlchunk[slot] = (unsigned short)c; }
-        }
-        if (hi & 0x80808080u) note_violation(S, FXG_V_BYTE_RANGE, base);
+        if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(S, FXG_V_BYTE_RANGE, base);
     }
     __syncthreads();
 
-    // ---- B. block scan of per-chunk counts (8 consecutive chunks per thread)
+    // ---- 2. block scan of per-chunk counts (8 consecutive chunks per thread)
     {
         uint2 w = *reinterpret_cast<const uint2 *>(&S.cnt[tid * 8]);
         unsigned int s = __dp4a(w.x, 0x01010101u, 0u) + __dp4a(w.y, 0x01010101u, 0u);
@@ -252,27 +483,30 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
     if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(S, FXG_V_DENSE_LINES, base);
 
-    // ---- D1. ordered '\n' position table from the chunks that have low bytes
+    //      ordered '\n' position table from the chunks that have bytes < 0x20
     {
-        const unsigned int nn = S.n_nlchunk;
+        const unsigned int nn = S.n_nlc;
         for (unsigned int q = tid; q < nn; q += kThreads) {
-            int c = S.nlchunk[q];
-            unsigned int idx = S.pre8[c >> 3];
-            for (int k = (c & ~7); k < c; ++k) idx += S.cnt[k];
-            for (int k = 0; k < 16; ++k) {
-                unsigned int by = tb[(c << 4) + k];
-                if (by < 0x20) {
-                    if (by != '\n') note_violation(S, FXG_V_BYTE_RANGE, base + (c << 4) + k);
-                    if (idx < (unsigned int)kMaxTileLines) S.nlpos[idx] = (unsigned short)((c << 4) + k);
-                    ++idx;
-                }
+            const int c = S.nlc[q];
+            unsigned int m16 = lin_mask(S.tile[c], kAdd20);
+            uint2 w = *reinterpret_cast<const uint2 *>(&S.cnt[c & ~7]);
+            const int sh = (c & 7) * 8;
+            const unsigned long long keep = sh ? ((1ull << sh) - 1ull) : 0ull;
+            unsigned int idx = S.pre8[c >> 3] + __dp4a(w.x & (unsigned int)keep, 0x01010101u, 0u) +
+                               __dp4a(w.y & (unsigned int)(keep >> 32), 0x01010101u, 0u);
+            while (m16) {
+                const int p = (c << 4) + __ffs(m16) - 1;
+                m16 &= m16 - 1;
+                if (tb[p] != '\n') note_violation(S, FXG_V_BYTE_RANGE, base + p);
+                if (idx < (unsigned int)kMaxTileLines) S.nlpos[idx] = (unsigned short)p;
+                ++idx;
             }
         }
     }
     __syncthreads();
 
-    // ---- look-back: publish aggregate (+ own last three '\n'), fetch exclusive prefix
     if (warp == 0) {
+        // ---- 4. look-back: publish aggregate (+ own last three '\n'), fetch exclusive prefix
         TileDesc *D = P.desc;
         unsigned long long own3 = n_tab >= 3 ? 3 : n_tab;
         if (lane == 0) {
@@ -335,132 +569,66 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
                 atomicExch(&D[t].status, st);
             }
         }
+    } else {
+        // ---- 3. one thread per line, all four phase hypotheses at once (warps 1..7)
+        unsigned int bad4 = 0;
+        if (n_tab == 0) {
+            if (tid == 32) {
+                unsigned int ms, mq;
+                range_any2(S, 0, kChunks, ms, mq);
+                bad4 = hyp_bits((ms ? kFS : 0u) | (mq ? kFQ : 0u), 0);
+            }
+        } else {
+            for (int i = tid - 32; i < n_tab; i += kThreads - 32) {
+                unsigned int own, nxt, tail;
+                line_flags(S, i, n_tab, own, nxt, tail);
+                bad4 |= hyp_bits(own, i) | hyp_bits(nxt | tail, i + 1);
+            }
+        }
+        bad4 = __reduce_or_sync(0xffffffffu, bad4);
+        if (lane == 0 && bad4) atomicOr(&S.hyp_bad, bad4);
     }
     __syncthreads();
     const unsigned long long lbase = S.lbase;
+    const int r = (int)(lbase & 3);
 
-    // ---- C. phase-aware class checks on chunks without '\n' + literal filter on every chunk
-#pragma unroll 2
-    for (int j = 0; j < kChunksPerThread; ++j) {
-        int c = warp * (kChunks / 8) + j * 32 + lane;
-        int off = c << 4;
-        if (off >= tile_len) continue;
-        uint4 x = S.tile[c];
-        if (S.cnt[c] == 0) {
-            uint2 w = *reinterpret_cast<const uint2 *>(&S.cnt[c & ~7]);
-            int sh = (c & 7) * 8;
-            unsigned long long m = sh ? ((1ull << sh) - 1ull) : 0ull;
-            unsigned int lo = w.x & (unsigned int)m, hi2 = w.y & (unsigned int)(m >> 32);
-            unsigned int pc = S.pre8[c >> 3] + __dp4a(lo, 0x01010101u, 0u) + __dp4a(hi2, 0x01010101u, 0u);
-            int ph = (int)((lbase + pc) & 3);
-            if (ph == 1) {
-                // sequence: every byte must have bit 6 set (0x40..0x7e) and not be '@'
-                unsigned int a = x.x & x.y & x.z & x.w;
-                unsigned int z = has_zero_byte(x.x ^ 0x40404040u) | has_zero_byte(x.y ^ 0x40404040u) |
-                                 has_zero_byte(x.z ^ 0x40404040u) | has_zero_byte(x.w ^ 0x40404040u);
-                if ((a & 0x40404040u) != 0x40404040u || z) note_violation(S, FXG_V_SEQ_CLASS, base + off);
-            } else if (ph == 3) {
-                // quality: no space (all other bytes already range-checked)
-                unsigned int z = has_zero_byte(x.x & 0x5f5f5f5fu) | has_zero_byte(x.y & 0x5f5f5f5fu) |
-                                 has_zero_byte(x.z & 0x5f5f5f5fu) | has_zero_byte(x.w & 0x5f5f5f5fu);
-                if (z) note_violation(S, FXG_V_QUAL_CLASS, base + off);
-            }
-        }
-        if (P.match_enabled) {
-            if (lit_unit == 8) {
-                unsigned int h0 = ((x.x * lit_mul1) ^ (x.y * lit_mul2)) >> 26;
-                unsigned int h1 = ((x.z * lit_mul1) ^ (x.w * lit_mul2)) >> 26;
-                unsigned long long k0 = S.lit_keys[h0], k1 = S.lit_keys[h1];
-                unsigned long long u0 = ((unsigned long long)x.y << 32) | x.x;
-                unsigned long long u1 = ((unsigned long long)x.w << 32) | x.z;
-                if (k0 == u0) push_candidate(S, P, lit, base, n_tab, off, S.lit_masks[h0]);
-                if (k1 == u1) push_candidate(S, P, lit, base, n_tab, off + 8, S.lit_masks[h1]);
-            } else {
-                const int U = lit_unit;
-                const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
-                for (int u = 0; u < 16; u += U) {
-                    unsigned int word = wv[u >> 2];
-                    unsigned int val = U == 4 ? word : (U == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu)
-                                                                : ((word >> ((u & 3) * 8)) & 0xffu));
-                    for (int k = 0; k < lit_nkeys; ++k)
-                        if ((unsigned int)S.lit_keys[k] == val) push_candidate(S, P, lit, base, n_tab, off + u, S.lit_masks[k]);
-                }
-            }
-        }
+    // ---- 5. phase is known: pick the hypothesis, edge lines, outputs, candidates
+    if ((S.hyp_bad >> r) & 1u) {
+        if (n_tab == 0) { if (tid == 0) note_violation(S, r == 1 ? FXG_V_SEQ_CLASS : FXG_V_QUAL_CLASS, base); }
+        else for (int i = tid; i < n_tab; i += kThreads) diagnose_line(S, base, i, n_tab, r);
     }
-
-    // ---- E. one thread per '\n': record structure + partial-chunk class checks + record table
-    for (int i = tid; i < n_tab; i += kThreads) {
-        const unsigned long long j = lbase + (unsigned long long)i;
-        const int ph = (int)(j & 3);
-        const int rel = S.nlpos[i];
-        const long long pos = (long long)base + rel;
-        const long long prev = nl_global(S, base, i - 1);
-        const long long llen = pos - prev - 1;                   // bytes in the line that ends here
-        if (llen > 0 && text_byte(S, P, base, pos - 1) == ' ') note_violation(S, FXG_V_HEADER_SPACE, (unsigned long long)pos);
-        if (ph == 0) {
-            if (llen < 1 || text_byte(S, P, base, prev + 1) != '@') note_violation(S, FXG_V_HEADER_AT, (unsigned long long)(prev + 1));
-            if (P.fld_off && (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT)) {
-                unsigned long long rec = j >> 2;
-                if (rec < P.rec_cap) {
-                    long long q = prev + 2, sp = -1;
-                    for (; q < pos; ++q) if (text_byte(S, P, base, q) == ' ') { sp = q; break; }
-                    if (P.target == FXG_TARGET_NAME) {
-                        long long ne = sp >= 0 ? sp : pos;
-                        P.fld_off[rec] = (unsigned long long)(prev + 2);
-                        P.fld_len[rec] = (unsigned int)(ne > prev + 2 ? ne - (prev + 2) : 0);
-                    } else {
-                        P.fld_off[rec] = (unsigned long long)(sp >= 0 ? sp + 1 : pos);
-                        P.fld_len[rec] = (unsigned int)(sp >= 0 ? pos - (sp + 1) : 0);
+    if (tid < 3 && tid < n_tab) check_edge_line(S, P, base, tid);
+    if (P.rec_start || P.fld_off) {
+        for (int i = tid; i < n_tab; i += kThreads) emit_line(S, P, base, i);
+        if (t == 0 && tid == 0 && P.rec_start) P.rec_start[0] = 0;
+    }
+    if (P.match_enabled) {
+        const unsigned int nc_all = S.n_cand;
+        if (nc_all <= (unsigned int)kCandCap) {
+            for (unsigned int q = tid; q < nc_all; q += kThreads) verify_candidate(S, P, base, n_tab, S.cand_off[q], S.cand_mask[q]);
+        } else {
+            // queue overflow (pattern hits nearly everywhere): rescan the tile and verify in place
+            for (int c = tid; c < kChunks && (c << 4) < tile_len; c += kThreads) {
+                const uint4 x = S.tile[c];
+                if (lit_unit == 8) {
+                    const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
+                    const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
+                    if (S.lit_fp[r0 >> 26] == r0) verify_candidate(S, P, base, n_tab, c << 4, S.lit_masks[r0 >> 26]);
+                    if (S.lit_fp[r1 >> 26] == r1) verify_candidate(S, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                } else {
+                    const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
+                    for (int u = 0; u < 16; u += lit_unit) {
+                        unsigned int word = wv[u >> 2];
+                        unsigned int val = lit_unit == 4 ? word : (lit_unit == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu)
+                                                                                 : ((word >> ((u & 3) * 8)) & 0xffu));
+                        for (int k = 0; k < lit_nkeys; ++k)
+                            if ((unsigned int)S.lit_keys[k] == val) verify_candidate(S, P, base, n_tab, (c << 4) + u, S.lit_masks[k]);
                     }
                 }
             }
-        } else if (ph == 1) {
-            if (llen < 1) note_violation(S, FXG_V_EMPTY_SEQ, (unsigned long long)pos);
-            if (P.fld_off && P.target == FXG_TARGET_SEQ) {
-                unsigned long long rec = j >> 2;
-                if (rec < P.rec_cap) { P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)llen; }
-            }
-        } else if (ph == 2) {
-            if (llen != 1 || text_byte(S, P, base, pos - 1) != '+') note_violation(S, FXG_V_PLUS_LINE, (unsigned long long)pos);
-        } else {
-            long long slen = nl_global(S, base, i - 2) - nl_global(S, base, i - 3) - 1;
-            if (llen != slen) note_violation(S, FXG_V_QUAL_LEN, (unsigned long long)pos);
-            unsigned long long rec = j >> 2;
-            if (P.rec_start && rec + 1 <= P.rec_cap) P.rec_start[rec + 1] = (unsigned long long)(pos + 1);
-            if (P.fld_off && P.target == FXG_TARGET_QUAL && rec < P.rec_cap) {
-                P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)llen;
-            }
-        }
-        // partial-chunk class checks around this '\n' (full chunks were checked in C)
-        {
-            int cb = rel & ~15;
-            int lo = (prev + 1 > (long long)base + cb) ? (int)(prev + 1 - (long long)base) : cb;
-            if (ph == 1) {
-                for (int b = lo; b < rel; ++b) { unsigned int ch = tb[b]; if (!(ch & 0x40) || ch == 0x40) note_violation(S, FXG_V_SEQ_CLASS, base + b); }
-            } else if (ph == 3) {
-                for (int b = lo; b < rel; ++b) if (tb[b] == ' ') note_violation(S, FXG_V_QUAL_CLASS, base + b);
-            }
-            int ce = cb + 16 < tile_len ? cb + 16 : tile_len;
-            int hi = (i + 1 < n_tab && S.nlpos[i + 1] < ce) ? S.nlpos[i + 1] : ce;
-            int ph2 = (ph + 1) & 3;
-            if (ph2 == 1) {
-                for (int b = rel + 1; b < hi; ++b) { unsigned int ch = tb[b]; if (!(ch & 0x40) || ch == 0x40) note_violation(S, FXG_V_SEQ_CLASS, base + b); }
-            } else if (ph2 == 3) {
-                for (int b = rel + 1; b < hi; ++b) if (tb[b] == ' ') note_violation(S, FXG_V_QUAL_CLASS, base + b);
-            }
         }
     }
-    if (t == 0 && tid == 0 && P.rec_start) P.rec_start[0] = 0;
     __syncthreads();
-
-    // ---- V. verify queued literal candidates
-    if (P.match_enabled) {
-        unsigned int nc = S.n_cand < (unsigned int)kCandCap ? S.n_cand : (unsigned int)kCandCap;
-        for (unsigned int q = tid; q < nc; q += kThreads)
-            verify_candidate(S, P, lit, base, n_tab, S.cand_off[q], S.cand_mask[q]);
-        __syncthreads();
-    }
 
     // ---- epilogue
     if (tid == 0) {
@@ -477,12 +645,15 @@ size_t scan_smem_bytes() { return sizeof(ScanSmem); }
 
 cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(scan_raw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
+    if (((uintptr_t)P.buf & 15) != 0) return cudaErrorMisalignedAddress;     // bulk copies need 16-byte alignment
     unsigned long long ntiles = (P.nbytes + kTileBytes - 1) / kTileBytes;
     if (ntiles == 0) return cudaSuccess;
     scan_raw_kernel<<<(unsigned int)ntiles, kThreads, sizeof(ScanSmem), stream>>>(P);
