@@ -305,7 +305,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     ScanParams P;
     memset(&P, 0, sizeof P);
     P.buf = d_buf; P.nbytes = nbytes; P.desc = ctx->d_desc; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
-    P.rec_start = emit ? ctx->d_rec_start : nullptr; P.rec_cap = rec_cap;
+    P.rec_start = emit ? ctx->d_rec_start : nullptr; P.rec_cap = rec_cap; P.one = 1;
     P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;

@@ -77,6 +77,7 @@ struct ScanParams {
     const uint8_t *pat_bytes;         // device copy of pattern bytes
     int target;
     int match_enabled;                // 0: index/validate only (multi / exact use the field table)
+    unsigned int one;                 // == 1 (lets the kernel issue adds as IMAD; see fma_add)
     // field table for the second-stage matchers (multi / exact): target field of record k
     unsigned long long *fld_off;      // [rec_cap] or nullptr
     unsigned int *fld_len;            // [rec_cap]

@@ -35,7 +35,9 @@ struct __align__(128) ScanSmem {
     unsigned char cnt[kChunks];               // bytes < 0x20 per chunk
     unsigned int pre8[kThreads];              // exclusive prefix of cnt per group of 8 chunks
     unsigned short nlpos[kMaxTileLines];      // tile-relative '\n' positions, in order
-    unsigned short nlc[kChunks];              // chunks that contain a byte < 0x20 (unordered)
+    unsigned short wl[kThreads / 32][kChunks / 8];   // per warp: its chunks that contain a byte < 0x20, in order
+    unsigned int wcnt[kThreads / 32];         // entries in wl[w]
+    unsigned int below[17];                   // interleaved-layout mask of the bytes < p of a chunk
     unsigned int sbits[kChunks / 32];         // bit c: chunk c has a byte < 0x41 (not a sequence letter)
     unsigned int qbits[kChunks / 32];         // bit c: chunk c has a byte < 0x21 (not a quality char)
     unsigned long long lit_keys[64];
@@ -48,7 +50,7 @@ struct __align__(128) ScanSmem {
     unsigned long long lbase;                 // '\n' count before this tile
     unsigned long long first_bad;
     long long e[3];                           // last three '\n' positions before the tile
-    unsigned int n_nlc, n_cand, tile_hits, viol, hyp_bad, total, tile_id;
+    unsigned int n_cand, tile_hits, viol, hyp_bad, total, tile_id;
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -98,6 +100,34 @@ constexpr unsigned int kHi = 0x80808080u;
 constexpr unsigned int kAdd20 = 0x60606060u;   // (w + kAdd20) has bit7 set per byte iff byte >= 0x20
 constexpr unsigned int kAdd21 = 0x5f5f5f5fu;   // ... iff byte >= 0x21
 constexpr unsigned int kAdd41 = 0x3f3f3f3fu;   // ... iff byte >= 0x41
+
+// x + k issued as IMAD (fma pipe) instead of IADD3 (alu pipe): the main pass is bound by the
+// alu pipe (LOP3/SHF/IADD3 share it at half rate), so the SWAR threshold adds go to the other
+// pipe.  `one` is a kernel parameter equal to 1 that ptxas cannot fold away.
+__device__ __forceinline__ unsigned int fma_add(unsigned int x, unsigned int one, unsigned int k)
+{
+    unsigned int r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(one), "r"(k));
+    return r;
+}
+
+// Interleaved-layout mask: bit (8k + 7 - i) set iff byte k of word i (byte 4i+k of the chunk) is
+// below the threshold encoded by `add`.  4 adds, 3 shifts, 4 LOP3 (bitwise selects).
+__device__ __forceinline__ unsigned int il_mask(const uint4 &x, unsigned int add)
+{
+    unsigned int t = x.x + add;
+    t = (t & 0x80808080u) | (((x.y + add) >> 1) & 0x40404040u);
+    t = (t & 0xc0c0c0c0u) | (((x.z + add) >> 2) & 0x20202020u);
+    t = (t & 0xe0e0e0e0u) | (((x.w + add) >> 3) & 0x10101010u);
+    return ~t & 0xf0f0f0f0u;
+}
+// il_mask of "bytes with index < p" (p in 0..16)
+__host__ __device__ inline unsigned int il_below(int p)
+{
+    unsigned int m = 0;
+    for (int b = 0; b < p; ++b) m |= 1u << (8 * (b & 3) + 7 - (b >> 2));
+    return m;
+}
 
 // 16-bit mask, bit b set iff byte b of the chunk is below the threshold encoded by `add`
 __device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int add)
@@ -175,12 +205,12 @@ __device__ __forceinline__ void line_flags(const ScanSmem &S, int i, int n_tab, 
     const int next = i + 1 < n_tab ? (int)S.nlpos[i + 1] : kTileBytes;
     const int c = pos >> 4, cb = c << 4, cp = prev >> 4;
     const uint4 x = S.tile[c];
-    const unsigned int s16 = lin_mask(x, kAdd41), q16 = lin_mask(x, kAdd21);
+    const unsigned int s16 = il_mask(x, kAdd41), q16 = il_mask(x, kAdd21);
     const int pb = pos - cb;
     const int lo = prev + 1 > cb ? prev + 1 - cb : 0;
-    const unsigned int r_tail = ((1u << pb) - 1u) & ~((1u << lo) - 1u);
+    const unsigned int r_tail = S.below[pb] & ~S.below[lo];
     const int hi = next - cb < 16 ? next - cb : 16;
-    const unsigned int r_head = ((1u << hi) - 1u) & ~((2u << pb) - 1u);
+    const unsigned int r_head = S.below[hi] & ~S.below[pb + 1];
     unsigned int ms, mq;
     range_any2(S, cp + 1, c, ms, mq);
     own = (((s16 & r_tail) | ms) ? kFS : 0u) | (((q16 & r_tail) | mq) ? kFQ : 0u);
@@ -300,11 +330,12 @@ __device__ __forceinline__ void push_candidate(ScanSmem &S, int unit_rel, unsign
 }
 
 // generic (short-pattern) literal filter: units of 4, 2 or 1 bytes compared against every key
-__device__ __noinline__ void filter_small_units(ScanSmem &S, const uint4 &x, int off, int U, int nkeys)
+__device__ __noinline__ void filter_small_units(ScanSmem &S, unsigned int x0, unsigned int x1, unsigned int x2,
+                                                unsigned int x3, int off, int U, int nkeys)
 {
-    const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
     for (int u = 0; u < 16; u += U) {
-        unsigned int word = wv[u >> 2];
+        const int wi = u >> 2;
+        unsigned int word = wi == 0 ? x0 : (wi == 1 ? x1 : (wi == 2 ? x2 : x3));
         unsigned int val = U == 4 ? word : (U == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu) : ((word >> ((u & 3) * 8)) & 0xffu));
         for (int k = 0; k < nkeys; ++k)
             if ((unsigned int)S.lit_keys[k] == val) push_candidate(S, off + u, S.lit_masks[k]);
@@ -375,7 +406,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
 
     if (tid == 0) {
         S.tile_id = atomicAdd(&P.ctr->ticket, 1u);
-        S.n_nlc = 0; S.n_cand = 0; S.tile_hits = 0; S.viol = 0; S.hyp_bad = 0;
+        S.n_cand = 0; S.tile_hits = 0; S.viol = 0; S.hyp_bad = 0;
         S.first_bad = ~0ull;
         mbar_init(&S.mbar, 1);
     }
@@ -392,6 +423,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
         mbar_expect_tx(&S.mbar, (unsigned int)bulk);
         bulk_g2s(S.tile, P.buf + base, (unsigned int)bulk, &S.mbar);
     }
+    if (tid >= 128 && tid < 145) S.below[tid - 128] = il_below(tid - 128);
     int lit_unit = 0, lit_nkeys = 0;
     unsigned int lit_mul1 = 0, lit_mul2 = 0;
     if (P.match_enabled) {
@@ -416,31 +448,37 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
 
     // ---- 1. main pass: 16 bytes per lane per step
     {
-        unsigned int hi_acc = 0;
+        const unsigned int one = P.one;
+        const unsigned int lt_mask = (1u << lane) - 1u;
+        unsigned int hi_acc = 0, wcount = 0;
+        unsigned short *my_list = S.wl[warp];
 #pragma unroll
         for (int j = 0; j < kChunksPerThread; ++j) {
             const int c = warp * (kChunks / 8) + j * 32 + lane;
             const uint4 x = S.tile[c];
-            hi_acc |= x.x | x.y | x.z | x.w;
-            hi_acc |= (x.x + 0x01010101u) | (x.y + 0x01010101u) | (x.z + 0x01010101u) | (x.w + 0x01010101u);
-            const unsigned int m = (~(x.x + kAdd20) & kHi) | ((~(x.y + kAdd20) & kHi) >> 1) |
-                                   ((~(x.z + kAdd20) & kHi) >> 2) | ((~(x.w + kAdd20) & kHi) >> 3);
-            const unsigned int n = __popc(m);
-            const bool s_any = (((x.x + kAdd41) & (x.y + kAdd41) & (x.z + kAdd41) & (x.w + kAdd41)) & kHi) != kHi;
-            const bool q_any = (((x.x + kAdd21) & (x.y + kAdd21) & (x.z + kAdd21) & (x.w + kAdd21)) & kHi) != kHi;
+            // bytes >= 0x7f anywhere
+            hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);
+            hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
+            hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
+            hi_acc |= x.w | fma_add(x.w, one, 0x01010101u);
+            // bytes < 0x20: count (dp4a over the isolated bit-7 flags = 128 * count)
+            unsigned int n = __dp4a(~fma_add(x.x, one, kAdd20) & kHi, 0x01010101u, 0u);
+            n = __dp4a(~fma_add(x.y, one, kAdd20) & kHi, 0x01010101u, n);
+            n = __dp4a(~fma_add(x.z, one, kAdd20) & kHi, 0x01010101u, n);
+            n = __dp4a(~fma_add(x.w, one, kAdd20) & kHi, 0x01010101u, n);
+            n >>= 7;
+            const bool s_any = ((fma_add(x.x, one, kAdd41) & fma_add(x.y, one, kAdd41) & fma_add(x.z, one, kAdd41) &
+                                 fma_add(x.w, one, kAdd41)) & kHi) != kHi;
+            const bool q_any = ((fma_add(x.x, one, kAdd21) & fma_add(x.y, one, kAdd21) & fma_add(x.z, one, kAdd21) &
+                                 fma_add(x.w, one, kAdd21)) & kHi) != kHi;
             const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
             const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
             const unsigned int nb = __ballot_sync(0xffffffffu, n != 0);
             S.cnt[c] = (unsigned char)n;
-            unsigned int slot0 = 0;
-            if (lane == 0) {
-                S.sbits[c >> 5] = sb; S.qbits[c >> 5] = qb;
-                if (nb) slot0 = atomicAdd(&S.n_nlc, (unsigned int)__popc(nb));
-            }
-            if (nb) {
-                slot0 = __shfl_sync(0xffffffffu, slot0, 0);
-                if (n) S.nlc[slot0 + __popc(nb & ((1u << lane) - 1u))] = (unsigned short)c;
-            }
+            S.sbits[c >> 5] = sb;                     // same word, same value from every lane
+            S.qbits[c >> 5] = qb;
+            if (n) my_list[wcount + __popc(nb & lt_mask)] = (unsigned short)c;
+            wcount += __popc(nb);
             if (P.match_enabled) {
                 if (lit_unit == 8) {
                     const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
@@ -448,10 +486,11 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
                     if (S.lit_fp[r0 >> 26] == r0) push_candidate(S, c << 4, S.lit_masks[r0 >> 26]);
                     if (S.lit_fp[r1 >> 26] == r1) push_candidate(S, (c << 4) + 8, S.lit_masks[r1 >> 26]);
                 } else if ((c << 4) < tile_len) {
-                    filter_small_units(S, x, c << 4, lit_unit, lit_nkeys);
+                    filter_small_units(S, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
                 }
             }
         }
+        if (lane == 0) S.wcnt[warp] = wcount;
         if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(S, FXG_V_BYTE_RANGE, base);
     }
     __syncthreads();
@@ -483,11 +522,12 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
     if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(S, FXG_V_DENSE_LINES, base);
 
-    //      ordered '\n' position table from the chunks that have bytes < 0x20
+    //      ordered '\n' position table: every warp walks its own list of flagged chunks
     {
-        const unsigned int nn = S.n_nlc;
-        for (unsigned int q = tid; q < nn; q += kThreads) {
-            const int c = S.nlc[q];
+        const unsigned int nn = S.wcnt[warp];
+        const unsigned short *my_list = S.wl[warp];
+        for (unsigned int q = lane; q < nn; q += 32) {
+            const int c = my_list[q];
             unsigned int m16 = lin_mask(S.tile[c], kAdd20);
             uint2 w = *reinterpret_cast<const uint2 *>(&S.cnt[c & ~7]);
             const int sh = (c & 7) * 8;
@@ -533,7 +573,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
                     if (++spins > (1u << 25)) { atomicOr(&P.ctr->violation, 1u << 30); st = kFlagInc; break; }   // never hang the GPU
                 } while ((st >> 62) == 0);
                 __threadfence();
-                q1 = ld_vol64s(&D[idx].p1); q2 = ld_vol64s(&D[idx].p2); q3 = ld_vol64s(&D[idx].p3);
+                if (have < 3) { q1 = ld_vol64s(&D[idx].p1); q2 = ld_vol64s(&D[idx].p2); q3 = ld_vol64s(&D[idx].p3); }
             } else if (idx == -1) {
                 st = kFlagInc | (1ull << 60);      // virtual '\n' at offset -1 opens line 0
                 q1 = -1;
@@ -549,15 +589,20 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
                 excl += val;
                 if (first_inc < 32) count_done = true;
             }
-            int c3 = (int)((st >> 60) & 3);
-            for (int l = 0; l < 32 && have < 3; ++l) {
-                int cc = __shfl_sync(0xffffffffu, c3, l);
-                long long r1 = __shfl_sync(0xffffffffu, q1, l);
-                long long r2 = __shfl_sync(0xffffffffu, q2, l);
-                long long r3 = __shfl_sync(0xffffffffu, q3, l);
-                if (cc >= 1 && have < 3) { if (have == 0) e0 = r1; else if (have == 1) e1 = r1; else e2 = r1; ++have; }
-                if (cc >= 2 && have < 3) { if (have == 0) e0 = r2; else if (have == 1) e1 = r2; else e2 = r2; ++have; }
-                if (cc >= 3 && have < 3) { if (have == 0) e0 = r3; else if (have == 1) e1 = r3; else e2 = r3; ++have; }
+            if (have < 3) {
+                const int c3 = (int)((st >> 60) & 3);
+                unsigned int has = __ballot_sync(0xffffffffu, c3 > 0);
+                while (has && have < 3) {             // nearest predecessor first; normally one round
+                    const int l = __ffs(has) - 1;
+                    has &= has - 1;
+                    const int cc = __shfl_sync(0xffffffffu, c3, l);
+                    const long long r1 = __shfl_sync(0xffffffffu, q1, l);
+                    const long long r2 = __shfl_sync(0xffffffffu, q2, l);
+                    const long long r3 = __shfl_sync(0xffffffffu, q3, l);
+                    if (cc >= 1 && have < 3) { if (have == 0) e0 = r1; else if (have == 1) e1 = r1; else e2 = r1; ++have; }
+                    if (cc >= 2 && have < 3) { if (have == 0) e0 = r2; else if (have == 1) e1 = r2; else e2 = r2; ++have; }
+                    if (cc >= 3 && have < 3) { if (have == 0) e0 = r3; else if (have == 1) e1 = r3; else e2 = r3; ++have; }
+                }
             }
             look -= 32;
             if (look < -1) { have = 3; if (!count_done) count_done = true; }
