@@ -88,12 +88,13 @@ __device__ __forceinline__ unsigned long long ld_vol64(const unsigned long long 
     asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
     return v;
 }
-__device__ __forceinline__ long long ld_vol64s(const long long *p)
+__device__ __forceinline__ void st_vol64(long long *p, unsigned long long v)
 {
-    long long v;
-    asm volatile("ld.volatile.global.s64 %0, [%1];" : "=l"(v) : "l"(p));
-    return v;
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// descriptor encoding of a '\n' position: 0 = not written yet, ~0 = none, else pos + 2 (pos >= -1)
+__device__ __forceinline__ unsigned long long enc_pos(long long pos) { return pos == kNoPos ? ~0ull : (unsigned long long)(pos + 2); }
+__device__ __forceinline__ long long dec_pos(unsigned long long v) { return v == ~0ull ? kNoPos : (long long)v - 2; }
 
 // ---------------------------------------------------------------- SWAR helpers (bytes < 0x80)
 constexpr unsigned int kHi = 0x80808080u;
@@ -128,6 +129,10 @@ __host__ __device__ inline unsigned int il_below(int p)
     for (int b = 0; b < p; ++b) m |= 1u << (8 * (b & 3) + 7 - (b >> 2));
     return m;
 }
+
+__constant__ unsigned int kBelowTab[17] = {
+    0x00000000u, 0x00000080u, 0x00008080u, 0x00808080u, 0x80808080u, 0x808080c0u, 0x8080c0c0u, 0x80c0c0c0u, 0xc0c0c0c0u,
+    0xc0c0c0e0u, 0xc0c0e0e0u, 0xc0e0e0e0u, 0xe0e0e0e0u, 0xe0e0e0f0u, 0xe0e0f0f0u, 0xe0f0f0f0u, 0xf0f0f0f0u};
 
 // 16-bit mask, bit b set iff byte b of the chunk is below the threshold encoded by `add`
 __device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int add)
@@ -423,7 +428,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
         mbar_expect_tx(&S.mbar, (unsigned int)bulk);
         bulk_g2s(S.tile, P.buf + base, (unsigned int)bulk, &S.mbar);
     }
-    if (tid >= 128 && tid < 145) S.below[tid - 128] = il_below(tid - 128);
+    if (tid >= 128 && tid < 145) S.below[tid - 128] = kBelowTab[tid - 128];
     int lit_unit = 0, lit_nkeys = 0;
     unsigned int lit_mul1 = 0, lit_mul2 = 0;
     if (P.match_enabled) {
@@ -520,7 +525,12 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     __syncthreads();
     const unsigned int total = S.total;
     const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
-    if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(S, FXG_V_DENSE_LINES, base);
+    if (tid == 0) {
+        // publish the tile aggregate as early as possible: successors only need the count to move on
+        const unsigned long long own3 = n_tab >= 3 ? 3 : n_tab;
+        atomicExch(&P.desc[t].status, (t == 0 ? kFlagInc : kFlagAgg) | (own3 << 60) | (unsigned long long)total);
+        if (total > (unsigned int)kMaxTileLines) note_violation(S, FXG_V_DENSE_LINES, base);
+    }
 
     //      ordered '\n' position table: every warp walks its own list of flagged chunks
     {
@@ -546,73 +556,75 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     __syncthreads();
 
     if (warp == 0) {
-        // ---- 4. look-back: publish aggregate (+ own last three '\n'), fetch exclusive prefix
+        // ---- 4. look-back over the tile aggregates (up to 128 predecessors per round)
         TileDesc *D = P.desc;
-        unsigned long long own3 = n_tab >= 3 ? 3 : n_tab;
+        const unsigned long long own3 = n_tab >= 3 ? 3 : n_tab;
         if (lane == 0) {
-            D[t].p1 = n_tab >= 1 ? (long long)(base + S.nlpos[n_tab - 1]) : kNoPos;
-            D[t].p2 = n_tab >= 2 ? (long long)(base + S.nlpos[n_tab - 2]) : kNoPos;
-            D[t].p3 = n_tab >= 3 ? (long long)(base + S.nlpos[n_tab - 3]) : kNoPos;
+            // own last three '\n' for the successors' edge lines: p3 is written last and is the ready marker
+            st_vol64(&D[t].p1, enc_pos(n_tab >= 1 ? (long long)(base + S.nlpos[n_tab - 1]) : kNoPos));
+            st_vol64(&D[t].p2, enc_pos(n_tab >= 2 ? (long long)(base + S.nlpos[n_tab - 2]) : kNoPos));
             __threadfence();
-            unsigned long long st = (t == 0 ? kFlagInc : kFlagAgg) | (own3 << 60) | (unsigned long long)total;
-            atomicExch(&D[t].status, st);
+            st_vol64(&D[t].p3, enc_pos(n_tab >= 3 ? (long long)(base + S.nlpos[n_tab - 3]) : kNoPos));
         }
-        unsigned long long excl = 0;
-        long long e0 = kNoPos, e1 = kNoPos, e2 = kNoPos;
-        int have = 0;
-        bool count_done = false;
+        unsigned long long excl = 0, st_near = 0;
         long long look = (long long)t - 1;
-        while (!count_done || have < 3) {
-            long long idx = look - lane;
-            unsigned long long st;
-            long long q1 = kNoPos, q2 = kNoPos, q3 = kNoPos;
-            if (idx >= 0) {
-                unsigned int spins = 0;
-                do {
-                    st = ld_vol64(&D[idx].status);
-                    if (++spins > (1u << 25)) { atomicOr(&P.ctr->violation, 1u << 30); st = kFlagInc; break; }   // never hang the GPU
-                } while ((st >> 62) == 0);
-                __threadfence();
-                if (have < 3) { q1 = ld_vol64s(&D[idx].p1); q2 = ld_vol64s(&D[idx].p2); q3 = ld_vol64s(&D[idx].p3); }
-            } else if (idx == -1) {
-                st = kFlagInc | (1ull << 60);      // virtual '\n' at offset -1 opens line 0
-                q1 = -1;
-            } else {
-                st = kFlagInc;
+        bool done = false, first = true;
+        while (!done) {
+            unsigned long long st[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const long long idx = look - (k * 32 + lane);
+                st[k] = idx >= 0 ? ld_vol64(&D[idx].status) : (idx == -1 ? (kFlagInc | (1ull << 60)) : kFlagInc);
             }
-            if (!count_done) {
-                unsigned int incmask = __ballot_sync(0xffffffffu, (st >> 62) == 2);
-                int first_inc = incmask ? (__ffs(incmask) - 1) : 32;
-                unsigned long long val = (lane <= first_inc) ? (st & kValMask) : 0ull;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const long long idx = look - (k * 32 + lane);
+                unsigned int spins = 0;
+                while ((st[k] >> 62) == 0) {
+                    st[k] = ld_vol64(&D[idx].status);
+                    if (++spins > (1u << 25)) { atomicOr(&P.ctr->violation, 1u << 30); st[k] = kFlagInc; }   // never hang the GPU
+                }
+            }
+            if (first) { st_near = st[0]; first = false; }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (done) break;
+                const unsigned int incmask = __ballot_sync(0xffffffffu, (st[k] >> 62) == 2);
+                const int first_inc = incmask ? (__ffs(incmask) - 1) : 32;
+                unsigned long long val = (lane <= first_inc) ? (st[k] & kValMask) : 0ull;
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
                 excl += val;
-                if (first_inc < 32) count_done = true;
+                if (first_inc < 32) done = true;
             }
-            if (have < 3) {
-                const int c3 = (int)((st >> 60) & 3);
-                unsigned int has = __ballot_sync(0xffffffffu, c3 > 0);
-                while (has && have < 3) {             // nearest predecessor first; normally one round
-                    const int l = __ffs(has) - 1;
-                    has &= has - 1;
-                    const int cc = __shfl_sync(0xffffffffu, c3, l);
-                    const long long r1 = __shfl_sync(0xffffffffu, q1, l);
-                    const long long r2 = __shfl_sync(0xffffffffu, q2, l);
-                    const long long r3 = __shfl_sync(0xffffffffu, q3, l);
-                    if (cc >= 1 && have < 3) { if (have == 0) e0 = r1; else if (have == 1) e1 = r1; else e2 = r1; ++have; }
-                    if (cc >= 2 && have < 3) { if (have == 0) e0 = r2; else if (have == 1) e1 = r2; else e2 = r2; ++have; }
-                    if (cc >= 3 && have < 3) { if (have == 0) e0 = r3; else if (have == 1) e1 = r3; else e2 = r3; ++have; }
-                }
-            }
-            look -= 32;
-            if (look < -1) { have = 3; if (!count_done) count_done = true; }
+            look -= 128;
         }
         if (lane == 0) {
-            S.lbase = excl; S.e[0] = e0; S.e[1] = e1; S.e[2] = e2;
-            if (t != 0) {
-                unsigned long long st = kFlagInc | (own3 << 60) | (excl + (unsigned long long)total);
-                atomicExch(&D[t].status, st);
+            if (t != 0) atomicExch(&D[t].status, kFlagInc | (own3 << 60) | (excl + (unsigned long long)total));
+            // last three '\n' before the tile, nearest predecessor first (normally tile t-1 alone)
+            long long e[3] = {kNoPos, kNoPos, kNoPos};
+            int have = 0;
+            unsigned long long stq = st_near;
+            for (long long idx = (long long)t - 1; have < 3; --idx) {
+                if (idx < 0) { if (idx == -1) e[have++] = -1; break; }     // virtual '\n' at offset -1 opens line 0
+                if (idx != (long long)t - 1) {
+                    unsigned int spins = 0;
+                    do { stq = ld_vol64(&D[idx].status); } while ((stq >> 62) == 0 && ++spins < (1u << 25));
+                }
+                const int c3 = (int)((stq >> 60) & 3);
+                if (c3 == 0) continue;
+                unsigned long long p3v;
+                unsigned int spins = 0;
+                do { p3v = ld_vol64((const unsigned long long *)&D[idx].p3); } while (p3v == 0 && ++spins < (1u << 25));
+                __threadfence();
+                const long long q1 = dec_pos(ld_vol64((const unsigned long long *)&D[idx].p1));
+                const long long q2 = dec_pos(ld_vol64((const unsigned long long *)&D[idx].p2));
+                const long long q3 = dec_pos(p3v);
+                if (c3 >= 1 && have < 3) e[have++] = q1;
+                if (c3 >= 2 && have < 3) e[have++] = q2;
+                if (c3 >= 3 && have < 3) e[have++] = q3;
             }
+            S.lbase = excl; S.e[0] = e[0]; S.e[1] = e[1]; S.e[2] = e[2];
         }
     } else {
         // ---- 3. one thread per line, all four phase hypotheses at once (warps 1..7)
