@@ -45,7 +45,9 @@ struct fxg_ctx {
     unsigned long long *d_slot_hash = nullptr; int *d_slot_pat = nullptr; unsigned int exact_mask = 0;
     // scan resources (shared; everything is ordered on one stream)
     size_t cap_bytes = 0; size_t rec_cap = 0; size_t ntiles_cap = 0; size_t nblocks_cap = 0;
-    fxg::TileDesc *d_desc = nullptr; fxg::ScanCounters *d_ctr = nullptr; unsigned int *d_hitbits = nullptr;
+    fxg::TileInfo *d_info = nullptr; unsigned short *d_tile_nl = nullptr; unsigned int *d_tile_hit = nullptr;
+    unsigned long long *d_lbase = nullptr;
+    fxg::ScanCounters *d_ctr = nullptr; unsigned int *d_hitbits = nullptr;
     unsigned long long *d_rec_start = nullptr, *d_fld_off = nullptr, *d_block_sums = nullptr, *d_counts = nullptr;
     unsigned int *d_fld_len = nullptr;
     // host path
@@ -227,14 +229,18 @@ static int build_exact(fxg_ctx *ctx)
 // ---------------------------------------------------------------- resources
 static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
 {
-    if (nbytes <= ctx->cap_bytes && ctx->d_desc) return FXG_OK;
+    if (nbytes <= ctx->cap_bytes && ctx->d_info) return FXG_OK;
     size_t cap = std::max(nbytes, (size_t)1 << 20);
     size_t ntiles = (cap + kTileBytes - 1) / kTileBytes;
     size_t rec_cap = cap / 48 + 64;
     size_t words = (rec_cap + 31) / 32;
     size_t nblocks = (words + 1023) / 1024 + 1;
     cudaError_t e;
-    if ((e = dev_realloc(ctx->d_desc, ntiles)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile descriptors");
+    if ((e = dev_realloc(ctx->d_info, ntiles)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile info");
+    if ((e = dev_realloc(ctx->d_tile_nl, ntiles * (size_t)kNlStride)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line tables");
+    if ((e = dev_realloc(ctx->d_lbase, ntiles + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile prefix");
+    if (ctx->cfg.mode == FXG_MODE_LITERAL &&
+        (e = dev_realloc(ctx->d_tile_hit, ntiles * (size_t)kHitWords)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line hits");
     if ((e = dev_realloc(ctx->d_hitbits, words + 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc hit bitset");
     if (!ctx->d_ctr && (e = dev_realloc(ctx->d_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counters");
     if (!ctx->d_counts && (e = dev_realloc(ctx->d_counts, 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counts");
@@ -297,23 +303,21 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     size_t ntiles = (nbytes + kTileBytes - 1) / kTileBytes;
     size_t rec_cap = std::min(ctx->rec_cap, nbytes / 48 + 64);
     size_t words = (rec_cap + 31) / 32;
-    FXG_CUDA_OK(cudaMemsetAsync(ctx->d_desc, 0, ntiles * sizeof(TileDesc), st));
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_hitbits, 0, (words + 4) * sizeof(unsigned int), st));
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, sizeof(ScanCounters), st));
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_counts, 0, 2 * sizeof(unsigned long long), st));
     FXG_CUDA_OK(cudaMemsetAsync(&ctx->d_ctr->first_bad, 0xff, 8, st));      // min-reduced by the kernel
     ScanParams P;
     memset(&P, 0, sizeof P);
-    P.buf = d_buf; P.nbytes = nbytes; P.desc = ctx->d_desc; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
+    P.buf = d_buf; P.nbytes = nbytes; P.ntiles = ntiles; P.info = ctx->d_info; P.tile_nl = ctx->d_tile_nl;
+    P.tile_hit = ctx->d_tile_hit; P.lbase = ctx->d_lbase; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
     P.rec_start = emit ? ctx->d_rec_start : nullptr; P.rec_cap = rec_cap; P.one = 1;
     P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;
     if (!literal) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
     if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[1], st));
-    FXG_CUDA_OK(launch_scan_raw(P, st));
-    if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[2], st));
-    ctx->last_launches += 1;
+    FXG_CUDA_OK(launch_scan_raw(P, st, &ctx->last_launches, ctx->profiling ? s.ev[2] : nullptr));
     if (!literal) {
         FieldSrc src; memset(&src, 0, sizeof src);
         src.base = d_buf; src.off64 = ctx->d_fld_off; src.len32 = ctx->d_fld_len; src.n_lines_dev = &ctx->d_ctr->n_lines;
@@ -440,7 +444,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
     void *dev[] = {ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat,
-                   ctx->d_desc, ctx->d_ctr, ctx->d_hitbits, ctx->d_rec_start, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
+                   ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_ctr, ctx->d_hitbits, ctx->d_rec_start, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_in, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);

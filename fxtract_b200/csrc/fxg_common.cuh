@@ -19,29 +19,29 @@ constexpr int kChunksPerThread = kChunks / kThreads;   // 8
 constexpr int kMaxTileLines = 4096;            // newline-table capacity per tile
 constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
 
-// ---------------------------------------------------------------- lookback
-// One descriptor per tile for the single-pass (decoupled look-back) prefix sum of
-// newline counts.  Besides the count it carries the tile's own last three newline
-// positions, so a tile can check record structure (|qual| == |seq|, "+" line, '@')
-// for records that straddle its left edge without re-reading its predecessor.
-struct __align__(32) TileDesc {
-    unsigned long long status;   // [63:62] flag (0 none, 1 aggregate, 2 inclusive) [61:60] min(own count,3) [59:0] value
-    long long p1, p2, p3;        // own last / 2nd last / 3rd last newline (global offsets)
+// ---------------------------------------------------------------- per-tile results
+// The scan kernel has no cross-tile dependency: every tile publishes its '\n' count, its
+// ordered '\n' position table, a 4-bit mask saying for which line phases (global line
+// number of the tile's first line, mod 4) the tile is illegal, and one "line has a match"
+// bit per local line.  A tiny second kernel turns the counts into global line numbers
+// (exclusive scan), picks the phase, checks the few lines that straddle tile edges and
+// converts line hits into record hits / record starts / field tables.
+struct __align__(16) TileInfo {
+    unsigned int total;          // bytes < 0x20 in the tile (== '\n' count unless FXG_V_BYTE_RANGE is raised)
+    unsigned int flags;          // [3:0] phase r is illegal; [31:8] phase-independent FXG_V_* bits
+    unsigned short kinds[4];     // FXG_V_* bits per phase (filled for illegal phases only)
 };
-constexpr unsigned long long kFlagAgg = 1ull << 62;
-constexpr unsigned long long kFlagInc = 2ull << 62;
-constexpr unsigned long long kValMask = (1ull << 60) - 1;
+constexpr int kNlStride = kMaxTileLines;           // u16 entries per tile in the global '\n' table
+constexpr int kHitWords = kMaxTileLines / 32 + 1;  // line-hit words per tile (local line indices 0..kMaxTileLines)
 constexpr long long kNoPos = -(1ll << 62);
 
 // ---------------------------------------------------------------- counters
 struct ScanCounters {
     unsigned long long n_lines;
     unsigned long long n_hits;        // records with >= 1 hit (deduplicated through the hit bitset)
-    unsigned long long first_bad;     // min offset of a violation
+    unsigned long long first_bad;     // min offset of a violation (tile granularity)
     unsigned int violation;           // FXG_V_* bitmask
     unsigned int last_byte;           // last byte of the batch (must be '\n')
-    unsigned int ticket;              // dynamic tile ticket
-    unsigned int pad;
 };
 
 // ---------------------------------------------------------------- literal matcher tables
@@ -68,7 +68,11 @@ struct LiteralTable {
 struct ScanParams {
     const uint8_t *buf;
     unsigned long long nbytes;
-    TileDesc *desc;
+    unsigned long long ntiles;
+    TileInfo *info;                   // [ntiles]
+    unsigned short *tile_nl;          // [ntiles * kNlStride] tile-relative '\n' positions
+    unsigned int *tile_hit;           // [ntiles * kHitWords] line-hit bits (literal mode)
+    unsigned long long *lbase;        // [ntiles + 1] '\n' count before each tile (tile_prefix_kernel)
     ScanCounters *ctr;
     unsigned int *hitbits;            // 1 bit per record
     unsigned long long *rec_start;    // [rec_cap + 1] or nullptr (count-only)
@@ -143,7 +147,7 @@ struct LiteralFieldParams {
 
 // launchers (fxg_scan.cu / fxg_fields.cu / fxg_synth.cu)
 size_t scan_smem_bytes();
-cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream);
+cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launches, cudaEvent_t after_scan);
 cudaError_t launch_compact(const unsigned int *hitbits, const unsigned long long *rec_start, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
                            fxg_run *runs, unsigned long long run_cap, int invert, cudaStream_t stream, int *launches);

@@ -5,27 +5,31 @@
 //   prepare_data (main.cpp:291-304)   ->  target field
 //   strstr x1..2 (main.cpp:568-588)   ->  literal hit
 //   on_match (main.cpp:258-271)       ->  count / select
-// with a position-centric kernel.  Every CTA takes a 32 KiB tile (ticket order),
-// pulls it into shared memory with one bulk async copy (TMA, mbarrier completion)
-// and then
-//   1. main pass, 16 bytes per lane per step, SWAR only: '\n' mask and count, byte
-//      range check, per-chunk class summaries ("has a byte < 0x41", "has a byte
-//      < 0x21") as ballot bit rows, and the literal filter over aligned 8-byte units;
+// with a position-centric kernel that has NO cross-tile dependency.  Every CTA takes one
+// 32 KiB tile, pulls it into shared memory with one bulk async copy (TMA, mbarrier
+// completion) and then
+//   1. main pass, 16 bytes per lane per step, SWAR only: count of bytes < 0x20, byte
+//      range check, per-chunk class summaries ("has a byte < 0x41", "has a byte < 0x21")
+//      as ballot bit rows, and the literal filter over aligned 8-byte units;
 //   2. block scan of the per-chunk counts -> ordered table of '\n' positions;
-//   3. one thread per line: record structure and character classes, evaluated for
-//      ALL FOUR possible line phases of the tile at once (4-bit "hypothesis" mask),
-//      so nothing here waits for the global line number;
-//   4. meanwhile warp 0 turns the per-tile '\n' counts into the global line number
-//      of the tile with a single-pass decoupled look-back (line phase = line# mod 4
-//      decides header / sequence / plus / quality) and picks the hypothesis;
-//   5. outputs: hit bit per record (verified literal candidates), record starts
-//      (when records are emitted), target-field table (multi / exact second stage).
-// The canonical-FASTQ predicate is what makes
-// kseq-parse-then-print the identity on the record bytes; a batch that violates
-// it is reported (never silently mis-parsed) and the host re-routes it.
+//   3. one thread per line: record structure and character classes, evaluated for ALL
+//      FOUR possible line phases of the tile at once (4-bit "hypothesis" mask) -- FASTQ
+//      line phase is not locally decidable ('@' may open a quality line), but the checks
+//      are, once conditioned on the phase;
+//   4. literal candidates are verified byte by byte and recorded as "local line i has a
+//      match that is valid if line i has the target's role";
+//   5. the tile publishes {count, hypothesis mask, '\n' table, line-hit bits}.
+// tile_prefix_kernel then turns the counts into global line numbers (line phase =
+// line# mod 4 decides header / sequence / plus / quality) and tile_finalize_kernel picks
+// the hypothesis, checks the lines that straddle tile edges, converts line hits into
+// record hits and, when records are emitted or a second-stage matcher follows, writes
+// record starts / the target-field table.
+// The canonical-FASTQ predicate is what makes kseq-parse-then-print
+// the identity on the record bytes; a batch that violates it is reported (never silently
+// mis-parsed) and the host re-routes it.
 //
-// HBM traffic: each input byte is read once; outputs are 1 bit/record (+ 8 B per
-// record of record starts only when records are emitted).
+// HBM traffic: each input byte is read once; the scan writes 2 B per line ('\n' table) and
+// a few words per tile; the finalize pass reads those back.
 #include "fxg_common.cuh"
 
 namespace fxg {
@@ -40,6 +44,7 @@ struct __align__(128) ScanSmem {
     unsigned int below[17];                   // interleaved-layout mask of the bytes < p of a chunk
     unsigned int sbits[kChunks / 32];         // bit c: chunk c has a byte < 0x41 (not a sequence letter)
     unsigned int qbits[kChunks / 32];         // bit c: chunk c has a byte < 0x21 (not a quality char)
+    unsigned int linehit[kHitWords];          // bit i: local line i has a (phase-conditional) match
     unsigned long long lit_keys[64];
     unsigned int lit_fp[64];
     unsigned short lit_masks[64];
@@ -47,10 +52,8 @@ struct __align__(128) ScanSmem {
     unsigned short cand_mask[kCandCap];       // (pattern,shift) bits to verify
     unsigned int warp_sums[kThreads / 32];
     unsigned long long mbar;                  // bulk-copy completion barrier
-    unsigned long long lbase;                 // '\n' count before this tile
-    unsigned long long first_bad;
-    long long e[3];                           // last three '\n' positions before the tile
-    unsigned int n_cand, tile_hits, viol, hyp_bad, total, tile_id;
+    unsigned int kinds[4];                    // FXG_V_* bits per illegal phase (slow path)
+    unsigned int n_cand, viol, total, any_hit;
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -82,19 +85,6 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *mbar, unsigned int
                  "DONE:\n"
                  "}" ::"r"(smem_u32(mbar)), "r"(parity) : "memory");
 }
-__device__ __forceinline__ unsigned long long ld_vol64(const unsigned long long *p)
-{
-    unsigned long long v;
-    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ void st_vol64(long long *p, unsigned long long v)
-{
-    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-// descriptor encoding of a '\n' position: 0 = not written yet, ~0 = none, else pos + 2 (pos >= -1)
-__device__ __forceinline__ unsigned long long enc_pos(long long pos) { return pos == kNoPos ? ~0ull : (unsigned long long)(pos + 2); }
-__device__ __forceinline__ long long dec_pos(unsigned long long v) { return v == ~0ull ? kNoPos : (long long)v - 2; }
 
 // ---------------------------------------------------------------- SWAR helpers (bytes < 0x80)
 constexpr unsigned int kHi = 0x80808080u;
@@ -144,11 +134,7 @@ __device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int ad
     return n0 | (n1 << 4) | (n2 << 8) | (n3 << 12);
 }
 
-__device__ __forceinline__ void note_violation(ScanSmem &S, unsigned int bit, unsigned long long off)
-{
-    atomicOr(&S.viol, bit);
-    atomicMin(&S.first_bad, off);
-}
+__device__ __forceinline__ void note_violation(ScanSmem &S, unsigned int bit) { atomicOr(&S.viol, bit); }
 
 // byte of the batch at global offset g: from the staged tile when inside it
 __device__ __forceinline__ unsigned int text_byte(const ScanSmem &S, const ScanParams &P,
@@ -168,13 +154,6 @@ __device__ __forceinline__ unsigned int lines_before(const ScanSmem &S, int rel)
     const unsigned char *tb = reinterpret_cast<const unsigned char *>(S.tile);
     for (int b = c << 4; b < rel; ++b) n += (tb[b] < 0x20);
     return n;
-}
-
-// global position of the '\n' with tile-local index i (i >= -3)
-__device__ __forceinline__ long long nl_global(const ScanSmem &S, unsigned long long base, int i)
-{
-    if (i >= kMaxTileLines) return kNoPos;
-    return i >= 0 ? (long long)(base + S.nlpos[i]) : S.e[-i - 1];
 }
 
 // any bit set in rows[lo, hi) (chunk indices) of both class bit rows
@@ -238,41 +217,19 @@ __device__ __forceinline__ void line_flags(const ScanSmem &S, int i, int n_tab, 
     }
 }
 
-// 4-bit hypothesis mask: bit r set iff a line with these flags and local index i is illegal
-// when the tile starts at global line number == r (mod 4), i.e. the line's role is (i + r) & 3.
-__device__ __forceinline__ unsigned int hyp_bits(unsigned int f, int i)
+// FXG_V_* bits of a line with flags f if its role is `role` (0 header, 1 sequence, 2 plus, 3 quality)
+__device__ __forceinline__ unsigned int role_kinds(unsigned int f, int role)
 {
-    unsigned int v = ((f & (kFA | kFSP)) ? 1u : 0u) | ((f & (kFB | kFS)) ? 2u : 0u) | ((f & kFC) ? 4u : 0u) |
-                     ((f & (kFD | kFQ)) ? 8u : 0u);
-    const int s = i & 3;
-    return ((v >> s) | (v << (4 - s))) & 0xfu;
-}
-
-// slow path, known phase: turn the flags of line i into FXG_V_* bits
-__device__ __noinline__ void diagnose_line(ScanSmem &S, unsigned long long base, int i, int n_tab, int r)
-{
-    unsigned int own, nxt, tail;
-    line_flags(S, i, n_tab, own, nxt, tail);
-    const unsigned long long at = base + S.nlpos[i];
-    const int role = (i + r) & 3;
-    if (role == 0) {
-        if (own & kFA) note_violation(S, FXG_V_HEADER_AT, at);
-        if (own & kFSP) note_violation(S, FXG_V_HEADER_SPACE, at);
-    } else if (role == 1) {
-        if (own & kFB) note_violation(S, FXG_V_EMPTY_SEQ, at);
-        if (own & kFS) note_violation(S, FXG_V_SEQ_CLASS, at);
-    } else if (role == 2) {
-        if (own & kFC) note_violation(S, FXG_V_PLUS_LINE, at);
-    } else {
-        if (own & kFD) note_violation(S, FXG_V_QUAL_LEN, at);
-        if (own & kFQ) note_violation(S, FXG_V_QUAL_CLASS, at);
-    }
-    const int role1 = (role + 1) & 3;
-    if (role1 == 1 && ((nxt | tail) & kFS)) note_violation(S, FXG_V_SEQ_CLASS, at + 1);
-    if (role1 == 3 && ((nxt | tail) & kFQ)) note_violation(S, FXG_V_QUAL_CLASS, at + 1);
+    if (role == 0) return ((f & kFA) ? FXG_V_HEADER_AT : 0u) | ((f & kFSP) ? FXG_V_HEADER_SPACE : 0u);
+    if (role == 1) return ((f & kFB) ? FXG_V_EMPTY_SEQ : 0u) | ((f & kFS) ? FXG_V_SEQ_CLASS : 0u);
+    if (role == 2) return (f & kFC) ? FXG_V_PLUS_LINE : 0u;
+    return ((f & kFD) ? FXG_V_QUAL_LEN : 0u) | ((f & kFQ) ? FXG_V_QUAL_CLASS : 0u);
 }
 
 // ---------------------------------------------------------------- verification of one literal candidate
+// A verified occurrence is recorded on its local line; whether that line has the target's
+// role (sequence / quality / header) is decided by tile_finalize_kernel.  Header targets add
+// the geometric condition (inside the name / inside the comment), which is phase-free.
 __device__ __noinline__ void verify_candidate(ScanSmem &S, const ScanParams &P, unsigned long long base, int n_tab,
                                               int unit_rel, unsigned int bits)
 {
@@ -290,17 +247,23 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, const ScanParams &P, 
             if (text_byte(S, P, base, p + k) != pb[k]) { ok = false; break; }
         }
         if (!ok) continue;
-        // line attribution: number of '\n' before p
+        // local line: number of '\n' before p inside the tile (an occurrence that starts in the
+        // previous tile lies on this tile's line 0)
         int rel = (int)(p - (long long)base);
         unsigned int loc = rel > 0 ? lines_before(S, rel) : 0u;
-        unsigned long long L = S.lbase + loc;
-        int ph = (int)(L & 3);
-        bool hit = false;
-        if (P.target == FXG_TARGET_SEQ) hit = (ph == 1);
-        else if (P.target == FXG_TARGET_QUAL) hit = (ph == 3);
-        else if (ph == 0) {
+        if (loc > (unsigned int)kMaxTileLines) continue;       // tile is flagged FXG_V_DENSE_LINES anyway
+        bool hit = true;
+        if (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT) {
             // header line: name = (ls, first ' ' or end), comment = after that ' '
-            long long ls = nl_global(S, base, (int)loc - 1) + 1;      // offset of '@'
+            long long ls;
+            if (loc >= 1 && loc <= (unsigned int)n_tab) ls = (long long)base + S.nlpos[loc - 1] + 1;
+            else {
+                long long q = (p < (long long)base ? p : (long long)base) - 1;
+                int guard = 1 << 20;
+                while (q >= 0 && P.buf[q] != '\n' && --guard) --q;
+                if (!guard) { note_violation(S, FXG_V_DENSE_LINES); continue; }
+                ls = q + 1;
+            }
             long long q = ls + 1, sp = -1;
             for (;; ++q) {
                 if ((unsigned long long)q >= P.nbytes) break;
@@ -315,16 +278,7 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, const ScanParams &P, 
                 hit = (sp >= 0) && (p >= sp + 1);
             }
         }
-        if (hit) {
-            unsigned long long rec = L >> 2;
-            if (rec < P.rec_cap) {
-                unsigned int bit = 1u << (rec & 31);
-                unsigned int old = atomicOr(&P.hitbits[rec >> 5], bit);
-                if (!(old & bit)) atomicAdd(&S.tile_hits, 1u);
-            } else {
-                note_violation(S, FXG_V_DENSE_LINES, (unsigned long long)p);
-            }
-        }
+        if (hit) { atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31)); S.any_hit = 1; }
     }
 }
 
@@ -347,76 +301,14 @@ __device__ __noinline__ void filter_small_units(ScanSmem &S, unsigned int x0, un
     }
 }
 
-// record / field table entries of local line i once the phase is known
-__device__ __forceinline__ void emit_line(const ScanSmem &S, const ScanParams &P, unsigned long long base, int i)
-{
-    const unsigned long long j = S.lbase + (unsigned long long)i;
-    const int ph = (int)(j & 3);
-    const unsigned long long rec = j >> 2;
-    const long long pos = (long long)base + S.nlpos[i];
-    if (ph == 3) {
-        if (P.rec_start && rec + 1 <= P.rec_cap) P.rec_start[rec + 1] = (unsigned long long)(pos + 1);
-        if (P.fld_off && P.target == FXG_TARGET_QUAL && rec < P.rec_cap) {
-            const long long prev = nl_global(S, base, i - 1);
-            P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
-        }
-    } else if (ph == 1) {
-        if (P.fld_off && P.target == FXG_TARGET_SEQ && rec < P.rec_cap) {
-            const long long prev = nl_global(S, base, i - 1);
-            P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
-        }
-    } else if (ph == 0) {
-        if (P.fld_off && (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT) && rec < P.rec_cap) {
-            const long long prev = nl_global(S, base, i - 1);
-            long long q = prev + 2, sp = -1;
-            for (; q < pos; ++q) if (text_byte(S, P, base, q) == ' ') { sp = q; break; }
-            if (P.target == FXG_TARGET_NAME) {
-                long long ne = sp >= 0 ? sp : pos;
-                P.fld_off[rec] = (unsigned long long)(prev + 2);
-                P.fld_len[rec] = (unsigned int)(ne > prev + 2 ? ne - (prev + 2) : 0);
-            } else {
-                P.fld_off[rec] = (unsigned long long)(sp >= 0 ? sp + 1 : pos);
-                P.fld_len[rec] = (unsigned int)(sp >= 0 ? pos - (sp + 1) : 0);
-            }
-        }
-    }
-}
-
-// structure checks of the first lines of a tile, whose predecessors lie in earlier tiles (phase known)
-__device__ __noinline__ void check_edge_line(ScanSmem &S, const ScanParams &P, unsigned long long base, int i)
-{
-    const int ph = (int)((S.lbase + (unsigned long long)i) & 3);
-    const long long pos = (long long)base + S.nlpos[i];
-    const long long prev = nl_global(S, base, i - 1);
-    const long long llen = pos - prev - 1;
-    if (i == 0) {
-        if (llen > 0 && text_byte(S, P, base, pos - 1) == ' ' && ph == 0) note_violation(S, FXG_V_HEADER_SPACE, (unsigned long long)pos);
-        if (ph == 0 && (llen < 1 || text_byte(S, P, base, prev + 1) != '@')) note_violation(S, FXG_V_HEADER_AT, (unsigned long long)(prev + 1));
-        if (ph == 1 && llen < 1) note_violation(S, FXG_V_EMPTY_SEQ, (unsigned long long)pos);
-        if (ph == 2 && (llen != 1 || text_byte(S, P, base, pos - 1) != '+')) note_violation(S, FXG_V_PLUS_LINE, (unsigned long long)pos);
-    }
-    if (ph == 3) {
-        const long long slen = nl_global(S, base, i - 2) - nl_global(S, base, i - 3) - 1;
-        if (llen != slen) note_violation(S, FXG_V_QUAL_LEN, (unsigned long long)pos);
-    }
-}
-
-// ---------------------------------------------------------------- the kernel
-__global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams P)
+// ---------------------------------------------------------------- kernel 1: per-tile scan
+__global__ void __launch_bounds__(kThreads, 4) scan_tiles_kernel(const ScanParams P)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem &S = *reinterpret_cast<ScanSmem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LiteralTable *lit = P.lit;
-
-    if (tid == 0) {
-        S.tile_id = atomicAdd(&P.ctr->ticket, 1u);
-        S.n_cand = 0; S.tile_hits = 0; S.viol = 0; S.hyp_bad = 0;
-        S.first_bad = ~0ull;
-        mbar_init(&S.mbar, 1);
-    }
-    __syncthreads();
-    const unsigned long long t = S.tile_id;
+    const unsigned long long t = blockIdx.x;
     const unsigned long long base = t * (unsigned long long)kTileBytes;
     const unsigned long long remain = P.nbytes - base;
     const int tile_len = remain < (unsigned long long)kTileBytes ? (int)remain : kTileBytes;
@@ -424,9 +316,14 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     unsigned char *tb = reinterpret_cast<unsigned char *>(S.tile);
 
     // ---- stage the tile: one bulk async copy; the ragged end of the batch is patched by hand
-    if (tid == 0 && bulk) {
-        mbar_expect_tx(&S.mbar, (unsigned int)bulk);
-        bulk_g2s(S.tile, P.buf + base, (unsigned int)bulk, &S.mbar);
+    if (tid == 0) {
+        S.n_cand = 0; S.viol = 0; S.any_hit = 0;
+        S.kinds[0] = S.kinds[1] = S.kinds[2] = S.kinds[3] = 0;
+        mbar_init(&S.mbar, 1);
+        if (bulk) {
+            mbar_expect_tx(&S.mbar, (unsigned int)bulk);
+            bulk_g2s(S.tile, P.buf + base, (unsigned int)bulk, &S.mbar);
+        }
     }
     if (tid >= 128 && tid < 145) S.below[tid - 128] = kBelowTab[tid - 128];
     int lit_unit = 0, lit_nkeys = 0;
@@ -437,6 +334,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
             const int k = tid - 64;
             S.lit_keys[k] = lit->keys[k]; S.lit_fp[k] = lit->fp[k]; S.lit_masks[k] = lit->masks[k];
         }
+        for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
     }
     if (tile_len < kTileBytes) {
         for (int b = bulk + tid * 16; b < kTileBytes; b += kThreads * 16) {
@@ -448,8 +346,8 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
             S.tile[b >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
         }
     }
+    __syncthreads();                 // mbarrier initialised, tables staged
     if (bulk) mbar_wait(&S.mbar, 0);
-    __syncthreads();
 
     // ---- 1. main pass: 16 bytes per lane per step
     {
@@ -496,7 +394,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
             }
         }
         if (lane == 0) S.wcnt[warp] = wcount;
-        if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(S, FXG_V_BYTE_RANGE, base);
+        if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(S, FXG_V_BYTE_RANGE);
     }
     __syncthreads();
 
@@ -525,12 +423,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     __syncthreads();
     const unsigned int total = S.total;
     const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
-    if (tid == 0) {
-        // publish the tile aggregate as early as possible: successors only need the count to move on
-        const unsigned long long own3 = n_tab >= 3 ? 3 : n_tab;
-        atomicExch(&P.desc[t].status, (t == 0 ? kFlagInc : kFlagAgg) | (own3 << 60) | (unsigned long long)total);
-        if (total > (unsigned int)kMaxTileLines) note_violation(S, FXG_V_DENSE_LINES, base);
-    }
+    if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(S, FXG_V_DENSE_LINES);
 
     //      ordered '\n' position table: every warp walks its own list of flagged chunks
     {
@@ -547,7 +440,7 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
             while (m16) {
                 const int p = (c << 4) + __ffs(m16) - 1;
                 m16 &= m16 - 1;
-                if (tb[p] != '\n') note_violation(S, FXG_V_BYTE_RANGE, base + p);
+                if (tb[p] != '\n') note_violation(S, FXG_V_BYTE_RANGE);
                 if (idx < (unsigned int)kMaxTileLines) S.nlpos[idx] = (unsigned short)p;
                 ++idx;
             }
@@ -555,110 +448,36 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     }
     __syncthreads();
 
-    if (warp == 0) {
-        // ---- 4. look-back over the tile aggregates (up to 128 predecessors per round)
-        TileDesc *D = P.desc;
-        const unsigned long long own3 = n_tab >= 3 ? 3 : n_tab;
-        if (lane == 0) {
-            // own last three '\n' for the successors' edge lines: p3 is written last and is the ready marker
-            st_vol64(&D[t].p1, enc_pos(n_tab >= 1 ? (long long)(base + S.nlpos[n_tab - 1]) : kNoPos));
-            st_vol64(&D[t].p2, enc_pos(n_tab >= 2 ? (long long)(base + S.nlpos[n_tab - 2]) : kNoPos));
-            __threadfence();
-            st_vol64(&D[t].p3, enc_pos(n_tab >= 3 ? (long long)(base + S.nlpos[n_tab - 3]) : kNoPos));
-        }
-        unsigned long long excl = 0, st_near = 0;
-        long long look = (long long)t - 1;
-        bool done = false, first = true;
-        while (!done) {
-            unsigned long long st[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const long long idx = look - (k * 32 + lane);
-                st[k] = idx >= 0 ? ld_vol64(&D[idx].status) : (idx == -1 ? (kFlagInc | (1ull << 60)) : kFlagInc);
-            }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const long long idx = look - (k * 32 + lane);
-                unsigned int spins = 0;
-                while ((st[k] >> 62) == 0) {
-                    st[k] = ld_vol64(&D[idx].status);
-                    if (++spins > (1u << 25)) { atomicOr(&P.ctr->violation, 1u << 30); st[k] = kFlagInc; }   // never hang the GPU
-                }
-            }
-            if (first) { st_near = st[0]; first = false; }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                if (done) break;
-                const unsigned int incmask = __ballot_sync(0xffffffffu, (st[k] >> 62) == 2);
-                const int first_inc = incmask ? (__ffs(incmask) - 1) : 32;
-                unsigned long long val = (lane <= first_inc) ? (st[k] & kValMask) : 0ull;
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
-                excl += val;
-                if (first_inc < 32) done = true;
-            }
-            look -= 128;
-        }
-        if (lane == 0) {
-            if (t != 0) atomicExch(&D[t].status, kFlagInc | (own3 << 60) | (excl + (unsigned long long)total));
-            // last three '\n' before the tile, nearest predecessor first (normally tile t-1 alone)
-            long long e[3] = {kNoPos, kNoPos, kNoPos};
-            int have = 0;
-            unsigned long long stq = st_near;
-            for (long long idx = (long long)t - 1; have < 3; --idx) {
-                if (idx < 0) { if (idx == -1) e[have++] = -1; break; }     // virtual '\n' at offset -1 opens line 0
-                if (idx != (long long)t - 1) {
-                    unsigned int spins = 0;
-                    do { stq = ld_vol64(&D[idx].status); } while ((stq >> 62) == 0 && ++spins < (1u << 25));
-                }
-                const int c3 = (int)((stq >> 60) & 3);
-                if (c3 == 0) continue;
-                unsigned long long p3v;
-                unsigned int spins = 0;
-                do { p3v = ld_vol64((const unsigned long long *)&D[idx].p3); } while (p3v == 0 && ++spins < (1u << 25));
-                __threadfence();
-                const long long q1 = dec_pos(ld_vol64((const unsigned long long *)&D[idx].p1));
-                const long long q2 = dec_pos(ld_vol64((const unsigned long long *)&D[idx].p2));
-                const long long q3 = dec_pos(p3v);
-                if (c3 >= 1 && have < 3) e[have++] = q1;
-                if (c3 >= 2 && have < 3) e[have++] = q2;
-                if (c3 >= 3 && have < 3) e[have++] = q3;
-            }
-            S.lbase = excl; S.e[0] = e[0]; S.e[1] = e[1]; S.e[2] = e[2];
-        }
-    } else {
-        // ---- 3. one thread per line, all four phase hypotheses at once (warps 1..7)
-        unsigned int bad4 = 0;
+    // ---- 3. one thread per line, all four phase hypotheses at once.  The stride (256) is a
+    //         multiple of 4, so every line of a thread has the same index mod 4: the flags of a
+    //         thread's lines are OR-ed and mapped to the four phases once, after the loop.
+    //         (A canonical tile is illegal under three of the four phases; only the phase that
+    //         tile_finalize_kernel selects matters.)
+    {
+        unsigned int f_own = 0, f_nxt = 0;
         if (n_tab == 0) {
-            if (tid == 32) {
+            if (tid == 0) {
                 unsigned int ms, mq;
                 range_any2(S, 0, kChunks, ms, mq);
-                bad4 = hyp_bits((ms ? kFS : 0u) | (mq ? kFQ : 0u), 0);
+                f_own = (ms ? kFS : 0u) | (mq ? kFQ : 0u);
             }
         } else {
-            for (int i = tid - 32; i < n_tab; i += kThreads - 32) {
+            for (int i = tid; i < n_tab; i += kThreads) {
                 unsigned int own, nxt, tail;
                 line_flags(S, i, n_tab, own, nxt, tail);
-                bad4 |= hyp_bits(own, i) | hyp_bits(nxt | tail, i + 1);
+                f_own |= own;
+                f_nxt |= nxt | tail;
             }
         }
-        bad4 = __reduce_or_sync(0xffffffffu, bad4);
-        if (lane == 0 && bad4) atomicOr(&S.hyp_bad, bad4);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            unsigned int k = role_kinds(f_own, (tid + r) & 3) | role_kinds(f_nxt, (tid + 1 + r) & 3);
+            k = __reduce_or_sync(0xffffffffu, k);
+            if (lane == 0 && k) atomicOr(&S.kinds[r], k);
+        }
     }
-    __syncthreads();
-    const unsigned long long lbase = S.lbase;
-    const int r = (int)(lbase & 3);
 
-    // ---- 5. phase is known: pick the hypothesis, edge lines, outputs, candidates
-    if ((S.hyp_bad >> r) & 1u) {
-        if (n_tab == 0) { if (tid == 0) note_violation(S, r == 1 ? FXG_V_SEQ_CLASS : FXG_V_QUAL_CLASS, base); }
-        else for (int i = tid; i < n_tab; i += kThreads) diagnose_line(S, base, i, n_tab, r);
-    }
-    if (tid < 3 && tid < n_tab) check_edge_line(S, P, base, tid);
-    if (P.rec_start || P.fld_off) {
-        for (int i = tid; i < n_tab; i += kThreads) emit_line(S, P, base, i);
-        if (t == 0 && tid == 0 && P.rec_start) P.rec_start[0] = 0;
-    }
+    // ---- 4. verify the literal candidates (phase-free; line hits)
     if (P.match_enabled) {
         const unsigned int nc_all = S.n_cand;
         if (nc_all <= (unsigned int)kCandCap) {
@@ -687,33 +506,214 @@ __global__ void __launch_bounds__(kThreads, 4) scan_raw_kernel(const ScanParams 
     }
     __syncthreads();
 
-    // ---- epilogue
-    if (tid == 0) {
-        if (S.tile_hits) atomicAdd(&P.ctr->n_hits, (unsigned long long)S.tile_hits);
-        if (S.viol) { atomicOr(&P.ctr->violation, S.viol); atomicMin(&P.ctr->first_bad, S.first_bad); }
-        if (base + (unsigned long long)tile_len == P.nbytes) {
-            P.ctr->n_lines = lbase + total;
-            P.ctr->last_byte = tb[tile_len - 1];
+    // ---- 5. publish the tile: count, per-phase violations, '\n' table, line hits
+    {
+        uint4 *dst = reinterpret_cast<uint4 *>(P.tile_nl + t * (unsigned long long)kNlStride);
+        const uint4 *src = reinterpret_cast<const uint4 *>(S.nlpos);
+        for (int q = tid; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
+        if (P.match_enabled) {
+            unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
+            const int nw = (n_tab >> 5) + 1;               // local line indices 0..n_tab
+            if (tid < nw) hd[tid] = S.any_hit ? S.linehit[tid] : 0u;
         }
+        if (tid == 0) {
+            TileInfo ti;
+            ti.total = total;
+            ti.flags = (S.kinds[0] ? 1u : 0u) | (S.kinds[1] ? 2u : 0u) | (S.kinds[2] ? 4u : 0u) | (S.kinds[3] ? 8u : 0u) |
+                       (S.viol << 8);
+            ti.kinds[0] = (unsigned short)S.kinds[0]; ti.kinds[1] = (unsigned short)S.kinds[1];
+            ti.kinds[2] = (unsigned short)S.kinds[2]; ti.kinds[3] = (unsigned short)S.kinds[3];
+            P.info[t] = ti;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- kernel 2a: exclusive scan of the tile counts
+// One CTA walks the (small) array: 4 tiles per thread per round, carry in shared memory.
+constexpr int kPrefixThreads = 1024;
+__global__ void __launch_bounds__(kPrefixThreads) tile_prefix_kernel(const ScanParams P)
+{
+    __shared__ unsigned long long wsum[kPrefixThreads / 32];
+    __shared__ unsigned long long carry_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (unsigned long long t0 = 0; t0 < P.ntiles; t0 += 4ull * kPrefixThreads) {
+        unsigned long long v[4], s = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned long long ti = t0 + 4ull * tid + k;
+            v[k] = ti < P.ntiles ? (unsigned long long)P.info[ti].total : 0ull;
+            s += v[k];
+        }
+        unsigned long long inc = s;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        unsigned long long woff = 0, tot = 0;
+        for (int w = 0; w < kPrefixThreads / 32; ++w) { unsigned long long x = wsum[w]; if (w < warp) woff += x; tot += x; }
+        unsigned long long run = carry_s + woff + inc - s;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned long long ti = t0 + 4ull * tid + k;
+            if (ti < P.ntiles) P.lbase[ti] = run;
+            run += v[k];
+        }
+        __syncthreads();
+        if (tid == 0) carry_s += tot;
+        __syncthreads();
+    }
+    if (tid == 0) P.lbase[P.ntiles] = carry_s;
+}
+
+// ---------------------------------------------------------------- kernel 2b: per-tile finalize (one warp per tile)
+struct TileView {
+    const ScanParams &P;
+    __device__ TileView(const ScanParams &p) : P(p) {}
+    __device__ int lines(unsigned long long t) const
+    {
+        unsigned int n = P.info[t].total;
+        return n < (unsigned int)kMaxTileLines ? (int)n : kMaxTileLines;
+    }
+    __device__ long long nl(unsigned long long t, int i) const
+    {
+        return (long long)(t * (unsigned long long)kTileBytes) + P.tile_nl[t * (unsigned long long)kNlStride + i];
+    }
+    // k-th '\n' before tile t (k = 1 is the nearest); a virtual '\n' at offset -1 opens line 0
+    __device__ long long prev_nl(unsigned long long t, int k) const
+    {
+        for (long long tt = (long long)t - 1; tt >= 0; --tt) {
+            const int n = lines((unsigned long long)tt);
+            if (n >= k) return nl((unsigned long long)tt, n - k);
+            k -= n;
+        }
+        return k == 1 ? -1 : kNoPos;
+    }
+    // global position of the '\n' with tile-local index i (i >= -3)
+    __device__ long long at(unsigned long long t, int i) const { return i >= 0 ? nl(t, i) : prev_nl(t, -i); }
+};
+
+__global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (t >= P.ntiles) return;
+    const TileView V(P);
+    const TileInfo ti = P.info[t];
+    const unsigned long long lb = P.lbase[t];
+    const unsigned long long base = t * (unsigned long long)kTileBytes;
+    const int r = (int)(lb & 3);
+    const int n_tab = ti.total < (unsigned int)kMaxTileLines ? (int)ti.total : kMaxTileLines;
+    unsigned int viol = 0;
+    if (lane == 0) {
+        viol = ti.flags >> 8;
+        if ((ti.flags >> r) & 1u) viol |= ti.kinds[r] ? (unsigned int)ti.kinds[r] : (unsigned int)FXG_V_SEQ_CLASS;
+    }
+    // structure of the first lines of the tile, whose predecessors lie in earlier tiles
+    if (lane < 3 && lane < n_tab) {
+        const int i = lane;
+        const int ph = (int)((lb + (unsigned long long)i) & 3);
+        const long long pos = V.nl(t, i);
+        if (i == 0) {
+            const long long prev = V.prev_nl(t, 1);
+            const long long llen = pos - prev - 1;
+            if (ph == 0) {
+                if (llen < 1 || P.buf[prev + 1] != '@') viol |= FXG_V_HEADER_AT;
+                else if (P.buf[pos - 1] == ' ') viol |= FXG_V_HEADER_SPACE;
+            } else if (ph == 1) { if (llen < 1) viol |= FXG_V_EMPTY_SEQ; }
+            else if (ph == 2) { if (llen != 1 || P.buf[pos - 1] != '+') viol |= FXG_V_PLUS_LINE; }
+        }
+        if (ph == 3) {
+            const long long llen = pos - V.at(t, i - 1) - 1;
+            const long long slen = V.at(t, i - 2) - V.at(t, i - 3) - 1;
+            if (llen != slen) viol |= FXG_V_QUAL_LEN;
+        }
+    }
+    viol = __reduce_or_sync(0xffffffffu, viol);
+    if (lane == 0 && viol) { atomicOr(&P.ctr->violation, viol); atomicMin(&P.ctr->first_bad, base); }
+
+    // line hits -> record hits: only lines whose role is the target's count
+    if (P.match_enabled) {
+        const int want = P.target == FXG_TARGET_SEQ ? 1 : (P.target == FXG_TARGET_QUAL ? 3 : 0);
+        const unsigned int role_mask = 0x11111111u << ((want - r) & 3);     // 32 % 4 == 0: same mask for every word
+        const unsigned int *hw = P.tile_hit + t * (unsigned long long)kHitWords;
+        unsigned int fresh = 0;
+        for (int w = lane; w * 32 <= n_tab; w += 32) {
+            unsigned int bits = hw[w] & role_mask;
+            while (bits) {
+                const int b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                const unsigned long long rec = (lb + (unsigned long long)(w * 32 + b)) >> 2;
+                if (rec < P.rec_cap) {
+                    const unsigned int bit = 1u << (rec & 31);
+                    const unsigned int old = atomicOr(&P.hitbits[rec >> 5], bit);
+                    if (!(old & bit)) ++fresh;
+                }
+            }
+        }
+        fresh = __reduce_add_sync(0xffffffffu, fresh);
+        if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
+    }
+
+    // record starts / target-field table
+    if (P.rec_start || P.fld_off) {
+        for (int i = lane; i < n_tab; i += 32) {
+            const unsigned long long j = lb + (unsigned long long)i;
+            const int ph = (int)(j & 3);
+            const unsigned long long rec = j >> 2;
+            const long long pos = V.nl(t, i);
+            if (ph == 3 && P.rec_start && rec + 1 <= P.rec_cap) P.rec_start[rec + 1] = (unsigned long long)(pos + 1);
+            if (P.fld_off && rec < P.rec_cap) {
+                if ((ph == 3 && P.target == FXG_TARGET_QUAL) || (ph == 1 && P.target == FXG_TARGET_SEQ)) {
+                    const long long prev = V.at(t, i - 1);
+                    P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
+                } else if (ph == 0 && (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT)) {
+                    const long long prev = V.at(t, i - 1);
+                    long long q = prev + 2, sp = -1;
+                    for (; q < pos; ++q) if (P.buf[q] == ' ') { sp = q; break; }
+                    if (P.target == FXG_TARGET_NAME) {
+                        const long long ne = sp >= 0 ? sp : pos;
+                        P.fld_off[rec] = (unsigned long long)(prev + 2);
+                        P.fld_len[rec] = (unsigned int)(ne > prev + 2 ? ne - (prev + 2) : 0);
+                    } else {
+                        P.fld_off[rec] = (unsigned long long)(sp >= 0 ? sp + 1 : pos);
+                        P.fld_len[rec] = (unsigned int)(sp >= 0 ? pos - (sp + 1) : 0);
+                    }
+                }
+            }
+        }
+        if (t == 0 && lane == 0 && P.rec_start) P.rec_start[0] = 0;
+    }
+    if (t + 1 == P.ntiles && lane == 0) {
+        P.ctr->n_lines = lb + ti.total;
+        P.ctr->last_byte = P.buf[P.nbytes - 1];
     }
 }
 
 size_t scan_smem_bytes() { return sizeof(ScanSmem); }
 
-cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream)
+cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launches, cudaEvent_t after_scan)
 {
     static bool attr_set[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(scan_raw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
+        cudaError_t e = cudaFuncSetAttribute(scan_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     if (((uintptr_t)P.buf & 15) != 0) return cudaErrorMisalignedAddress;     // bulk copies need 16-byte alignment
-    unsigned long long ntiles = (P.nbytes + kTileBytes - 1) / kTileBytes;
-    if (ntiles == 0) return cudaSuccess;
-    scan_raw_kernel<<<(unsigned int)ntiles, kThreads, sizeof(ScanSmem), stream>>>(P);
+    if (P.ntiles == 0) return cudaSuccess;
+    scan_tiles_kernel<<<(unsigned int)P.ntiles, kThreads, sizeof(ScanSmem), stream>>>(P);
+    if (after_scan) cudaEventRecord(after_scan, stream);
+    tile_prefix_kernel<<<1, kPrefixThreads, 0, stream>>>(P);
+    const unsigned long long warps_per_block = 256 / 32;
+    tile_finalize_kernel<<<(unsigned int)((P.ntiles + warps_per_block - 1) / warps_per_block), 256, 0, stream>>>(P);
+    if (launches) *launches += 3;
     return cudaGetLastError();
 }
 
