@@ -72,7 +72,8 @@ struct ScanParams {
     TileInfo *info;                   // [ntiles]
     unsigned short *tile_nl;          // [ntiles * kNlStride] tile-relative '\n' positions
     unsigned int *tile_hit;           // [ntiles * kHitWords] line-hit bits (literal mode)
-    unsigned long long *lbase;        // [ntiles + 1] '\n' count before each tile (tile_prefix_kernel)
+    unsigned long long *lbase;        // [ntiles] '\n' count before each tile, relative to its 4096-tile span
+    unsigned long long *bsum;         // [ntiles / 4096 + 1] '\n' count before each span
     ScanCounters *ctr;
     unsigned int *hitbits;            // 1 bit per record
     unsigned long long *rec_start;    // [rec_cap + 1] or nullptr (count-only)

@@ -529,24 +529,52 @@ __global__ void __launch_bounds__(kThreads, 4) scan_tiles_kernel(const ScanParam
 }
 
 // ---------------------------------------------------------------- kernel 2a: exclusive scan of the tile counts
-// One CTA walks the (small) array: 4 tiles per thread per round, carry in shared memory.
+// Two tiny launches: every CTA scans 4096 consecutive tiles (4 per thread) and leaves its
+// block sum; one CTA then scans the block sums.  '\n' count before tile t =
+// lbase[t] + bsum[t / kPrefixSpan].
 constexpr int kPrefixThreads = 1024;
-__global__ void __launch_bounds__(kPrefixThreads) tile_prefix_kernel(const ScanParams P)
+constexpr int kPrefixSpan = 4 * kPrefixThreads;
+__global__ void __launch_bounds__(kPrefixThreads) tile_prefix_local_kernel(const ScanParams P)
+{
+    __shared__ unsigned long long wsum[kPrefixThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned long long t0 = (unsigned long long)blockIdx.x * kPrefixSpan + 4ull * tid;
+    unsigned long long v[4], s = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        v[k] = t0 + k < P.ntiles ? (unsigned long long)P.info[t0 + k].total : 0ull;
+        s += v[k];
+    }
+    unsigned long long inc = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    unsigned long long woff = 0, tot = 0;
+    for (int w = 0; w < kPrefixThreads / 32; ++w) { unsigned long long x = wsum[w]; if (w < warp) woff += x; tot += x; }
+    unsigned long long run = woff + inc - s;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (t0 + k < P.ntiles) P.lbase[t0 + k] = run;
+        run += v[k];
+    }
+    if (tid == 0) P.bsum[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kPrefixThreads) tile_prefix_blocks_kernel(const ScanParams P, unsigned int nblk)
 {
     __shared__ unsigned long long wsum[kPrefixThreads / 32];
     __shared__ unsigned long long carry_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) carry_s = 0;
     __syncthreads();
-    for (unsigned long long t0 = 0; t0 < P.ntiles; t0 += 4ull * kPrefixThreads) {
-        unsigned long long v[4], s = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const unsigned long long ti = t0 + 4ull * tid + k;
-            v[k] = ti < P.ntiles ? (unsigned long long)P.info[ti].total : 0ull;
-            s += v[k];
-        }
-        unsigned long long inc = s;
+    for (unsigned int b0 = 0; b0 < nblk; b0 += kPrefixThreads) {
+        const unsigned int i = b0 + tid;
+        const unsigned long long v = i < nblk ? P.bsum[i] : 0ull;
+        unsigned long long inc = v;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
@@ -556,24 +584,18 @@ __global__ void __launch_bounds__(kPrefixThreads) tile_prefix_kernel(const ScanP
         __syncthreads();
         unsigned long long woff = 0, tot = 0;
         for (int w = 0; w < kPrefixThreads / 32; ++w) { unsigned long long x = wsum[w]; if (w < warp) woff += x; tot += x; }
-        unsigned long long run = carry_s + woff + inc - s;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const unsigned long long ti = t0 + 4ull * tid + k;
-            if (ti < P.ntiles) P.lbase[ti] = run;
-            run += v[k];
-        }
+        if (i < nblk) P.bsum[i] = carry_s + woff + inc - v;
         __syncthreads();
         if (tid == 0) carry_s += tot;
         __syncthreads();
     }
-    if (tid == 0) P.lbase[P.ntiles] = carry_s;
 }
 
-// ---------------------------------------------------------------- kernel 2b: per-tile finalize (one warp per tile)
+// ---------------------------------------------------------------- kernels 2b / 2c: per-tile finalize
 struct TileView {
     const ScanParams &P;
     __device__ TileView(const ScanParams &p) : P(p) {}
+    __device__ unsigned long long lbase(unsigned long long t) const { return P.lbase[t] + P.bsum[t / kPrefixSpan]; }
     __device__ int lines(unsigned long long t) const
     {
         unsigned int n = P.info[t].total;
@@ -597,44 +619,46 @@ struct TileView {
     __device__ long long at(unsigned long long t, int i) const { return i >= 0 ? nl(t, i) : prev_nl(t, -i); }
 };
 
+// 2b: one THREAD per tile -- pick the phase, check the lines that straddle the tile's left edge,
+// turn line hits into record hits.
 __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
 {
-    const int lane = threadIdx.x & 31;
-    const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= P.ntiles) return;
     const TileView V(P);
     const TileInfo ti = P.info[t];
-    const unsigned long long lb = P.lbase[t];
+    const unsigned long long lb = V.lbase(t);
     const unsigned long long base = t * (unsigned long long)kTileBytes;
     const int r = (int)(lb & 3);
     const int n_tab = ti.total < (unsigned int)kMaxTileLines ? (int)ti.total : kMaxTileLines;
-    unsigned int viol = 0;
-    if (lane == 0) {
-        viol = ti.flags >> 8;
-        if ((ti.flags >> r) & 1u) viol |= ti.kinds[r] ? (unsigned int)ti.kinds[r] : (unsigned int)FXG_V_SEQ_CLASS;
-    }
+    unsigned int viol = ti.flags >> 8;
+    if ((ti.flags >> r) & 1u) viol |= ti.kinds[r];
     // structure of the first lines of the tile, whose predecessors lie in earlier tiles
-    if (lane < 3 && lane < n_tab) {
-        const int i = lane;
-        const int ph = (int)((lb + (unsigned long long)i) & 3);
-        const long long pos = V.nl(t, i);
-        if (i == 0) {
-            const long long prev = V.prev_nl(t, 1);
-            const long long llen = pos - prev - 1;
-            if (ph == 0) {
-                if (llen < 1 || P.buf[prev + 1] != '@') viol |= FXG_V_HEADER_AT;
-                else if (P.buf[pos - 1] == ' ') viol |= FXG_V_HEADER_SPACE;
-            } else if (ph == 1) { if (llen < 1) viol |= FXG_V_EMPTY_SEQ; }
-            else if (ph == 2) { if (llen != 1 || P.buf[pos - 1] != '+') viol |= FXG_V_PLUS_LINE; }
-        }
-        if (ph == 3) {
-            const long long llen = pos - V.at(t, i - 1) - 1;
-            const long long slen = V.at(t, i - 2) - V.at(t, i - 3) - 1;
+    if (n_tab > 0) {
+        long long p[6];                          // '\n' positions with local index -3 .. 2
+        p[2] = V.prev_nl(t, 1);
+        const int ph0 = r;
+        const long long pos0 = V.nl(t, 0);
+        const long long llen0 = pos0 - p[2] - 1;
+        if (ph0 == 0) {
+            if (llen0 < 1 || P.buf[p[2] + 1] != '@') viol |= FXG_V_HEADER_AT;
+            else if (P.buf[pos0 - 1] == ' ') viol |= FXG_V_HEADER_SPACE;
+        } else if (ph0 == 1) { if (llen0 < 1) viol |= FXG_V_EMPTY_SEQ; }
+        else if (ph0 == 2) { if (llen0 != 1 || P.buf[pos0 - 1] != '+') viol |= FXG_V_PLUS_LINE; }
+        // the one quality line among local lines 0..2 (if it exists): |qual| == |seq|
+        const int iq = (3 - r) & 3;              // local index of the first line with phase 3
+        if (iq < 3 && iq < n_tab) {
+            p[3] = pos0;
+            if (iq >= 1) p[4] = V.nl(t, 1);
+            if (iq >= 2) p[5] = V.nl(t, 2);
+            if (iq < 2) p[1] = V.prev_nl(t, 2);
+            if (iq < 1) p[0] = V.prev_nl(t, 3);
+            const long long llen = p[3 + iq] - p[2 + iq] - 1;
+            const long long slen = p[1 + iq] - p[iq] - 1;
             if (llen != slen) viol |= FXG_V_QUAL_LEN;
         }
     }
-    viol = __reduce_or_sync(0xffffffffu, viol);
-    if (lane == 0 && viol) { atomicOr(&P.ctr->violation, viol); atomicMin(&P.ctr->first_bad, base); }
+    if (viol) { atomicOr(&P.ctr->violation, viol); atomicMin(&P.ctr->first_bad, base); }
 
     // line hits -> record hits: only lines whose role is the target's count
     if (P.match_enabled) {
@@ -642,7 +666,7 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
         const unsigned int role_mask = 0x11111111u << ((want - r) & 3);     // 32 % 4 == 0: same mask for every word
         const unsigned int *hw = P.tile_hit + t * (unsigned long long)kHitWords;
         unsigned int fresh = 0;
-        for (int w = lane; w * 32 <= n_tab; w += 32) {
+        for (int w = 0; w * 32 <= n_tab; ++w) {
             unsigned int bits = hw[w] & role_mask;
             while (bits) {
                 const int b = __ffs(bits) - 1;
@@ -655,43 +679,50 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
                 }
             }
         }
-        fresh = __reduce_add_sync(0xffffffffu, fresh);
-        if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
+        if (fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
     }
-
-    // record starts / target-field table
-    if (P.rec_start || P.fld_off) {
-        for (int i = lane; i < n_tab; i += 32) {
-            const unsigned long long j = lb + (unsigned long long)i;
-            const int ph = (int)(j & 3);
-            const unsigned long long rec = j >> 2;
-            const long long pos = V.nl(t, i);
-            if (ph == 3 && P.rec_start && rec + 1 <= P.rec_cap) P.rec_start[rec + 1] = (unsigned long long)(pos + 1);
-            if (P.fld_off && rec < P.rec_cap) {
-                if ((ph == 3 && P.target == FXG_TARGET_QUAL) || (ph == 1 && P.target == FXG_TARGET_SEQ)) {
-                    const long long prev = V.at(t, i - 1);
-                    P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
-                } else if (ph == 0 && (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT)) {
-                    const long long prev = V.at(t, i - 1);
-                    long long q = prev + 2, sp = -1;
-                    for (; q < pos; ++q) if (P.buf[q] == ' ') { sp = q; break; }
-                    if (P.target == FXG_TARGET_NAME) {
-                        const long long ne = sp >= 0 ? sp : pos;
-                        P.fld_off[rec] = (unsigned long long)(prev + 2);
-                        P.fld_len[rec] = (unsigned int)(ne > prev + 2 ? ne - (prev + 2) : 0);
-                    } else {
-                        P.fld_off[rec] = (unsigned long long)(sp >= 0 ? sp + 1 : pos);
-                        P.fld_len[rec] = (unsigned int)(sp >= 0 ? pos - (sp + 1) : 0);
-                    }
-                }
-            }
-        }
-        if (t == 0 && lane == 0 && P.rec_start) P.rec_start[0] = 0;
-    }
-    if (t + 1 == P.ntiles && lane == 0) {
+    if (t + 1 == P.ntiles) {
         P.ctr->n_lines = lb + ti.total;
         P.ctr->last_byte = P.buf[P.nbytes - 1];
     }
+}
+
+// 2c: one WARP per tile -- record starts / target-field table (only when records are emitted or a
+// second-stage matcher follows)
+__global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (t >= P.ntiles) return;
+    const TileView V(P);
+    const unsigned long long lb = V.lbase(t);
+    const int n_tab = V.lines(t);
+    for (int i = lane; i < n_tab; i += 32) {
+        const unsigned long long j = lb + (unsigned long long)i;
+        const int ph = (int)(j & 3);
+        const unsigned long long rec = j >> 2;
+        const long long pos = V.nl(t, i);
+        if (ph == 3 && P.rec_start && rec + 1 <= P.rec_cap) P.rec_start[rec + 1] = (unsigned long long)(pos + 1);
+        if (P.fld_off && rec < P.rec_cap) {
+            if ((ph == 3 && P.target == FXG_TARGET_QUAL) || (ph == 1 && P.target == FXG_TARGET_SEQ)) {
+                const long long prev = V.at(t, i - 1);
+                P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
+            } else if (ph == 0 && (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT)) {
+                const long long prev = V.at(t, i - 1);
+                long long q = prev + 2, sp = -1;
+                for (; q < pos; ++q) if (P.buf[q] == ' ') { sp = q; break; }
+                if (P.target == FXG_TARGET_NAME) {
+                    const long long ne = sp >= 0 ? sp : pos;
+                    P.fld_off[rec] = (unsigned long long)(prev + 2);
+                    P.fld_len[rec] = (unsigned int)(ne > prev + 2 ? ne - (prev + 2) : 0);
+                } else {
+                    P.fld_off[rec] = (unsigned long long)(sp >= 0 ? sp + 1 : pos);
+                    P.fld_len[rec] = (unsigned int)(sp >= 0 ? pos - (sp + 1) : 0);
+                }
+            }
+        }
+    }
+    if (t == 0 && lane == 0 && P.rec_start) P.rec_start[0] = 0;
 }
 
 size_t scan_smem_bytes() { return sizeof(ScanSmem); }
@@ -710,10 +741,15 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
     if (P.ntiles == 0) return cudaSuccess;
     scan_tiles_kernel<<<(unsigned int)P.ntiles, kThreads, sizeof(ScanSmem), stream>>>(P);
     if (after_scan) cudaEventRecord(after_scan, stream);
-    tile_prefix_kernel<<<1, kPrefixThreads, 0, stream>>>(P);
-    const unsigned long long warps_per_block = 256 / 32;
-    tile_finalize_kernel<<<(unsigned int)((P.ntiles + warps_per_block - 1) / warps_per_block), 256, 0, stream>>>(P);
-    if (launches) *launches += 3;
+    const unsigned int nblk = (unsigned int)((P.ntiles + kPrefixSpan - 1) / kPrefixSpan);
+    tile_prefix_local_kernel<<<nblk, kPrefixThreads, 0, stream>>>(P);
+    tile_prefix_blocks_kernel<<<1, kPrefixThreads, 0, stream>>>(P, nblk);
+    tile_finalize_kernel<<<(unsigned int)((P.ntiles + 255) / 256), 256, 0, stream>>>(P);
+    if (launches) *launches += 4;
+    if (P.rec_start || P.fld_off) {
+        tile_emit_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
+        if (launches) *launches += 1;
+    }
     return cudaGetLastError();
 }
 
