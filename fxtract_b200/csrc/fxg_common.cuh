@@ -13,9 +13,9 @@ int set_cuda_error(fxg_ctx *ctx, cudaError_t e, const char *what);
 
 // ---------------------------------------------------------------- geometry
 constexpr int kTileBytes = 32768;              // bytes of input one CTA scans
-constexpr int kThreads = 256;                  // threads per CTA (8 warps)
+constexpr int kThreads = 512;                  // threads per CTA (16 warps)
 constexpr int kChunks = kTileBytes / 16;       // 16-byte chunks per tile (2048)
-constexpr int kChunksPerThread = kChunks / kThreads;   // 8
+constexpr int kChunksPerThread = kChunks / kThreads;   // 4
 constexpr int kMaxTileLines = 4096;            // newline-table capacity per tile
 constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
 
@@ -28,8 +28,9 @@ constexpr int kCandCap = 512;                  // literal candidates queued per 
 // converts line hits into record hits / record starts / field tables.
 struct __align__(16) TileInfo {
     unsigned int total;          // bytes < 0x20 in the tile (== '\n' count unless FXG_V_BYTE_RANGE is raised)
-    unsigned int flags;          // [3:0] phase r is illegal; [31:8] phase-independent FXG_V_* bits
-    unsigned short kinds[4];     // FXG_V_* bits per phase (filled for illegal phases only)
+    unsigned int viol;           // phase-independent FXG_V_* bits
+    unsigned short cls[4];       // OR of the line flags of the lines with local index == k (mod 4): low byte = the
+                                 // line itself, high byte = class flags of the head of the following line
 };
 constexpr int kNlStride = kMaxTileLines;           // u16 entries per tile in the global '\n' table
 constexpr int kHitWords = kMaxTileLines / 32 + 1;  // line-hit words per tile (local line indices 0..kMaxTileLines)
@@ -82,6 +83,7 @@ struct ScanParams {
     const uint8_t *pat_bytes;         // device copy of pattern bytes
     int target;
     int match_enabled;                // 0: index/validate only (multi / exact use the field table)
+    int lit_unit;                     // host copy of lit->unit (selects the kernel variant)
     unsigned int one;                 // == 1 (lets the kernel issue adds as IMAD; see fma_add)
     // field table for the second-stage matchers (multi / exact): target field of record k
     unsigned long long *fld_off;      // [rec_cap] or nullptr

@@ -34,13 +34,16 @@
 
 namespace fxg {
 
+constexpr int kWarps = kThreads / 32;
+constexpr int kWarpChunks = kChunks / kWarps;       // chunks one warp covers (contiguous)
+
 struct __align__(128) ScanSmem {
-    uint4 tile[kChunks];                      // staged tile bytes (bulk-copy destination)
+    uint4 tile[2][kChunks];                   // staged tile bytes, double buffered (bulk-copy destinations)
     unsigned char cnt[kChunks];               // bytes < 0x20 per chunk
-    unsigned int pre8[kThreads];              // exclusive prefix of cnt per group of 8 chunks
+    unsigned int pre[kThreads];               // exclusive prefix of cnt per group of kChunksPerThread chunks
     unsigned short nlpos[kMaxTileLines];      // tile-relative '\n' positions, in order
-    unsigned short wl[kThreads / 32][kChunks / 8];   // per warp: its chunks that contain a byte < 0x20, in order
-    unsigned int wcnt[kThreads / 32];         // entries in wl[w]
+    unsigned short wl[kWarps][kWarpChunks];   // per warp: its chunks that contain a byte < 0x20
+    unsigned int wcnt[kWarps];                // entries in wl[w]
     unsigned int below[17];                   // interleaved-layout mask of the bytes < p of a chunk
     unsigned int sbits[kChunks / 32];         // bit c: chunk c has a byte < 0x41 (not a sequence letter)
     unsigned int qbits[kChunks / 32];         // bit c: chunk c has a byte < 0x21 (not a quality char)
@@ -50,9 +53,9 @@ struct __align__(128) ScanSmem {
     unsigned short lit_masks[64];
     int cand_off[kCandCap];                   // tile-relative offset of a candidate unit
     unsigned short cand_mask[kCandCap];       // (pattern,shift) bits to verify
-    unsigned int warp_sums[kThreads / 32];
-    unsigned long long mbar;                  // bulk-copy completion barrier
-    unsigned int kinds[4];                    // FXG_V_* bits per illegal phase (slow path)
+    unsigned int warp_sums[kWarps];
+    unsigned long long mbar[2];               // bulk-copy completion barriers
+    unsigned int cls[4];                      // line flags OR-ed per (local line index mod 4)
     unsigned int n_cand, viol, total, any_hit;
 };
 
@@ -137,21 +140,20 @@ __device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int ad
 __device__ __forceinline__ void note_violation(ScanSmem &S, unsigned int bit) { atomicOr(&S.viol, bit); }
 
 // byte of the batch at global offset g: from the staged tile when inside it
-__device__ __forceinline__ unsigned int text_byte(const ScanSmem &S, const ScanParams &P,
+__device__ __forceinline__ unsigned int text_byte(const unsigned char *tb, const ScanParams &P,
                                                   unsigned long long base, long long g)
 {
     long long rel = g - (long long)base;
-    if (rel >= 0 && rel < kTileBytes) return reinterpret_cast<const unsigned char *>(S.tile)[rel];
+    if (rel >= 0 && rel < kTileBytes) return tb[rel];
     return P.buf[g];
 }
 
 // '\n' count in tile bytes [0, rel)
-__device__ __forceinline__ unsigned int lines_before(const ScanSmem &S, int rel)
+__device__ __forceinline__ unsigned int lines_before(const ScanSmem &S, const unsigned char *tb, int rel)
 {
     int c = rel >> 4;
-    unsigned int n = S.pre8[c >> 3];
-    for (int q = (c & ~7); q < c; ++q) n += S.cnt[q];
-    const unsigned char *tb = reinterpret_cast<const unsigned char *>(S.tile);
+    unsigned int n = S.pre[c / kChunksPerThread];
+    for (int q = c - c % kChunksPerThread; q < c; ++q) n += S.cnt[q];
     for (int b = c << 4; b < rel; ++b) n += (tb[b] < 0x20);
     return n;
 }
@@ -180,15 +182,15 @@ constexpr unsigned int kFA = 1, kFB = 2, kFC = 4, kFD = 8, kFS = 16, kFQ = 32, k
 //  kFD  length differs from the line two above                  (FXG_V_QUAL_LEN)
 //  kFS  has a byte outside [0x41,0x7e]                          (FXG_V_SEQ_CLASS)
 //  kFQ  has a byte outside [0x21,0x7e]                          (FXG_V_QUAL_CLASS)
-__device__ __forceinline__ void line_flags(const ScanSmem &S, int i, int n_tab, unsigned int &own, unsigned int &nxt,
-                                           unsigned int &tail)
+__device__ __forceinline__ void line_flags(const ScanSmem &S, const uint4 *tile, int i, int n_tab, unsigned int &own,
+                                           unsigned int &nxt)
 {
-    const unsigned char *tb = reinterpret_cast<const unsigned char *>(S.tile);
+    const unsigned char *tb = reinterpret_cast<const unsigned char *>(tile);
     const int pos = S.nlpos[i];
     const int prev = i > 0 ? (int)S.nlpos[i - 1] : -1;
     const int next = i + 1 < n_tab ? (int)S.nlpos[i + 1] : kTileBytes;
     const int c = pos >> 4, cb = c << 4, cp = prev >> 4;
-    const uint4 x = S.tile[c];
+    const uint4 x = tile[c];
     const unsigned int s16 = il_mask(x, kAdd41), q16 = il_mask(x, kAdd21);
     const int pb = pos - cb;
     const int lo = prev + 1 > cb ? prev + 1 - cb : 0;
@@ -199,11 +201,6 @@ __device__ __forceinline__ void line_flags(const ScanSmem &S, int i, int n_tab, 
     range_any2(S, cp + 1, c, ms, mq);
     own = (((s16 & r_tail) | ms) ? kFS : 0u) | (((q16 & r_tail) | mq) ? kFQ : 0u);
     nxt = ((s16 & r_head) ? kFS : 0u) | ((q16 & r_head) ? kFQ : 0u);
-    tail = 0;
-    if (i == n_tab - 1) {                      // bytes after the last '\n': an unterminated line of index n_tab
-        range_any2(S, c + 1, kChunks, ms, mq);
-        tail = (ms ? kFS : 0u) | (mq ? kFQ : 0u);
-    }
     if (i >= 1) {                              // line starts inside the tile: structure is local
         const int llen = pos - prev - 1;
         const unsigned int fb = tb[prev + 1], lb = tb[pos - 1];
@@ -218,7 +215,7 @@ __device__ __forceinline__ void line_flags(const ScanSmem &S, int i, int n_tab, 
 }
 
 // FXG_V_* bits of a line with flags f if its role is `role` (0 header, 1 sequence, 2 plus, 3 quality)
-__device__ __forceinline__ unsigned int role_kinds(unsigned int f, int role)
+__host__ __device__ inline unsigned int role_kinds(unsigned int f, int role)
 {
     if (role == 0) return ((f & kFA) ? FXG_V_HEADER_AT : 0u) | ((f & kFSP) ? FXG_V_HEADER_SPACE : 0u);
     if (role == 1) return ((f & kFB) ? FXG_V_EMPTY_SEQ : 0u) | ((f & kFS) ? FXG_V_SEQ_CLASS : 0u);
@@ -230,8 +227,8 @@ __device__ __forceinline__ unsigned int role_kinds(unsigned int f, int role)
 // A verified occurrence is recorded on its local line; whether that line has the target's
 // role (sequence / quality / header) is decided by tile_finalize_kernel.  Header targets add
 // the geometric condition (inside the name / inside the comment), which is phase-free.
-__device__ __noinline__ void verify_candidate(ScanSmem &S, const ScanParams &P, unsigned long long base, int n_tab,
-                                              int unit_rel, unsigned int bits)
+__device__ __noinline__ void verify_candidate(ScanSmem &S, const unsigned char *tb, const ScanParams &P,
+                                              unsigned long long base, int n_tab, int unit_rel, unsigned int bits)
 {
     const LiteralTable *lit = P.lit;
     while (bits) {
@@ -244,13 +241,13 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, const ScanParams &P, 
         const uint8_t *pb = P.pat_bytes + lit->pat_off[pat];
         bool ok = true;
         for (int k = 0; k < len; ++k) {
-            if (text_byte(S, P, base, p + k) != pb[k]) { ok = false; break; }
+            if (text_byte(tb, P, base, p + k) != pb[k]) { ok = false; break; }
         }
         if (!ok) continue;
         // local line: number of '\n' before p inside the tile (an occurrence that starts in the
         // previous tile lies on this tile's line 0)
         int rel = (int)(p - (long long)base);
-        unsigned int loc = rel > 0 ? lines_before(S, rel) : 0u;
+        unsigned int loc = rel > 0 ? lines_before(S, tb, rel) : 0u;
         if (loc > (unsigned int)kMaxTileLines) continue;       // tile is flagged FXG_V_DENSE_LINES anyway
         bool hit = true;
         if (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT) {
@@ -267,7 +264,7 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, const ScanParams &P, 
             long long q = ls + 1, sp = -1;
             for (;; ++q) {
                 if ((unsigned long long)q >= P.nbytes) break;
-                unsigned int ch = text_byte(S, P, base, q);
+                unsigned int ch = text_byte(tb, P, base, q);
                 if (ch == '\n') break;
                 if (ch == ' ') { sp = q; break; }
             }
@@ -302,229 +299,252 @@ __device__ __noinline__ void filter_small_units(ScanSmem &S, unsigned int x0, un
 }
 
 // ---------------------------------------------------------------- kernel 1: per-tile scan
-__global__ void __launch_bounds__(kThreads, 4) scan_tiles_kernel(const ScanParams P)
+// Persistent CTAs (2 per SM, 16 warps each): tile t = blockIdx.x, += gridDim.x.  The next tile
+// is prefetched into the other shared-memory buffer while the current one is processed.
+// LM = literal filter mode: 0 none (multi / exact strategies), 8 = aligned 8-byte units with the
+// fingerprint table, 1 = short patterns (units of 4 / 2 / 1 bytes).
+template <int LM>
+__global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParams P)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem &S = *reinterpret_cast<ScanSmem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LiteralTable *lit = P.lit;
-    const unsigned long long t = blockIdx.x;
-    const unsigned long long base = t * (unsigned long long)kTileBytes;
-    const unsigned long long remain = P.nbytes - base;
-    const int tile_len = remain < (unsigned long long)kTileBytes ? (int)remain : kTileBytes;
-    const int bulk = tile_len & ~15;
-    unsigned char *tb = reinterpret_cast<unsigned char *>(S.tile);
 
-    // ---- stage the tile: one bulk async copy; the ragged end of the batch is patched by hand
+    // ---- once per CTA: tables, barriers, first tile in flight
     if (tid == 0) {
-        S.n_cand = 0; S.viol = 0; S.any_hit = 0;
-        S.kinds[0] = S.kinds[1] = S.kinds[2] = S.kinds[3] = 0;
-        mbar_init(&S.mbar, 1);
-        if (bulk) {
-            mbar_expect_tx(&S.mbar, (unsigned int)bulk);
-            bulk_g2s(S.tile, P.buf + base, (unsigned int)bulk, &S.mbar);
+        mbar_init(&S.mbar[0], 1);
+        mbar_init(&S.mbar[1], 1);
+        const unsigned long long t0 = blockIdx.x;
+        const unsigned long long rem0 = P.nbytes - t0 * (unsigned long long)kTileBytes;
+        const unsigned int bulk0 = (unsigned int)(rem0 < (unsigned long long)kTileBytes ? rem0 : (unsigned long long)kTileBytes) & ~15u;
+        if (bulk0) {
+            mbar_expect_tx(&S.mbar[0], bulk0);
+            bulk_g2s(S.tile[0], P.buf + t0 * (unsigned long long)kTileBytes, bulk0, &S.mbar[0]);
         }
     }
     if (tid >= 128 && tid < 145) S.below[tid - 128] = kBelowTab[tid - 128];
     int lit_unit = 0, lit_nkeys = 0;
     unsigned int lit_mul1 = 0, lit_mul2 = 0;
-    if (P.match_enabled) {
+    if (LM != 0) {
         lit_unit = lit->unit; lit_nkeys = lit->n_keys; lit_mul1 = lit->mul1; lit_mul2 = lit->mul2;
         if (tid >= 64 && tid < 128) {
             const int k = tid - 64;
             S.lit_keys[k] = lit->keys[k]; S.lit_fp[k] = lit->fp[k]; S.lit_masks[k] = lit->masks[k];
         }
-        for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
     }
-    if (tile_len < kTileBytes) {
-        for (int b = bulk + tid * 16; b < kTileBytes; b += kThreads * 16) {
-            unsigned int w[4] = {0x78787878u, 0x78787878u, 0x78787878u, 0x78787878u};   // neutral filler
-            for (int k = 0; k < 16 && b + k < tile_len; ++k) {
-                unsigned int by = P.buf[base + b + k];
-                w[k >> 2] = (w[k >> 2] & ~(0xffu << ((k & 3) * 8))) | (by << ((k & 3) * 8));
-            }
-            S.tile[b >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
-        }
-    }
-    __syncthreads();                 // mbarrier initialised, tables staged
-    if (bulk) mbar_wait(&S.mbar, 0);
+    const unsigned int one = P.one;
+    const unsigned int lt_mask = (1u << lane) - 1u;
 
-    // ---- 1. main pass: 16 bytes per lane per step
-    {
-        const unsigned int one = P.one;
-        const unsigned int lt_mask = (1u << lane) - 1u;
-        unsigned int hi_acc = 0, wcount = 0;
-        unsigned short *my_list = S.wl[warp];
+    unsigned int it = 0;
+    for (unsigned long long t = blockIdx.x; t < P.ntiles; t += gridDim.x, ++it) {
+        const int cur = (int)(it & 1u);
+        const uint4 *tile = S.tile[cur];
+        const unsigned char *tb = reinterpret_cast<const unsigned char *>(tile);
+        const unsigned long long base = t * (unsigned long long)kTileBytes;
+        const unsigned long long remain = P.nbytes - base;
+        const int tile_len = remain < (unsigned long long)kTileBytes ? (int)remain : kTileBytes;
+        const int bulk = tile_len & ~15;
+
+        // ---- prefetch the next tile of this CTA into the other buffer (free since the end of the
+        //      previous iteration); per-tile state
+        if (tid == 0) {
+            const unsigned long long tn = t + gridDim.x;
+            if (tn < P.ntiles) {
+                const unsigned long long remn = P.nbytes - tn * (unsigned long long)kTileBytes;
+                const unsigned int bulkn = (unsigned int)(remn < (unsigned long long)kTileBytes ? remn : (unsigned long long)kTileBytes) & ~15u;
+                if (bulkn) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_expect_tx(&S.mbar[cur ^ 1], bulkn);
+                    bulk_g2s(S.tile[cur ^ 1], P.buf + tn * (unsigned long long)kTileBytes, bulkn, &S.mbar[cur ^ 1]);
+                }
+            }
+            S.n_cand = 0; S.viol = 0; S.any_hit = 0;
+            S.cls[0] = S.cls[1] = S.cls[2] = S.cls[3] = 0;
+        }
+        if (LM != 0) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
+        if (tile_len < kTileBytes) {             // ragged end of the batch: patch by hand, neutral filler
+            for (int b = bulk + tid * 16; b < kTileBytes; b += kThreads * 16) {
+                unsigned int w[4] = {0x78787878u, 0x78787878u, 0x78787878u, 0x78787878u};
+                for (int k = 0; k < 16 && b + k < tile_len; ++k) {
+                    unsigned int by = P.buf[base + b + k];
+                    w[k >> 2] = (w[k >> 2] & ~(0xffu << ((k & 3) * 8))) | (by << ((k & 3) * 8));
+                }
+                S.tile[cur][b >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
+        __syncthreads();
+        if (bulk) mbar_wait(&S.mbar[cur], (it >> 1) & 1u);
+
+        // ---- 1. main pass: 16 bytes per lane per step
+        {
+            unsigned int hi_acc = 0, wcount = 0;
+            unsigned short *my_list = S.wl[warp];
 #pragma unroll
-        for (int j = 0; j < kChunksPerThread; ++j) {
-            const int c = warp * (kChunks / 8) + j * 32 + lane;
-            const uint4 x = S.tile[c];
-            // bytes >= 0x7f anywhere
-            hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);
-            hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
-            hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
-            hi_acc |= x.w | fma_add(x.w, one, 0x01010101u);
-            // bytes < 0x20: count (dp4a over the isolated bit-7 flags = 128 * count)
-            unsigned int n = __dp4a(~fma_add(x.x, one, kAdd20) & kHi, 0x01010101u, 0u);
-            n = __dp4a(~fma_add(x.y, one, kAdd20) & kHi, 0x01010101u, n);
-            n = __dp4a(~fma_add(x.z, one, kAdd20) & kHi, 0x01010101u, n);
-            n = __dp4a(~fma_add(x.w, one, kAdd20) & kHi, 0x01010101u, n);
-            n >>= 7;
-            const bool s_any = ((fma_add(x.x, one, kAdd41) & fma_add(x.y, one, kAdd41) & fma_add(x.z, one, kAdd41) &
-                                 fma_add(x.w, one, kAdd41)) & kHi) != kHi;
-            const bool q_any = ((fma_add(x.x, one, kAdd21) & fma_add(x.y, one, kAdd21) & fma_add(x.z, one, kAdd21) &
-                                 fma_add(x.w, one, kAdd21)) & kHi) != kHi;
-            const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
-            const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
-            const unsigned int nb = __ballot_sync(0xffffffffu, n != 0);
-            S.cnt[c] = (unsigned char)n;
-            S.sbits[c >> 5] = sb;                     // same word, same value from every lane
-            S.qbits[c >> 5] = qb;
-            if (n) my_list[wcount + __popc(nb & lt_mask)] = (unsigned short)c;
-            wcount += __popc(nb);
-            if (P.match_enabled) {
-                if (lit_unit == 8) {
+            for (int j = 0; j < kChunksPerThread; ++j) {
+                const int c = warp * kWarpChunks + j * 32 + lane;
+                const uint4 x = tile[c];
+                // bytes >= 0x7f anywhere
+                hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);
+                hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
+                hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
+                hi_acc |= x.w | fma_add(x.w, one, 0x01010101u);
+                // bytes < 0x20: count (dp4a over the isolated bit-7 flags = 128 * count)
+                unsigned int n = __dp4a(~fma_add(x.x, one, kAdd20) & kHi, 0x01010101u, 0u);
+                n = __dp4a(~fma_add(x.y, one, kAdd20) & kHi, 0x01010101u, n);
+                n = __dp4a(~fma_add(x.z, one, kAdd20) & kHi, 0x01010101u, n);
+                n = __dp4a(~fma_add(x.w, one, kAdd20) & kHi, 0x01010101u, n);
+                n >>= 7;
+                const bool s_any = ((fma_add(x.x, one, kAdd41) & fma_add(x.y, one, kAdd41) & fma_add(x.z, one, kAdd41) &
+                                     fma_add(x.w, one, kAdd41)) & kHi) != kHi;
+                const bool q_any = ((fma_add(x.x, one, kAdd21) & fma_add(x.y, one, kAdd21) & fma_add(x.z, one, kAdd21) &
+                                     fma_add(x.w, one, kAdd21)) & kHi) != kHi;
+                const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
+                const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
+                const unsigned int nb = __ballot_sync(0xffffffffu, n != 0);
+                S.cnt[c] = (unsigned char)n;
+                S.sbits[c >> 5] = sb;                     // same word, same value from every lane
+                S.qbits[c >> 5] = qb;
+                if (n) my_list[wcount + __popc(nb & lt_mask)] = (unsigned short)c;
+                wcount += __popc(nb);
+                if (LM == 8) {
                     const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
                     const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
-                    if (S.lit_fp[r0 >> 26] == r0) push_candidate(S, c << 4, S.lit_masks[r0 >> 26]);
-                    if (S.lit_fp[r1 >> 26] == r1) push_candidate(S, (c << 4) + 8, S.lit_masks[r1 >> 26]);
-                } else if ((c << 4) < tile_len) {
-                    filter_small_units(S, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
+                    const bool c0 = S.lit_fp[r0 >> 26] == r0, c1 = S.lit_fp[r1 >> 26] == r1;
+                    if (__any_sync(0xffffffffu, c0 || c1)) {          // rare: keep the hot loop branch-free
+                        if (c0) push_candidate(S, c << 4, S.lit_masks[r0 >> 26]);
+                        if (c1) push_candidate(S, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                    }
+                } else if (LM == 1) {
+                    if ((c << 4) < tile_len) filter_small_units(S, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
+                }
+            }
+            if (lane == 0) S.wcnt[warp] = wcount;
+            if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(S, FXG_V_BYTE_RANGE);
+        }
+        __syncthreads();
+
+        // ---- 2. block scan of per-chunk counts (kChunksPerThread consecutive chunks per thread)
+        {
+            const unsigned int w4 = *reinterpret_cast<const unsigned int *>(&S.cnt[tid * kChunksPerThread]);
+            const unsigned int s = __dp4a(w4, 0x01010101u, 0u);
+            unsigned int inc = s;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            if (lane == 31) S.warp_sums[warp] = inc;
+            __syncthreads();
+            unsigned int woff = 0, tot = 0;
+#pragma unroll
+            for (int w2 = 0; w2 < kWarps; ++w2) {
+                unsigned int ws = S.warp_sums[w2];
+                if (w2 < warp) woff += ws;
+                tot += ws;
+            }
+            S.pre[tid] = woff + inc - s;
+            if (tid == 0) S.total = tot;
+        }
+        __syncthreads();
+        const unsigned int total = S.total;
+        const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
+        if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(S, FXG_V_DENSE_LINES);
+
+        //      ordered '\n' position table: every warp walks its own list of flagged chunks
+        {
+            const unsigned int nn = S.wcnt[warp];
+            const unsigned short *my_list = S.wl[warp];
+            for (unsigned int q = lane; q < nn; q += 32) {
+                const int c = my_list[q];
+                unsigned int m16 = lin_mask(tile[c], kAdd20);
+                const unsigned int w4 = *reinterpret_cast<const unsigned int *>(&S.cnt[c & ~3]);
+                const int sh = (c & 3) * 8;
+                unsigned int idx = S.pre[c >> 2] + __dp4a(w4 & ((1u << sh) - 1u), 0x01010101u, 0u);
+                while (m16) {
+                    const int p = (c << 4) + __ffs(m16) - 1;
+                    m16 &= m16 - 1;
+                    if (tb[p] != '\n') note_violation(S, FXG_V_BYTE_RANGE);
+                    if (idx < (unsigned int)kMaxTileLines) S.nlpos[idx] = (unsigned short)p;
+                    ++idx;
                 }
             }
         }
-        if (lane == 0) S.wcnt[warp] = wcount;
-        if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(S, FXG_V_BYTE_RANGE);
-    }
-    __syncthreads();
-
-    // ---- 2. block scan of per-chunk counts (8 consecutive chunks per thread)
-    {
-        uint2 w = *reinterpret_cast<const uint2 *>(&S.cnt[tid * 8]);
-        unsigned int s = __dp4a(w.x, 0x01010101u, 0u) + __dp4a(w.y, 0x01010101u, 0u);
-        unsigned int inc = s;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += o;
-        }
-        if (lane == 31) S.warp_sums[warp] = inc;
         __syncthreads();
-        unsigned int woff = 0, tot = 0;
-#pragma unroll
-        for (int w2 = 0; w2 < kThreads / 32; ++w2) {
-            unsigned int ws = S.warp_sums[w2];
-            if (w2 < warp) woff += ws;
-            tot += ws;
-        }
-        S.pre8[tid] = woff + inc - s;
-        if (tid == 0) S.total = tot;
-    }
-    __syncthreads();
-    const unsigned int total = S.total;
-    const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
-    if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(S, FXG_V_DENSE_LINES);
 
-    //      ordered '\n' position table: every warp walks its own list of flagged chunks
-    {
-        const unsigned int nn = S.wcnt[warp];
-        const unsigned short *my_list = S.wl[warp];
-        for (unsigned int q = lane; q < nn; q += 32) {
-            const int c = my_list[q];
-            unsigned int m16 = lin_mask(S.tile[c], kAdd20);
-            uint2 w = *reinterpret_cast<const uint2 *>(&S.cnt[c & ~7]);
-            const int sh = (c & 7) * 8;
-            const unsigned long long keep = sh ? ((1ull << sh) - 1ull) : 0ull;
-            unsigned int idx = S.pre8[c >> 3] + __dp4a(w.x & (unsigned int)keep, 0x01010101u, 0u) +
-                               __dp4a(w.y & (unsigned int)(keep >> 32), 0x01010101u, 0u);
-            while (m16) {
-                const int p = (c << 4) + __ffs(m16) - 1;
-                m16 &= m16 - 1;
-                if (tb[p] != '\n') note_violation(S, FXG_V_BYTE_RANGE);
-                if (idx < (unsigned int)kMaxTileLines) S.nlpos[idx] = (unsigned short)p;
-                ++idx;
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- 3. one thread per line, all four phase hypotheses at once.  The stride (256) is a
-    //         multiple of 4, so every line of a thread has the same index mod 4: the flags of a
-    //         thread's lines are OR-ed and mapped to the four phases once, after the loop.
-    //         (A canonical tile is illegal under three of the four phases; only the phase that
-    //         tile_finalize_kernel selects matters.)
-    {
-        unsigned int f_own = 0, f_nxt = 0;
-        if (n_tab == 0) {
-            if (tid == 0) {
-                unsigned int ms, mq;
-                range_any2(S, 0, kChunks, ms, mq);
-                f_own = (ms ? kFS : 0u) | (mq ? kFQ : 0u);
-            }
-        } else {
+        // ---- 3. one thread per line.  FASTQ line phase is unknown here, so the flags of the lines
+        //         are OR-ed per (local line index mod 4); tile_finalize_kernel maps them to roles once
+        //         the phase is known.  The stride (512) is a multiple of 4: one class per thread.
+        {
+            unsigned int f_own = 0, f_nxt = 0;
             for (int i = tid; i < n_tab; i += kThreads) {
-                unsigned int own, nxt, tail;
-                line_flags(S, i, n_tab, own, nxt, tail);
+                unsigned int own, nxt;
+                line_flags(S, tile, i, n_tab, own, nxt);
                 f_own |= own;
-                f_nxt |= nxt | tail;
+                f_nxt |= nxt;
+            }
+            unsigned int v = f_own | (f_nxt << 8);
+            v = __reduce_or_sync(0x11111111u << (lane & 3), v);
+            if (lane < 4 && v) atomicOr(&S.cls[lane], v);
+            if (tid == kThreads - 1) {           // bytes after the last '\n': an unterminated line of index n_tab
+                unsigned int ms, mq;
+                range_any2(S, n_tab ? (S.nlpos[n_tab - 1] >> 4) + 1 : 0, kChunks, ms, mq);
+                const unsigned int f = (ms ? kFS : 0u) | (mq ? kFQ : 0u);
+                if (f) atomicOr(&S.cls[n_tab & 3], f);
             }
         }
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            unsigned int k = role_kinds(f_own, (tid + r) & 3) | role_kinds(f_nxt, (tid + 1 + r) & 3);
-            k = __reduce_or_sync(0xffffffffu, k);
-            if (lane == 0 && k) atomicOr(&S.kinds[r], k);
-        }
-    }
 
-    // ---- 4. verify the literal candidates (phase-free; line hits)
-    if (P.match_enabled) {
-        const unsigned int nc_all = S.n_cand;
-        if (nc_all <= (unsigned int)kCandCap) {
-            for (unsigned int q = tid; q < nc_all; q += kThreads) verify_candidate(S, P, base, n_tab, S.cand_off[q], S.cand_mask[q]);
-        } else {
-            // queue overflow (pattern hits nearly everywhere): rescan the tile and verify in place
-            for (int c = tid; c < kChunks && (c << 4) < tile_len; c += kThreads) {
-                const uint4 x = S.tile[c];
-                if (lit_unit == 8) {
-                    const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
-                    const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
-                    if (S.lit_fp[r0 >> 26] == r0) verify_candidate(S, P, base, n_tab, c << 4, S.lit_masks[r0 >> 26]);
-                    if (S.lit_fp[r1 >> 26] == r1) verify_candidate(S, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> 26]);
-                } else {
-                    const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
-                    for (int u = 0; u < 16; u += lit_unit) {
-                        unsigned int word = wv[u >> 2];
-                        unsigned int val = lit_unit == 4 ? word : (lit_unit == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu)
-                                                                                 : ((word >> ((u & 3) * 8)) & 0xffu));
-                        for (int k = 0; k < lit_nkeys; ++k)
-                            if ((unsigned int)S.lit_keys[k] == val) verify_candidate(S, P, base, n_tab, (c << 4) + u, S.lit_masks[k]);
+        // ---- 4. verify the literal candidates (phase-free; line hits)
+        if (LM != 0) {
+            const unsigned int nc_all = S.n_cand;
+            if (nc_all <= (unsigned int)kCandCap) {
+                for (unsigned int q = tid; q < nc_all; q += kThreads)
+                    verify_candidate(S, tb, P, base, n_tab, S.cand_off[q], S.cand_mask[q]);
+            } else {
+                // queue overflow (pattern hits nearly everywhere): rescan the tile and verify in place
+                for (int c = tid; c < kChunks && (c << 4) < tile_len; c += kThreads) {
+                    const uint4 x = tile[c];
+                    if (LM == 8) {
+                        const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
+                        const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
+                        if (S.lit_fp[r0 >> 26] == r0) verify_candidate(S, tb, P, base, n_tab, c << 4, S.lit_masks[r0 >> 26]);
+                        if (S.lit_fp[r1 >> 26] == r1) verify_candidate(S, tb, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                    } else {
+                        const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
+                        for (int u = 0; u < 16; u += lit_unit) {
+                            unsigned int word = wv[u >> 2];
+                            unsigned int val = lit_unit == 4 ? word : (lit_unit == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu)
+                                                                                     : ((word >> ((u & 3) * 8)) & 0xffu));
+                            for (int k = 0; k < lit_nkeys; ++k)
+                                if ((unsigned int)S.lit_keys[k] == val)
+                                    verify_candidate(S, tb, P, base, n_tab, (c << 4) + u, S.lit_masks[k]);
+                        }
                     }
                 }
             }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // ---- 5. publish the tile: count, per-phase violations, '\n' table, line hits
-    {
-        uint4 *dst = reinterpret_cast<uint4 *>(P.tile_nl + t * (unsigned long long)kNlStride);
-        const uint4 *src = reinterpret_cast<const uint4 *>(S.nlpos);
-        for (int q = tid; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
-        if (P.match_enabled) {
-            unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
-            const int nw = (n_tab >> 5) + 1;               // local line indices 0..n_tab
-            if (tid < nw) hd[tid] = S.any_hit ? S.linehit[tid] : 0u;
+        // ---- 5. publish the tile: count, line-class flags, '\n' table, line hits
+        {
+            uint4 *dst = reinterpret_cast<uint4 *>(P.tile_nl + t * (unsigned long long)kNlStride);
+            const uint4 *src = reinterpret_cast<const uint4 *>(S.nlpos);
+            for (int q = tid; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
+            if (LM != 0) {
+                unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
+                const int nw = (n_tab >> 5) + 1;               // local line indices 0..n_tab
+                if (tid < nw) hd[tid] = S.any_hit ? S.linehit[tid] : 0u;
+            }
+            if (tid == 0) {
+                TileInfo ti;
+                ti.total = total;
+                ti.viol = S.viol;
+                ti.cls[0] = (unsigned short)S.cls[0]; ti.cls[1] = (unsigned short)S.cls[1];
+                ti.cls[2] = (unsigned short)S.cls[2]; ti.cls[3] = (unsigned short)S.cls[3];
+                P.info[t] = ti;
+            }
         }
-        if (tid == 0) {
-            TileInfo ti;
-            ti.total = total;
-            ti.flags = (S.kinds[0] ? 1u : 0u) | (S.kinds[1] ? 2u : 0u) | (S.kinds[2] ? 4u : 0u) | (S.kinds[3] ? 8u : 0u) |
-                       (S.viol << 8);
-            ti.kinds[0] = (unsigned short)S.kinds[0]; ti.kinds[1] = (unsigned short)S.kinds[1];
-            ti.kinds[2] = (unsigned short)S.kinds[2]; ti.kinds[3] = (unsigned short)S.kinds[3];
-            P.info[t] = ti;
-        }
+        __syncthreads();                         // everything of this tile is consumed: buffers may be reused
     }
 }
 
@@ -631,8 +651,10 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
     const unsigned long long base = t * (unsigned long long)kTileBytes;
     const int r = (int)(lb & 3);
     const int n_tab = ti.total < (unsigned int)kMaxTileLines ? (int)ti.total : kMaxTileLines;
-    unsigned int viol = ti.flags >> 8;
-    if ((ti.flags >> r) & 1u) viol |= ti.kinds[r];
+    unsigned int viol = ti.viol;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)                  // lines with local index == k (mod 4) have role (k + r) & 3
+        viol |= role_kinds(ti.cls[k] & 0x7fu, (k + r) & 3) | role_kinds(ti.cls[k] >> 8, (k + 1 + r) & 3);
     // structure of the first lines of the tile, whose predecessors lie in earlier tiles
     if (n_tab > 0) {
         long long p[6];                          // '\n' positions with local index -3 .. 2
@@ -727,19 +749,37 @@ __global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
 
 size_t scan_smem_bytes() { return sizeof(ScanSmem); }
 
-cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launches, cudaEvent_t after_scan)
+template <int LM> static cudaError_t launch_scan_tiles(const ScanParams &P, cudaStream_t stream, int dev)
 {
     static bool attr_set[64] = {false};
+    static int grid_cap[64] = {0};
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(scan_tiles_kernel<LM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
+        if (e != cudaSuccess) return e;
+        int sms = 0, per_sm = 0;
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_tiles_kernel<LM>, kThreads, sizeof(ScanSmem))) != cudaSuccess) return e;
+        if (per_sm < 1) per_sm = 1;
+        grid_cap[dev] = sms * per_sm;            // persistent CTAs: one wave, 148 SMs x 2 on B200
+        attr_set[dev] = true;
+    }
+    const unsigned long long grid = P.ntiles < (unsigned long long)grid_cap[dev] ? P.ntiles : (unsigned long long)grid_cap[dev];
+    scan_tiles_kernel<LM><<<(unsigned int)grid, kThreads, sizeof(ScanSmem), stream>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launches, cudaEvent_t after_scan)
+{
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(scan_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
-        if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
     if (((uintptr_t)P.buf & 15) != 0) return cudaErrorMisalignedAddress;     // bulk copies need 16-byte alignment
     if (P.ntiles == 0) return cudaSuccess;
-    scan_tiles_kernel<<<(unsigned int)P.ntiles, kThreads, sizeof(ScanSmem), stream>>>(P);
+    cudaError_t e;
+    if (!P.match_enabled) e = launch_scan_tiles<0>(P, stream, dev);
+    else if (P.lit_unit == 8) e = launch_scan_tiles<8>(P, stream, dev);
+    else e = launch_scan_tiles<1>(P, stream, dev);
+    if (e != cudaSuccess) return e;
     if (after_scan) cudaEventRecord(after_scan, stream);
     const unsigned int nblk = (unsigned int)((P.ntiles + kPrefixSpan - 1) / kPrefixSpan);
     tile_prefix_local_kernel<<<nblk, kPrefixThreads, 0, stream>>>(P);
