@@ -1,0 +1,373 @@
+// strategies.cpp -- the three literal strategies of the reference (main.cpp:306-349 hash_search,
+// :351-452 multipattern_search, :596-652 simple_string_search) with every matcher on the GPU.
+//
+// Two front-ends feed the same device matchers:
+//   raw path    -- canonical uncompressed single-end FASTQ: raw bytes go to the GPU, which finds
+//                  record boundaries, validates, matches and returns the selected byte runs; the
+//                  host writes those runs from its own pinned copy.  A batch the GPU predicate
+//                  rejects is re-routed, from its first byte, to the
+//   fields path -- host reader with kseq semantics -> target fields packed into the pinned
+//                  buffer -> per-field flags (+ first-hit pattern ids) -> per-strategy pair rules,
+//                  printing and routing on the host exactly as the reference does.
+// The POSIX-regex strategies (main.cpp:462-514) are outside the graft and stay on the CPU.
+#include "fxhost.h"
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <fcntl.h>
+#include <memory>
+#include <regex.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#ifndef REG_BASIC
+#define REG_BASIC 0
+#endif
+
+namespace fxh {
+
+namespace {
+
+enum Strategy { S_LITERAL, S_MULTI, S_EXACT };
+
+struct Stats {
+    uint64_t raw_bytes = 0, raw_batches = 0, field_bytes = 0, field_batches = 0, records = 0, rerouted = 0;
+};
+
+// main.cpp:291-304 prepare_data; the multi-pattern twin (main.cpp:389-405, :410-425) differs for -Q
+void target_slice(const CliOptions &o, Strategy st, const PairBatch &b, const RecView &r, bool second,
+                  const char *&p, uint32_t &n)
+{
+    Field f;
+    bool none = false;
+    if (o.H) f = F_NAME;
+    else if (o.Q) {
+        if (st == S_MULTI) {
+            if (r.is_fasta()) none = true;            // reference leaves `data` untouched (UB / stale): nothing to match
+            f = second ? F_SEQ : F_QUAL;              // main.cpp:416 scans read 2's *sequence* under -Q
+        } else f = r.is_fasta() ? F_SEQ : F_QUAL;
+    } else if (o.C) f = F_COMMENT;
+    else f = F_SEQ;
+    p = b.arena.data() + r.off[f];
+    n = none ? 0 : r.len[f];
+    if (st == S_MULTI && o.Q && !none) n = r.len[F_SEQ];     // data.len = pair.X.length()
+    if (st == S_LITERAL) n = (uint32_t)strnlen(p, n);        // strstr works on c_str()
+}
+
+int fxg_target(const CliOptions &o)
+{
+    return o.H ? FXG_TARGET_NAME : (o.Q ? FXG_TARGET_QUAL : (o.C ? FXG_TARGET_COMMENT : FXG_TARGET_SEQ));
+}
+
+// on_match (main.cpp:258-271): 1 = "-l: caller prints the file name and stops"
+int on_match(Job &job, FILE *out, const PairBatch &b, size_t i)
+{
+    if (job.opt.l) return 1;
+    if (job.opt.c) { ++job.matched_records; return 0; }
+    if (out) print_pair(out, b, i);
+    return 0;
+}
+
+// Applies one strategy's pair rules to a batch whose per-field flags are known.
+// Returns true when the input is finished early (-l).
+bool apply_rules(Job &job, Strategy st, const PairBatch &b, bool paired, const uint8_t *flags, const int32_t *pid,
+                 const std::string &file1, const std::string &file2)
+{
+    const CliOptions &o = job.opt;
+    const size_t stride = paired ? 2 : 1;
+    for (size_t i = 0; i < b.size(); ++i) {
+        const bool m1 = flags[i * stride] != 0;
+        const bool has2 = paired && !b.second[i].empty();
+        const bool m2 = has2 && flags[i * stride + 1] != 0;
+        if (st == S_LITERAL) {                                   // main.cpp:599-648
+            if (m1) {
+                if (!o.v && on_match(job, stdout, b, i) == 1) { printf("%s\n", file1.c_str()); return true; }
+            } else if (o.v) on_match(job, stdout, b, i);
+            else if (m2 && on_match(job, stdout, b, i) == 1) { printf("%s\n", file1.c_str()); return true; }   // :636 prints file 1
+        } else if (st == S_EXACT) {                              // main.cpp:311-346
+            if (m1) {
+                FILE *out = job.router.find(pid[i * stride]);    // lookup side effects happen even under -v / -c
+                if (!o.v && on_match(job, out, b, i) == 1) { printf("%s\n", file1.c_str()); return true; }
+            } else if (has2) {
+                if (m2) {
+                    FILE *out = job.router.find(pid[i * stride + 1]);
+                    if (on_match(job, out, b, i) == 1) { printf("%s\n", file2.c_str()); return true; }    // -v ignored here (:331-337)
+                } else if (o.v) on_match(job, stdout, b, i);
+            } else if (o.v) on_match(job, stdout, b, i);
+        } else {                                                 // main.cpp:388-446 with on_match2 (:273-289)
+            auto hit = [&](int id) {
+                if (o.v || o.l) return;
+                if (o.c) { ++job.matched_records; return; }
+                FILE *out = job.router.find(id);
+                if (out) print_pair(out, b, i);
+            };
+            if (m1) {
+                hit(pid[i * stride]);
+                if (o.l) { printf("%s\n", file1.c_str()); return true; }
+            } else if (has2) {
+                if (m2) hit(pid[i * stride + 1]);
+                if (!m2 && o.v) on_match(job, stdout, b, i);
+                else if (o.l) { printf("%s\n", file2.c_str()); return true; }     // also taken for a miss without -v (:427-435)
+            } else if (o.v) on_match(job, stdout, b, i);
+        }
+    }
+    return false;
+}
+
+// ------------------------------------------------------------------ fields path
+bool run_fields(Job &job, Strategy st, PairSource &src, bool paired, DevicePool &pool, Stats &stats)
+{
+    const size_t max_pairs = 1u << 20;
+    std::deque<std::unique_ptr<PairBatch>> pending;
+    std::vector<uint32_t> off;
+    auto finish_oldest = [&]() -> bool {
+        fxg_result r;
+        pool.collect(&r);
+        std::unique_ptr<PairBatch> b = std::move(pending.front());
+        pending.pop_front();
+        return apply_rules(job, st, *b, paired, r.flags, r.pattern_id, src.name1(), src.name2());
+    };
+    for (;;) {
+        std::unique_ptr<PairBatch> b(new PairBatch());
+        src.read_batch(*b, max_pairs, pool.batch_bytes() / 2);
+        const bool ended = b->ended;
+        if (b->size()) {
+            if (b->arena.size() + 64 > pool.batch_bytes()) {        // one oversized record: drain, then enlarge the staging buffers
+                while (!pending.empty()) if (finish_oldest()) return true;
+                size_t want = pool.batch_bytes();
+                while (want < b->arena.size() + 64) want <<= 1;
+                pool.grow(want);
+            }
+            if (pool.inflight() == pool.capacity() && finish_oldest()) return true;
+            void *pin; size_t cap;
+            pool.acquire(&pin, &cap);
+            char *dst = (char *)pin;
+            size_t used = 0;
+            off.clear();
+            off.push_back(0);
+            for (size_t i = 0; i < b->size(); ++i) {
+                const char *p; uint32_t n;
+                target_slice(job.opt, st, *b, b->first[i], false, p, n);
+                memcpy(dst + used, p, n); used += n; off.push_back((uint32_t)used);
+                if (paired) {
+                    if (b->second[i].empty()) n = 0;
+                    else target_slice(job.opt, st, *b, b->second[i], true, p, n);
+                    memcpy(dst + used, p, n); used += n; off.push_back((uint32_t)used);
+                }
+            }
+            pool.submit_fields(used, off.data(), (uint32_t)off.size() - 1);
+            stats.field_bytes += used; stats.field_batches++; stats.records += b->size();
+            pending.push_back(std::move(b));
+        }
+        if (ended) break;
+    }
+    while (!pending.empty()) if (finish_oldest()) return true;
+    return false;
+}
+
+// ------------------------------------------------------------------ raw path
+struct RawPending { const uint8_t *host; uint64_t file_off; size_t nbytes; };
+
+bool raw_path_allowed(const Job &job, const char *file2)
+{
+    const char *mode = getenv("FXTRACT_PATH");
+    if (mode && !strcmp(mode, "fields")) return false;
+    const CliOptions &o = job.opt;
+    if (file2 || o.I || o.l) return false;           // mates and -l need per-pair rules: fields path
+    return job.router.all_stdout();                  // per-pattern output files need first-hit ids: fields path
+}
+
+// Returns: -1 = raw path not applicable (nothing consumed), otherwise the byte offset from which
+// the fields path has to continue (== file size when the raw path handled everything).
+int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
+{
+    struct stat sb;
+    if (fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode)) return -1;
+    unsigned char magic[2] = {0, 0};
+    if (pread(fd, magic, 2, 0) < 1 || magic[0] != '@') return -1;      // FASTA, gzip (1f 8b), empty, ...: general reader
+    const CliOptions &o = job.opt;
+    std::deque<RawPending> pending;
+    uint64_t file_pos = 0;            // next byte to read from the file
+    const uint8_t *carry = nullptr;   // unconsumed tail of the previous batch (a partial record)
+    size_t carry_n = 0;
+    uint64_t batch_start = 0;         // file offset of the first byte of the batch being filled
+    bool eof = false;
+    int64_t reroute_at = -1;
+    auto finish_oldest = [&]() {
+        fxg_result r;
+        pool.collect(&r);
+        RawPending p = pending.front();
+        pending.pop_front();
+        if (reroute_at >= 0) return;                                   // results after a rejected batch are discarded
+        if (!r.canonical_ok) { reroute_at = (int64_t)p.file_off; stats.rerouted++; return; }
+        if (o.c) job.matched_records += (long)r.n_selected;
+        else for (uint64_t k = 0; k < r.n_runs; ++k) fwrite(p.host + r.runs[k].off, 1, r.runs[k].len, stdout);
+        stats.records += r.n_records;
+    };
+    while (!eof && reroute_at < 0) {
+        if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute_at >= 0) break; }
+        void *pin; size_t cap;
+        pool.acquire(&pin, &cap);
+        uint8_t *dst = (uint8_t *)pin;
+        size_t have = 0;
+        if (carry_n) { memmove(dst, carry, carry_n); have = carry_n; }
+        batch_start = file_pos - carry_n;
+        while (have < cap) {
+            ssize_t got = pread(fd, dst + have, cap - have, (off_t)file_pos);
+            if (got < 0) { perror("fxtract: read"); exit(1); }
+            if (got == 0) { eof = true; break; }
+            have += (size_t)got; file_pos += (uint64_t)got;
+        }
+        size_t n = have;
+        if (!eof) {
+            n = fxg_find_record_cut(dst, have);
+            if (n == 0) {                           // no record boundary in a whole buffer: not the fast path's business
+                pool.submit_raw(0, false);          // hands the lent buffer back
+                pending.push_back(RawPending{dst, batch_start, 0});
+                while (!pending.empty()) finish_oldest();
+                if (reroute_at < 0) reroute_at = (int64_t)batch_start;
+                break;
+            }
+        }
+        carry = dst + n; carry_n = have - n;
+        pool.submit_raw(n, eof);
+        pending.push_back(RawPending{dst, batch_start, n});
+        stats.raw_bytes += n; stats.raw_batches++;
+    }
+    while (!pending.empty()) finish_oldest();
+    if (reroute_at >= 0) {
+        const char *mode = getenv("FXTRACT_PATH");
+        if (mode && !strcmp(mode, "raw")) {
+            fprintf(stderr, "fxtract: FXTRACT_PATH=raw but the input is not canonical FASTQ at byte %lld\n", (long long)reroute_at);
+            exit(1);
+        }
+        return reroute_at;
+    }
+    return (int64_t)file_pos;
+}
+
+// ------------------------------------------------------------------ POSIX regex (outside the graft; CPU, main.cpp:462-514)
+int run_regex(Job &job, PairSource &src, bool paired, regex_t *re)
+{
+    const CliOptions &o = job.opt;
+    std::string tmp;
+    auto field_of = [&](const PairBatch &b, const RecView &r) -> const char * {
+        const char *p; uint32_t n;
+        target_slice(o, S_EXACT, b, r, false, p, n);
+        tmp.assign(p, n);
+        return tmp.c_str();
+    };
+    auto regfail = [&](int code) {
+        size_t len = regerror(code, re, nullptr, 0);
+        std::string msg(len, '\0');
+        regerror(code, re, &msg[0], len);
+        fprintf(stderr, "%s\n", msg.c_str());
+    };
+    for (;;) {
+        PairBatch b;
+        src.read_batch(b, 1u << 16, 32u << 20);
+        for (size_t i = 0; i < b.size(); ++i) {
+            int ret = regexec(re, field_of(b, b.first[i]), 0, nullptr, 0);
+            if (ret == REG_NOMATCH) {
+                if (paired && !b.second[i].empty()) {
+                    ret = regexec(re, field_of(b, b.second[i]), 0, nullptr, 0);
+                    if (ret == REG_NOMATCH && o.v) on_match(job, stdout, b, i);
+                    if (ret != REG_NOMATCH && ret != 0) { regfail(ret); return 1; }
+                    else if (ret == 0 && on_match(job, stdout, b, i) == 1) { printf("%s\n", src.name2().c_str()); return 0; }
+                } else if (o.v) on_match(job, stdout, b, i);
+            } else if (ret != 0) { regfail(ret); return 1; }
+            else if (!o.v && on_match(job, stdout, b, i) == 1) { printf("%s\n", src.name1().c_str()); return 0; }
+        }
+        if (b.ended) break;
+    }
+    return 0;
+}
+
+}  // namespace
+
+int run_input(Job &job, const char *file1, const char *file2)
+{
+    const CliOptions &o = job.opt;
+    const bool paired = (file2 != nullptr) || o.I;
+    PairSource src;
+    if (src.open(file1, file2, o.I) != 0) {
+        fprintf(stderr, "Failed to open stream\n");
+        return 1;
+    }
+    if (o.E || o.G) {                                            // dispatch priority: regex first (main.cpp:707-725)
+        regex_t re;
+        int flags = REG_NOSUB | (o.E ? REG_EXTENDED : REG_BASIC);
+        int rc = regcomp(&re, job.pattern.c_str(), flags);
+        if (rc) {
+            size_t len = regerror(rc, &re, nullptr, 0);
+            std::string msg(len, '\0');
+            regerror(rc, &re, &msg[0], len);
+            fprintf(stderr, "%s\n", msg.c_str());
+            return 1;
+        }
+        run_regex(job, src, paired, &re);
+        regfree(&re);
+        return 0;
+    }
+    const Strategy st = o.X ? S_EXACT : (o.f ? S_MULTI : S_LITERAL);      // X beats f (main.cpp:749-757)
+    std::vector<std::string> pats;
+    if (st == S_LITERAL) {
+        pats.push_back(job.pattern);
+        // prepare_revcomp (main.cpp:557-565): XOR rule; an empty reverse complement is not searched (:602)
+        if (o.r != (o.H || o.Q || o.C)) {
+            std::string rc = reverse_complement(job.pattern);
+            if (!rc.empty()) pats.push_back(rc);
+        }
+    } else {
+        pats = job.router.patterns();
+        if (pats.empty()) {
+            if (st == S_MULTI) fprintf(stderr, "problem initalizing multi-search\n");   // ssearch_create(…, 0) == NULL
+            // exact lookup in an empty map never hits: only -v prints; handled below with a pattern that cannot occur
+            if (st == S_MULTI) return 0;
+            pats.push_back(std::string("\n\n", 2));
+        }
+    }
+    PoolConfig pc;
+    pc.mode = st == S_LITERAL ? FXG_MODE_LITERAL : (st == S_MULTI ? FXG_MODE_MULTI : FXG_MODE_EXACT);
+    pc.target = fxg_target(o);
+    pc.invert = o.v; pc.count_only = o.c; pc.want_pattern_id = st != S_LITERAL;
+    pc.batch_bytes = batch_bytes_from_env();
+    pc.devices = devices_from_env();
+    DevicePool pool(pc, pats);
+
+    Stats stats;
+    const auto t0 = std::chrono::steady_clock::now();
+    uint64_t input_bytes = 0;
+    bool done = false;
+    if (raw_path_allowed(job, file2)) {
+        int fd = open(file1, O_RDONLY);
+        if (fd >= 0) {
+            int64_t next = run_raw(job, fd, pool, stats);
+            if (next >= 0) {
+                struct stat sb;
+                fstat(fd, &sb);
+                input_bytes = (uint64_t)sb.st_size;
+                if ((uint64_t)next >= (uint64_t)sb.st_size) done = true;
+                else {
+                    PairSource rest;                             // kseq has last_char == 0 at a FASTQ record boundary
+                    rest.open_fd_at(fd, (uint64_t)next, file1);
+                    run_fields(job, st, rest, false, pool, stats);
+                    done = true;
+                }
+            }
+            close(fd);
+        }
+    }
+    if (!done) run_fields(job, st, src, paired, pool, stats);
+    if (job.stats) {
+        const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        fprintf(stderr, "[fxtract] %s: raw %llu B in %llu batches, fields %llu B in %llu batches, %llu records, %llu re-routed, "
+                        "%.3f s%s\n", file1, (unsigned long long)stats.raw_bytes, (unsigned long long)stats.raw_batches,
+                (unsigned long long)stats.field_bytes, (unsigned long long)stats.field_batches,
+                (unsigned long long)stats.records, (unsigned long long)stats.rerouted, s,
+                input_bytes ? (", " + std::to_string(input_bytes / s / 1e9) + " GB/s").c_str() : "");
+    }
+    return 0;
+}
+
+}  // namespace fxh

@@ -1,0 +1,152 @@
+/*
+ * tests/cpu_shim/shim_fxgpu.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ * A CPU stand-in for the *fields path* of libfxgpu's C ABI (include/fxgpu.h) so that the
+ * host CLI's own logic -- reader, pair rules, output routing, option surface, raw->fields
+ * re-routing -- can be exercised by the `-m "not gpu"` tests in a container without a GPU.
+ * It is built by tests/test_cli_host.py into tests/cpu_shim/_build/ and reaches the CLI only
+ * through an explicit LD_LIBRARY_PATH set by that test.  It is never installed, never on the
+ * product's rpath, and proves nothing about the CUDA kernels: GPU parity is tests -m gpu.
+ * The raw path always answers "not canonical", which forces (and thereby tests) the re-route.
+ */
+#include "../../include/fxgpu.h"
+#include "../../oracle/fxo_ac.h"
+#include <stdlib.h>
+#include <string.h>
+
+struct fxg_ctx {
+    fxg_config cfg;
+    uint8_t *blob; uint32_t *off; uint32_t n;
+    fxo_ac *ac;
+    uint8_t *buf[2]; int state[2];          /* 0 free 1 lent 2 submitted */
+    uint8_t *flags[2]; int32_t *pid[2]; uint64_t nrec[2], nhit[2]; int raw[2];
+    int fifo[2]; int nfifo;
+};
+
+static const char *g_err = "";
+
+int fxg_device_count(int *n) { if (n) *n = 1; return FXG_OK; }
+const char *fxg_last_error(const fxg_ctx *c) { (void)c; return g_err; }
+
+int fxg_create(const fxg_config *cfg, fxg_ctx **out)
+{
+    fxg_ctx *c = (fxg_ctx *)calloc(1, sizeof *c);
+    c->cfg = *cfg;
+    if (!c->cfg.batch_bytes) c->cfg.batch_bytes = 1u << 20;
+    *out = c;
+    return FXG_OK;
+}
+
+void fxg_destroy(fxg_ctx *c)
+{
+    if (!c) return;
+    for (int i = 0; i < 2; ++i) { free(c->buf[i]); free(c->flags[i]); free(c->pid[i]); }
+    if (c->ac) fxo_ac_free(c->ac);
+    free(c->blob); free(c->off); free(c);
+}
+
+int fxg_set_patterns(fxg_ctx *c, const uint8_t *blob, const uint32_t *off, uint32_t n)
+{
+    if (n == 0) { g_err = "empty pattern set"; return FXG_ERR_ARG; }
+    c->n = n;
+    c->off = (uint32_t *)malloc(sizeof(uint32_t) * (n + 1));
+    memcpy(c->off, off, sizeof(uint32_t) * (n + 1));
+    c->blob = (uint8_t *)malloc(off[n] + 1);
+    memcpy(c->blob, blob, off[n]);
+    if (c->cfg.mode == FXG_MODE_MULTI) {
+        const char **p = (const char **)malloc(sizeof(char *) * n);
+        size_t *l = (size_t *)malloc(sizeof(size_t) * n);
+        for (uint32_t i = 0; i < n; ++i) { p[i] = (const char *)c->blob + off[i]; l[i] = off[i + 1] - off[i]; }
+        c->ac = fxo_ac_build(p, l, (int)n);
+        free(p); free(l);
+    }
+    return FXG_OK;
+}
+
+int fxg_acquire_buffer(fxg_ctx *c, void **pinned, size_t *cap)
+{
+    for (int i = 0; i < 2; ++i) if (c->state[i] == 1) { g_err = "a buffer is already lent out"; return FXG_ERR_STATE; }
+    for (int i = 0; i < 2; ++i) if (c->state[i] == 0) {
+        if (!c->buf[i]) c->buf[i] = (uint8_t *)malloc(c->cfg.batch_bytes + 64);
+        c->state[i] = 1; *pinned = c->buf[i]; *cap = c->cfg.batch_bytes;
+        return FXG_OK;
+    }
+    g_err = "both buffers are in flight";
+    return FXG_ERR_STATE;
+}
+
+static int lent(fxg_ctx *c) { for (int i = 0; i < 2; ++i) if (c->state[i] == 1) return i; return -1; }
+
+int fxg_submit_raw(fxg_ctx *c, size_t nbytes, int is_last)
+{
+    (void)is_last;
+    int s = lent(c);
+    if (s < 0) { g_err = "no acquired buffer"; return FXG_ERR_STATE; }
+    c->raw[s] = nbytes ? 1 : 2; c->state[s] = 2; c->fifo[c->nfifo++] = s;
+    return FXG_OK;
+}
+
+int fxg_submit_raw_from(fxg_ctx *c, const void *h, size_t n, int l) { (void)c; (void)h; (void)n; (void)l; g_err = "shim: unsupported"; return FXG_ERR_UNSUPPORTED; }
+
+static const uint8_t *find_bytes(const uint8_t *h, size_t hn, const uint8_t *p, size_t pn)
+{
+    if (pn == 0) return h;
+    if (pn > hn) return NULL;
+    for (size_t i = 0; i + pn <= hn; ++i) if (h[i] == p[0] && !memcmp(h + i, p, pn)) return h + i;
+    return NULL;
+}
+
+int fxg_submit_fields(fxg_ctx *c, size_t nbytes, const uint32_t *off, uint32_t nrec)
+{
+    (void)nbytes;
+    int s = lent(c);
+    if (s < 0) { g_err = "no acquired buffer"; return FXG_ERR_STATE; }
+    free(c->flags[s]); free(c->pid[s]);
+    c->flags[s] = (uint8_t *)calloc(nrec + 1, 1);
+    c->pid[s] = (int32_t *)malloc(sizeof(int32_t) * (nrec + 1));
+    c->nhit[s] = 0; c->nrec[s] = nrec; c->raw[s] = 0;
+    for (uint32_t k = 0; k < nrec; ++k) {
+        const uint8_t *f = c->buf[s] + off[k];
+        size_t fl = off[k + 1] - off[k];
+        int id = -1;
+        if (c->cfg.mode == FXG_MODE_LITERAL) {
+            for (uint32_t q = 0; q < c->n && q < 2 && id < 0; ++q)
+                if (find_bytes(f, fl, c->blob + c->off[q], c->off[q + 1] - c->off[q])) id = (int)q;
+        } else if (c->cfg.mode == FXG_MODE_MULTI) {
+            size_t end;
+            id = fxo_ac_first(c->ac, (const char *)f, fl, &end);
+        } else {
+            for (uint32_t q = 0; q < c->n && id < 0; ++q)
+                if (c->off[q + 1] - c->off[q] == fl && !memcmp(c->blob + c->off[q], f, fl)) id = (int)q;
+        }
+        c->flags[s][k] = id >= 0; c->pid[s][k] = id; c->nhit[s] += id >= 0;
+    }
+    c->state[s] = 2; c->fifo[c->nfifo++] = s;
+    return FXG_OK;
+}
+
+int fxg_collect(fxg_ctx *c, fxg_result *r)
+{
+    if (!c->nfifo) { g_err = "nothing submitted"; return FXG_ERR_STATE; }
+    int s = c->fifo[0];
+    c->fifo[0] = c->fifo[1]; c->nfifo--;
+    memset(r, 0, sizeof *r);
+    if (c->raw[s]) {                         /* raw path: always "not canonical" (empty batches are fine) */
+        r->canonical_ok = c->raw[s] == 2;
+        r->violation = c->raw[s] == 2 ? 0 : FXG_V_DENSE_LINES;
+    } else {
+        r->canonical_ok = 1; r->n_records = c->nrec[s]; r->n_matched = r->n_selected = c->nhit[s];
+        r->flags = c->flags[s]; r->pattern_id = c->cfg.want_pattern_id ? c->pid[s] : NULL;
+    }
+    c->state[s] = 0;
+    return FXG_OK;
+}
+
+int fxg_count(fxg_ctx *c, uint64_t *t) { (void)c; *t = 0; return FXG_OK; }
+
+size_t fxg_find_record_cut(const uint8_t *buf, size_t n)
+{
+    /* any line start that looks like a header; the shim's raw path rejects everything anyway */
+    for (size_t c = n; c > 1; --c) if (buf[c - 1] == '@' && buf[c - 2] == '\n') return c - 1;
+    return 0;
+}

@@ -133,3 +133,86 @@ def pick_substring(rng, data, lo=4, hi=24):
     n = rng.randint(lo, min(hi, len(l)))
     s = rng.randint(0, len(l) - n)
     return l[s:s + n].strip(b"\r")
+
+
+# ------------------------------------------------------------------ randomised CLI cases
+FLAGSETS = ["", "-v", "-c", "-vc", "-H", "-Hv", "-C", "-Q", "-r", "-rH", "-X", "-HX", "-HXv", "-rX",
+            "-f", "-Hf", "-vf", "-cf", "-rf", "-HXf", "-Cf", "-HXcf", "-l", "-lf", "-lX", "-I", "-Iv", "-IHf", "-IX",
+            "-Qf", "-vHXf", "-lv"]
+
+
+def stash(wd, name, suffix):
+    p = os.path.join(wd, name)
+    if os.path.exists(p):
+        os.replace(p, p + suffix)
+
+
+def read_or_none(wd, name):
+    p = os.path.join(wd, name)
+    return open(p, "rb").read() if os.path.exists(p) else None
+
+
+def random_cli_cases(rng, wd, trials=12):
+    """Yields (argv, [output files]) over freshly written random inputs a.fx / b.fx in wd.
+    Covers the three literal strategies, all targets, -v/-c/-l/-r, pairs, -I, -S, gz input and
+    pattern files with per-pattern output files."""
+    kind = rng.choice(["fq", "fq_dirty", "fa"])
+    if kind == "fq":
+        d1 = make_fastq(rng, rng.randint(1, 40)); d2 = make_fastq(rng, rng.randint(1, 40))
+    elif kind == "fq_dirty":
+        d1 = make_fastq(rng, rng.randint(1, 40), dirty=True); d2 = make_fastq(rng, rng.randint(1, 40), dirty=True)
+    else:
+        d1 = make_fasta(rng, rng.randint(1, 40)); d2 = make_fasta(rng, rng.randint(1, 40))
+    open(os.path.join(wd, "a.fx"), "wb").write(d1)
+    open(os.path.join(wd, "b.fx"), "wb").write(d2)
+    with gzip.open(os.path.join(wd, "a.fx.gz"), "wb") as f:
+        f.write(d1)
+    for trial in range(trials):
+        flags = rng.choice(FLAGSETS)
+        target = "H" if "H" in flags else ("C" if "C" in flags else ("Q" if "Q" in flags else "S"))
+        if "Q" in flags and "f" in flags and kind == "fa":
+            continue  # reference UB (main.cpp:394-398)
+        pats = []
+        for _ in range(rng.randint(1, 4)):
+            if target == "H":
+                names = [l[1:].split()[0] for l in d1.split(b"\n") if l[:1] in b">@" and len(l) > 1 and l[1:].split()]
+                nm = rng.choice(names) if names else b"zz"
+                pats.append(nm if ("X" in flags or rng.random() < 0.5) else nm[: max(1, len(nm) // 2)])
+            elif target == "C":
+                pats.append(rng.choice([b"N:0", b"Accumuli", b"x", b"sample=", b"two"]))
+            elif target == "Q":
+                pats.append(bytes([rng.randint(40, 70)]) * rng.randint(1, 2))
+            else:
+                sub = pick_substring(rng, d1)
+                if "X" in flags:
+                    lines = [l for l in d1.split(b"\n") if l and l[:1] not in b">@+"]
+                    sub = rng.choice(lines) if lines else sub
+                pats.append(sub)
+        pats = [p for p in pats if p and b"\n" not in p and b"\t" not in p and b"\r" not in p]
+        if not pats:
+            continue
+        argv, outs = [], []
+        if flags:
+            argv.append(flags if "f" not in flags else flags.replace("f", "") + "f")
+        if "f" in flags:
+            pf = os.path.join(wd, "p%d.txt" % trial)
+            with_files = rng.random() < 0.4
+            lines = []
+            for k, p in enumerate(pats):
+                if with_files and rng.random() < 0.7:
+                    out = "out_%d_%d.fx" % (trial, k % 2)
+                    outs.append(out)
+                    lines.append(p + b"\t" + out.encode())
+                else:
+                    lines.append(p)
+            open(pf, "wb").write(b"\n".join(lines) + b"\n")
+            argv.append(pf)
+        else:
+            argv.append(pats[0].decode("latin1"))
+        single = ("I" in flags) or rng.random() < 0.5
+        if single and "I" not in flags:
+            argv.insert(0, "-S")
+        first = "a.fx.gz" if rng.random() < 0.2 else "a.fx"
+        argv += [first] if single else [first, "b.fx"]
+        argv = [a for a in argv if a != "-"]
+        yield argv, sorted(set(outs))
