@@ -47,6 +47,7 @@ struct fxg_ctx {
     size_t cap_bytes = 0; size_t rec_cap = 0; size_t ntiles_cap = 0; size_t nblocks_cap = 0;
     fxg::TileInfo *d_info = nullptr; unsigned short *d_tile_nl = nullptr; unsigned int *d_tile_hit = nullptr;
     unsigned long long *d_lbase = nullptr, *d_bsum = nullptr;
+    unsigned int *d_redo = nullptr;      // [ntiles] list + [1] count at index ntiles_cap
     fxg::ScanCounters *d_ctr = nullptr; unsigned int *d_hitbits = nullptr;
     unsigned long long *d_rec_start = nullptr, *d_fld_off = nullptr, *d_block_sums = nullptr, *d_counts = nullptr;
     unsigned int *d_fld_len = nullptr;
@@ -240,6 +241,7 @@ static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
     if ((e = dev_realloc(ctx->d_tile_nl, ntiles * (size_t)kNlStride)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line tables");
     if ((e = dev_realloc(ctx->d_lbase, ntiles + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile prefix");
     if ((e = dev_realloc(ctx->d_bsum, ntiles / 4096 + 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc span prefix");
+    if ((e = dev_realloc(ctx->d_redo, ntiles + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc redo list");
     if (ctx->cfg.mode == FXG_MODE_LITERAL &&
         (e = dev_realloc(ctx->d_tile_hit, ntiles * (size_t)kHitWords)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line hits");
     if ((e = dev_realloc(ctx->d_hitbits, words + 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc hit bitset");
@@ -308,11 +310,13 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, sizeof(ScanCounters), st));
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_counts, 0, 2 * sizeof(unsigned long long), st));
     FXG_CUDA_OK(cudaMemsetAsync(&ctx->d_ctr->first_bad, 0xff, 8, st));      // min-reduced by the kernel
+    FXG_CUDA_OK(cudaMemsetAsync(ctx->d_redo + ctx->ntiles_cap, 0, sizeof(unsigned int), st));
     ScanParams P;
     memset(&P, 0, sizeof P);
     P.buf = d_buf; P.nbytes = nbytes; P.ntiles = ntiles; P.info = ctx->d_info; P.tile_nl = ctx->d_tile_nl;
     P.tile_hit = ctx->d_tile_hit; P.lbase = ctx->d_lbase; P.bsum = ctx->d_bsum; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
     P.rec_start = emit ? ctx->d_rec_start : nullptr; P.rec_cap = rec_cap; P.one = 1;
+    P.redo_list = ctx->d_redo; P.redo_count = ctx->d_redo + ctx->ntiles_cap;
     P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;
@@ -446,7 +450,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
     void *dev[] = {ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat,
-                   ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_ctr, ctx->d_hitbits, ctx->d_rec_start, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
+                   ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_rec_start, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_in, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);

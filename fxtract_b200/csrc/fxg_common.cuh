@@ -28,7 +28,8 @@ constexpr int kCandCap = 512;                  // literal candidates queued per 
 // converts line hits into record hits / record starts / field tables.
 struct __align__(16) TileInfo {
     unsigned int total;          // bytes < 0x20 in the tile (== '\n' count unless FXG_V_BYTE_RANGE is raised)
-    unsigned int viol;           // phase-independent FXG_V_* bits
+    unsigned int viol;           // bits 0..15: FXG_V_* bits (phase-independent ones, plus -- when bits 16..18 are
+                                 // non-zero -- everything evaluated under the guessed phase (bits 16..18) - 1)
     unsigned short cls[4];       // OR of the line flags of the lines with local index == k (mod 4): low byte = the
                                  // line itself, high byte = class flags of the head of the following line
 };
@@ -85,6 +86,8 @@ struct ScanParams {
     int match_enabled;                // 0: index/validate only (multi / exact use the field table)
     int lit_unit;                     // host copy of lit->unit (selects the kernel variant)
     unsigned int one;                 // == 1 (lets the kernel issue adds as IMAD; see fma_add)
+    unsigned int *redo_list;          // [ntiles] tiles whose locally guessed line phase was wrong (normally none)
+    unsigned int *redo_count;         // [1]
     // field table for the second-stage matchers (multi / exact): target field of record k
     unsigned long long *fld_off;      // [rec_cap] or nullptr
     unsigned int *fld_len;            // [rec_cap]

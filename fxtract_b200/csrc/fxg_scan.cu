@@ -39,11 +39,10 @@ constexpr int kWarpChunks = kChunks / kWarps;       // chunks one warp covers (c
 
 struct __align__(128) ScanSmem {
     uint4 tile[2][kChunks];                   // staged tile bytes, double buffered (bulk-copy destinations)
-    unsigned char cnt[kChunks];               // bytes < 0x20 per chunk
-    unsigned int pre[kThreads];               // exclusive prefix of cnt per group of kChunksPerThread chunks
     unsigned short nlpos[kMaxTileLines];      // tile-relative '\n' positions, in order
-    unsigned short wl[kWarps][kWarpChunks];   // per warp: its chunks that contain a byte < 0x20
-    unsigned int wcnt[kWarps];                // entries in wl[w]
+    unsigned short wl[kWarps][kWarpChunks];   // per warp: its chunks that contain a byte < 0x21 ('\n' candidates)
+    unsigned short wm[kWarps][kWarpChunks];   // per entry of wl: 16-bit mask of the bytes < 0x20 of that chunk
+    unsigned int wtot[kWarps];                // '\n' count of each warp's 2 KiB segment
     unsigned int below[17];                   // interleaved-layout mask of the bytes < p of a chunk
     unsigned int sbits[kChunks / 32];         // bit c: chunk c has a byte < 0x41 (not a sequence letter)
     unsigned int qbits[kChunks / 32];         // bit c: chunk c has a byte < 0x21 (not a quality char)
@@ -53,11 +52,21 @@ struct __align__(128) ScanSmem {
     unsigned short lit_masks[64];
     int cand_off[kCandCap];                   // tile-relative offset of a candidate unit
     unsigned short cand_mask[kCandCap];       // (pattern,shift) bits to verify
-    unsigned int warp_sums[kWarps];
     unsigned long long mbar[2];               // bulk-copy completion barriers
-    unsigned int cls[4];                      // line flags OR-ed per (local line index mod 4)
-    unsigned int n_cand, viol, total, any_hit;
+    // per-tile scalars, double buffered by tile parity: the copy of the previous tile is reset by
+    // thread 0 while the current one is in use (no extra barrier between "last read" and "first write")
+    struct TileState {
+        unsigned int cls[4];                  // generic path: line flags OR-ed per (local line index mod 4)
+        unsigned int n_cand, viol, any_hit;
+        unsigned int plus_idx;                // smallest local index of a line that is exactly "+" (phase anchor)
+    } st[2];
 };
+typedef ScanSmem::TileState TileState;
+__device__ __forceinline__ void reset_state(TileState &T)
+{
+    T.n_cand = 0; T.viol = 0; T.any_hit = 0; T.plus_idx = 0xffffffffu;
+    T.cls[0] = T.cls[1] = T.cls[2] = T.cls[3] = 0;
+}
 
 // ---------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ unsigned int smem_u32(const void *p) { return (unsigned int)__cvta_generic_to_shared(p); }
@@ -137,7 +146,7 @@ __device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int ad
     return n0 | (n1 << 4) | (n2 << 8) | (n3 << 12);
 }
 
-__device__ __forceinline__ void note_violation(ScanSmem &S, unsigned int bit) { atomicOr(&S.viol, bit); }
+__device__ __forceinline__ void note_violation(TileState &T, unsigned int bit) { atomicOr(&T.viol, bit); }
 
 // byte of the batch at global offset g: from the staged tile when inside it
 __device__ __forceinline__ unsigned int text_byte(const unsigned char *tb, const ScanParams &P,
@@ -148,14 +157,15 @@ __device__ __forceinline__ unsigned int text_byte(const unsigned char *tb, const
     return P.buf[g];
 }
 
-// '\n' count in tile bytes [0, rel)
-__device__ __forceinline__ unsigned int lines_before(const ScanSmem &S, const unsigned char *tb, int rel)
+// '\n' count in tile bytes [0, rel): lower bound in the finished position table
+__device__ __forceinline__ unsigned int lines_before(const ScanSmem &S, int n_tab, int rel)
 {
-    int c = rel >> 4;
-    unsigned int n = S.pre[c / kChunksPerThread];
-    for (int q = c - c % kChunksPerThread; q < c; ++q) n += S.cnt[q];
-    for (int b = c << 4; b < rel; ++b) n += (tb[b] < 0x20);
-    return n;
+    int lo = 0, hi = n_tab;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if ((int)S.nlpos[mid] < rel) lo = mid + 1; else hi = mid;
+    }
+    return (unsigned int)lo;
 }
 
 // any bit set in rows[lo, hi) (chunk indices) of both class bit rows
@@ -227,7 +237,7 @@ __host__ __device__ inline unsigned int role_kinds(unsigned int f, int role)
 // A verified occurrence is recorded on its local line; whether that line has the target's
 // role (sequence / quality / header) is decided by tile_finalize_kernel.  Header targets add
 // the geometric condition (inside the name / inside the comment), which is phase-free.
-__device__ __noinline__ void verify_candidate(ScanSmem &S, const unsigned char *tb, const ScanParams &P,
+__device__ __noinline__ void verify_candidate(ScanSmem &S, TileState &T, const unsigned char *tb, const ScanParams &P,
                                               unsigned long long base, int n_tab, int unit_rel, unsigned int bits)
 {
     const LiteralTable *lit = P.lit;
@@ -247,8 +257,7 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, const unsigned char *
         // local line: number of '\n' before p inside the tile (an occurrence that starts in the
         // previous tile lies on this tile's line 0)
         int rel = (int)(p - (long long)base);
-        unsigned int loc = rel > 0 ? lines_before(S, tb, rel) : 0u;
-        if (loc > (unsigned int)kMaxTileLines) continue;       // tile is flagged FXG_V_DENSE_LINES anyway
+        unsigned int loc = rel > 0 ? lines_before(S, n_tab, rel) : 0u;
         bool hit = true;
         if (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT) {
             // header line: name = (ls, first ' ' or end), comment = after that ' '
@@ -258,7 +267,7 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, const unsigned char *
                 long long q = (p < (long long)base ? p : (long long)base) - 1;
                 int guard = 1 << 20;
                 while (q >= 0 && P.buf[q] != '\n' && --guard) --q;
-                if (!guard) { note_violation(S, FXG_V_DENSE_LINES); continue; }
+                if (!guard) { note_violation(T, FXG_V_DENSE_LINES); continue; }
                 ls = q + 1;
             }
             long long q = ls + 1, sp = -1;
@@ -275,18 +284,18 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, const unsigned char *
                 hit = (sp >= 0) && (p >= sp + 1);
             }
         }
-        if (hit) { atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31)); S.any_hit = 1; }
+        if (hit) { atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31)); T.any_hit = 1; }
     }
 }
 
-__device__ __forceinline__ void push_candidate(ScanSmem &S, int unit_rel, unsigned int bits)
+__device__ __forceinline__ void push_candidate(ScanSmem &S, TileState &T, int unit_rel, unsigned int bits)
 {
-    unsigned int slot = atomicAdd(&S.n_cand, 1u);
+    unsigned int slot = atomicAdd(&T.n_cand, 1u);
     if (slot < kCandCap) { S.cand_off[slot] = unit_rel; S.cand_mask[slot] = (unsigned short)bits; }
 }
 
 // generic (short-pattern) literal filter: units of 4, 2 or 1 bytes compared against every key
-__device__ __noinline__ void filter_small_units(ScanSmem &S, unsigned int x0, unsigned int x1, unsigned int x2,
+__device__ __noinline__ void filter_small_units(ScanSmem &S, TileState &T, unsigned int x0, unsigned int x1, unsigned int x2,
                                                 unsigned int x3, int off, int U, int nkeys)
 {
     for (int u = 0; u < 16; u += U) {
@@ -294,8 +303,33 @@ __device__ __noinline__ void filter_small_units(ScanSmem &S, unsigned int x0, un
         unsigned int word = wi == 0 ? x0 : (wi == 1 ? x1 : (wi == 2 ? x2 : x3));
         unsigned int val = U == 4 ? word : (U == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu) : ((word >> ((u & 3) * 8)) & 0xffu));
         for (int k = 0; k < nkeys; ++k)
-            if ((unsigned int)S.lit_keys[k] == val) push_candidate(S, off + u, S.lit_masks[k]);
+            if ((unsigned int)S.lit_keys[k] == val) push_candidate(S, T, off + u, S.lit_masks[k]);
     }
+}
+
+// ---------------------------------------------------------------- class check of a byte range
+// any bit set in row[lo, hi) (chunk indices)
+__device__ __forceinline__ unsigned int row_any(const unsigned int *row, int lo, int hi)
+{
+    if (lo >= hi) return 0u;
+    const int wl = lo >> 5, wh = (hi - 1) >> 5;
+    const unsigned int ml = 0xffffffffu << (lo & 31), mh = 0xffffffffu >> (31 - ((hi - 1) & 31));
+    if (wl == wh) return row[wl] & ml & mh;
+    unsigned int any = (row[wl] & ml) | (row[wh] & mh);
+    for (int w = wl + 1; w < wh; ++w) any |= row[w];
+    return any;
+}
+// non-zero iff tile bytes [a, b) hold a byte below 0x41 (seq) / 0x21 (!seq)
+__device__ __forceinline__ unsigned int class_bad(const ScanSmem &S, const uint4 *tile, int a, int b, bool seq)
+{
+    if (b <= a) return 0u;
+    const unsigned int add = seq ? kAdd41 : kAdd21;
+    const unsigned int *row = seq ? S.sbits : S.qbits;
+    const int ca = a >> 4, cb = (b - 1) >> 4;
+    const unsigned int ma = il_mask(tile[ca], add) & ~S.below[a - (ca << 4)];
+    if (ca == cb) return ma & S.below[b - (ca << 4)];
+    const unsigned int mb = il_mask(tile[cb], add) & S.below[b - (cb << 4)];
+    return ma | mb | row_any(row, ca + 1, cb);
 }
 
 // ---------------------------------------------------------------- kernel 1: per-tile scan
@@ -303,27 +337,35 @@ __device__ __noinline__ void filter_small_units(ScanSmem &S, unsigned int x0, un
 // is prefetched into the other shared-memory buffer while the current one is processed.
 // LM = literal filter mode: 0 none (multi / exact strategies), 8 = aligned 8-byte units with the
 // fingerprint table, 1 = short patterns (units of 4 / 2 / 1 bytes).
-template <int LM>
+// REDO = second launch over the (normally empty) list of tiles whose locally guessed line phase
+// turned out wrong: those are re-evaluated with the phase-free per-line path.
+template <int LM, bool REDO>
 __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParams P)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem &S = *reinterpret_cast<ScanSmem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LiteralTable *lit = P.lit;
+    const unsigned long long n_work = REDO ? (unsigned long long)*P.redo_count : P.ntiles;
+    if ((unsigned long long)blockIdx.x >= n_work) return;
+#define FXG_TILE_OF(k) (REDO ? (unsigned long long)P.redo_list[(k)] : (unsigned long long)(k))
 
     // ---- once per CTA: tables, barriers, first tile in flight
     if (tid == 0) {
         mbar_init(&S.mbar[0], 1);
         mbar_init(&S.mbar[1], 1);
-        const unsigned long long t0 = blockIdx.x;
+        const unsigned long long t0 = FXG_TILE_OF(blockIdx.x);
         const unsigned long long rem0 = P.nbytes - t0 * (unsigned long long)kTileBytes;
         const unsigned int bulk0 = (unsigned int)(rem0 < (unsigned long long)kTileBytes ? rem0 : (unsigned long long)kTileBytes) & ~15u;
         if (bulk0) {
             mbar_expect_tx(&S.mbar[0], bulk0);
             bulk_g2s(S.tile[0], P.buf + t0 * (unsigned long long)kTileBytes, bulk0, &S.mbar[0]);
         }
+        reset_state(S.st[0]);
+        reset_state(S.st[1]);
     }
     if (tid >= 128 && tid < 145) S.below[tid - 128] = kBelowTab[tid - 128];
+    if (LM != 0) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
     int lit_unit = 0, lit_nkeys = 0;
     unsigned int lit_mul1 = 0, lit_mul2 = 0;
     if (LM != 0) {
@@ -335,11 +377,16 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
     }
     const unsigned int one = P.one;
     const unsigned int lt_mask = (1u << lane) - 1u;
+    unsigned short *my_list = S.wl[warp];
+    unsigned short *my_mask = S.wm[warp];
+    __syncthreads();
 
     unsigned int it = 0;
-    for (unsigned long long t = blockIdx.x; t < P.ntiles; t += gridDim.x, ++it) {
+    for (unsigned long long k = blockIdx.x; k < n_work; k += gridDim.x, ++it) {
+        const unsigned long long t = FXG_TILE_OF(k);
         const int cur = (int)(it & 1u);
         const uint4 *tile = S.tile[cur];
+        TileState &T = S.st[cur];
         const unsigned char *tb = reinterpret_cast<const unsigned char *>(tile);
         const unsigned long long base = t * (unsigned long long)kTileBytes;
         const unsigned long long remain = P.nbytes - base;
@@ -347,10 +394,12 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
         const int bulk = tile_len & ~15;
 
         // ---- prefetch the next tile of this CTA into the other buffer (free since the end of the
-        //      previous iteration); per-tile state
+        //      previous iteration); reset the other copy of the per-tile scalars
         if (tid == 0) {
-            const unsigned long long tn = t + gridDim.x;
-            if (tn < P.ntiles) {
+            if (it) reset_state(S.st[cur ^ 1]);
+            const unsigned long long kn = k + gridDim.x;
+            if (kn < n_work) {
+                const unsigned long long tn = FXG_TILE_OF(kn);
                 const unsigned long long remn = P.nbytes - tn * (unsigned long long)kTileBytes;
                 const unsigned int bulkn = (unsigned int)(remn < (unsigned long long)kTileBytes ? remn : (unsigned long long)kTileBytes) & ~15u;
                 if (bulkn) {
@@ -359,123 +408,147 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
                     bulk_g2s(S.tile[cur ^ 1], P.buf + tn * (unsigned long long)kTileBytes, bulkn, &S.mbar[cur ^ 1]);
                 }
             }
-            S.n_cand = 0; S.viol = 0; S.any_hit = 0;
-            S.cls[0] = S.cls[1] = S.cls[2] = S.cls[3] = 0;
         }
-        if (LM != 0) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
         if (tile_len < kTileBytes) {             // ragged end of the batch: patch by hand, neutral filler
             for (int b = bulk + tid * 16; b < kTileBytes; b += kThreads * 16) {
                 unsigned int w[4] = {0x78787878u, 0x78787878u, 0x78787878u, 0x78787878u};
-                for (int k = 0; k < 16 && b + k < tile_len; ++k) {
-                    unsigned int by = P.buf[base + b + k];
-                    w[k >> 2] = (w[k >> 2] & ~(0xffu << ((k & 3) * 8))) | (by << ((k & 3) * 8));
+                for (int q = 0; q < 16 && b + q < tile_len; ++q) {
+                    unsigned int by = P.buf[base + b + q];
+                    w[q >> 2] = (w[q >> 2] & ~(0xffu << ((q & 3) * 8))) | (by << ((q & 3) * 8));
                 }
                 S.tile[cur][b >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
             }
+            __syncthreads();
         }
-        __syncthreads();
         if (bulk) mbar_wait(&S.mbar[cur], (it >> 1) & 1u);
 
-        // ---- 1. main pass: 16 bytes per lane per step
+        // ---- 1. main pass: 16 bytes per lane per step, SWAR only.  Per chunk: byte range, "has a
+        //         byte < 0x41" / "< 0x21" ballot rows, list of the chunks with a byte < 0x21 (the only
+        //         ones that can hold a '\n'), literal filter.
+        unsigned int wcount = 0;
         {
-            unsigned int hi_acc = 0, wcount = 0;
-            unsigned short *my_list = S.wl[warp];
+            unsigned int hi_acc = 0;
 #pragma unroll
             for (int j = 0; j < kChunksPerThread; ++j) {
                 const int c = warp * kWarpChunks + j * 32 + lane;
                 const uint4 x = tile[c];
-                // bytes >= 0x7f anywhere
-                hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);
+                hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);     // bytes >= 0x7f anywhere
                 hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
                 hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
                 hi_acc |= x.w | fma_add(x.w, one, 0x01010101u);
-                // bytes < 0x20: count (dp4a over the isolated bit-7 flags = 128 * count)
-                unsigned int n = __dp4a(~fma_add(x.x, one, kAdd20) & kHi, 0x01010101u, 0u);
-                n = __dp4a(~fma_add(x.y, one, kAdd20) & kHi, 0x01010101u, n);
-                n = __dp4a(~fma_add(x.z, one, kAdd20) & kHi, 0x01010101u, n);
-                n = __dp4a(~fma_add(x.w, one, kAdd20) & kHi, 0x01010101u, n);
-                n >>= 7;
                 const bool s_any = ((fma_add(x.x, one, kAdd41) & fma_add(x.y, one, kAdd41) & fma_add(x.z, one, kAdd41) &
                                      fma_add(x.w, one, kAdd41)) & kHi) != kHi;
                 const bool q_any = ((fma_add(x.x, one, kAdd21) & fma_add(x.y, one, kAdd21) & fma_add(x.z, one, kAdd21) &
                                      fma_add(x.w, one, kAdd21)) & kHi) != kHi;
                 const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
                 const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
-                const unsigned int nb = __ballot_sync(0xffffffffu, n != 0);
-                S.cnt[c] = (unsigned char)n;
-                S.sbits[c >> 5] = sb;                     // same word, same value from every lane
-                S.qbits[c >> 5] = qb;
-                if (n) my_list[wcount + __popc(nb & lt_mask)] = (unsigned short)c;
-                wcount += __popc(nb);
+                if (lane == 0) { S.sbits[c >> 5] = sb; S.qbits[c >> 5] = qb; }
+                if (q_any) my_list[wcount + __popc(qb & lt_mask)] = (unsigned short)c;
+                wcount += __popc(qb);
                 if (LM == 8) {
                     const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
                     const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
                     const bool c0 = S.lit_fp[r0 >> 26] == r0, c1 = S.lit_fp[r1 >> 26] == r1;
                     if (__any_sync(0xffffffffu, c0 || c1)) {          // rare: keep the hot loop branch-free
-                        if (c0) push_candidate(S, c << 4, S.lit_masks[r0 >> 26]);
-                        if (c1) push_candidate(S, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                        if (c0) push_candidate(S, T, c << 4, S.lit_masks[r0 >> 26]);
+                        if (c1) push_candidate(S, T, (c << 4) + 8, S.lit_masks[r1 >> 26]);
                     }
                 } else if (LM == 1) {
-                    if ((c << 4) < tile_len) filter_small_units(S, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
+                    if ((c << 4) < tile_len) filter_small_units(S, T, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
                 }
             }
-            if (lane == 0) S.wcnt[warp] = wcount;
-            if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(S, FXG_V_BYTE_RANGE);
+            if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(T, FXG_V_BYTE_RANGE);
+        }
+
+        // ---- 2. (warp local) exact '\n' masks of the listed chunks, '\n' count of the warp's segment
+        {
+            __syncwarp();
+            unsigned int cnt = 0;
+            for (unsigned int q = lane; q < wcount; q += 32) {
+                const unsigned int m16 = lin_mask(tile[my_list[q]], kAdd20);
+                my_mask[q] = (unsigned short)m16;
+                cnt += __popc(m16);
+            }
+            cnt = __reduce_add_sync(0xffffffffu, cnt);
+            if (lane == 0) S.wtot[warp] = cnt;
         }
         __syncthreads();
 
-        // ---- 2. block scan of per-chunk counts (kChunksPerThread consecutive chunks per thread)
+        // ---- 3. (warp local) ordered '\n' position table; a line that is exactly "+" anchors the phase
+        unsigned int total;
         {
-            const unsigned int w4 = *reinterpret_cast<const unsigned int *>(&S.cnt[tid * kChunksPerThread]);
-            const unsigned int s = __dp4a(w4, 0x01010101u, 0u);
-            unsigned int inc = s;
+            const unsigned int wt = lane < kWarps ? S.wtot[lane] : 0u;
+            total = __reduce_add_sync(0xffffffffu, wt);
+            unsigned int idx0 = __reduce_add_sync(0xffffffffu, lane < warp ? wt : 0u);
+            unsigned int plus = 0xffffffffu;
+            for (unsigned int q0 = 0; q0 < wcount; q0 += 32) {
+                const unsigned int q = q0 + lane;
+                unsigned int m16 = q < wcount ? (unsigned int)my_mask[q] : 0u;
+                const int cb = q < wcount ? ((int)my_list[q] << 4) : 0;
+                const unsigned int n = __popc(m16);
+                unsigned int inc = n;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
-                if (lane >= d) inc += o;
-            }
-            if (lane == 31) S.warp_sums[warp] = inc;
-            __syncthreads();
-            unsigned int woff = 0, tot = 0;
-#pragma unroll
-            for (int w2 = 0; w2 < kWarps; ++w2) {
-                unsigned int ws = S.warp_sums[w2];
-                if (w2 < warp) woff += ws;
-                tot += ws;
-            }
-            S.pre[tid] = woff + inc - s;
-            if (tid == 0) S.total = tot;
-        }
-        __syncthreads();
-        const unsigned int total = S.total;
-        const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
-        if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(S, FXG_V_DENSE_LINES);
-
-        //      ordered '\n' position table: every warp walks its own list of flagged chunks
-        {
-            const unsigned int nn = S.wcnt[warp];
-            const unsigned short *my_list = S.wl[warp];
-            for (unsigned int q = lane; q < nn; q += 32) {
-                const int c = my_list[q];
-                unsigned int m16 = lin_mask(tile[c], kAdd20);
-                const unsigned int w4 = *reinterpret_cast<const unsigned int *>(&S.cnt[c & ~3]);
-                const int sh = (c & 3) * 8;
-                unsigned int idx = S.pre[c >> 2] + __dp4a(w4 & ((1u << sh) - 1u), 0x01010101u, 0u);
+                for (int d = 1; d < 32; d <<= 1) {
+                    const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                    if (lane >= d) inc += o;
+                }
+                unsigned int idx = idx0 + inc - n;
+                idx0 += __shfl_sync(0xffffffffu, inc, 31);
                 while (m16) {
-                    const int p = (c << 4) + __ffs(m16) - 1;
+                    const int p = cb + __ffs(m16) - 1;
                     m16 &= m16 - 1;
-                    if (tb[p] != '\n') note_violation(S, FXG_V_BYTE_RANGE);
+                    if (tb[p] != '\n') note_violation(T, FXG_V_BYTE_RANGE);
                     if (idx < (unsigned int)kMaxTileLines) S.nlpos[idx] = (unsigned short)p;
+                    if (p >= 2 && tb[p - 1] == '+' && tb[p - 2] == '\n' && idx < plus) plus = idx;
                     ++idx;
                 }
             }
+            if (!REDO) {
+                plus = __reduce_min_sync(0xffffffffu, plus);
+                if (lane == 0 && plus != 0xffffffffu) atomicMin(&T.plus_idx, plus);
+            }
         }
+        const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
+        if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(T, FXG_V_DENSE_LINES);
         __syncthreads();
 
-        // ---- 3. one thread per line.  FASTQ line phase is unknown here, so the flags of the lines
-        //         are OR-ed per (local line index mod 4); tile_finalize_kernel maps them to roles once
-        //         the phase is known.  The stride (512) is a multiple of 4: one class per thread.
-        {
+        // ---- 4. record structure and character classes
+        const unsigned int plus_idx = REDO ? 0xffffffffu : T.plus_idx;
+        if (plus_idx != 0xffffffffu) {
+            // fast path: the phase is taken from the "+" line (role 2): local line i has role (i + r) & 3.
+            // One thread per half record: a structure line (header / plus) and the class line after it
+            // (sequence / quality).  tile_finalize_kernel checks the guess against the global line
+            // number and sends the tile to the REDO launch if it was wrong (only a 1-base read whose
+            // quality line is "+" can cause that).
+            const int r = (int)((2u - plus_idx) & 3u);
+            const int J = (n_tab + r + 2) >> 1;
+            unsigned int viol = 0;
+            for (int j = tid; j < J; j += kThreads) {
+                const int i0 = 2 * j - r, i1 = i0 + 1;
+                const bool upper = (j & 1) == 0;              // (header, sequence) vs (plus, quality)
+                if (i0 >= 1 && i0 < n_tab) {
+                    const int a0 = (int)S.nlpos[i0 - 1] + 1, e0 = (int)S.nlpos[i0];
+                    const int len0 = e0 - a0;
+                    if (upper) {
+                        if (len0 < 1 || tb[a0] != '@') viol |= FXG_V_HEADER_AT;
+                        else if (tb[e0 - 1] == ' ') viol |= FXG_V_HEADER_SPACE;
+                    } else if (len0 != 1 || tb[a0] != '+') viol |= FXG_V_PLUS_LINE;
+                }
+                if (i1 >= 0 && i1 <= n_tab) {
+                    const int a1 = i1 >= 1 ? (int)S.nlpos[i1 - 1] + 1 : 0;
+                    const int b1 = i1 < n_tab ? (int)S.nlpos[i1] : kTileBytes;
+                    if (class_bad(S, tile, a1, b1, upper)) viol |= upper ? FXG_V_SEQ_CLASS : FXG_V_QUAL_CLASS;
+                    if (i1 >= 1 && i1 < n_tab) {
+                        if (upper) { if (b1 - a1 < 1) viol |= FXG_V_EMPTY_SEQ; }
+                        else if (i1 >= 3 && b1 - a1 != (int)S.nlpos[i1 - 2] - (int)S.nlpos[i1 - 3] - 1) viol |= FXG_V_QUAL_LEN;
+                    }
+                }
+            }
+            viol = __reduce_or_sync(0xffffffffu, viol);
+            if (lane == 0 && viol) atomicOr(&T.viol, viol);
+        } else {
+            // generic path (no "+" line in the tile, or REDO): one thread per line, flags OR-ed per
+            // (local line index mod 4); tile_finalize_kernel maps them to roles once the phase is known.
             unsigned int f_own = 0, f_nxt = 0;
             for (int i = tid; i < n_tab; i += kThreads) {
                 unsigned int own, nxt;
@@ -485,21 +558,21 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
             }
             unsigned int v = f_own | (f_nxt << 8);
             v = __reduce_or_sync(0x11111111u << (lane & 3), v);
-            if (lane < 4 && v) atomicOr(&S.cls[lane], v);
+            if (lane < 4 && v) atomicOr(&T.cls[lane], v);
             if (tid == kThreads - 1) {           // bytes after the last '\n': an unterminated line of index n_tab
                 unsigned int ms, mq;
                 range_any2(S, n_tab ? (S.nlpos[n_tab - 1] >> 4) + 1 : 0, kChunks, ms, mq);
                 const unsigned int f = (ms ? kFS : 0u) | (mq ? kFQ : 0u);
-                if (f) atomicOr(&S.cls[n_tab & 3], f);
+                if (f) atomicOr(&T.cls[n_tab & 3], f);
             }
         }
 
-        // ---- 4. verify the literal candidates (phase-free; line hits)
-        if (LM != 0) {
-            const unsigned int nc_all = S.n_cand;
+        // ---- 5. verify the literal candidates (phase-free; line hits)
+        if (LM != 0 && !REDO) {
+            const unsigned int nc_all = T.n_cand;
             if (nc_all <= (unsigned int)kCandCap) {
                 for (unsigned int q = tid; q < nc_all; q += kThreads)
-                    verify_candidate(S, tb, P, base, n_tab, S.cand_off[q], S.cand_mask[q]);
+                    verify_candidate(S, T, tb, P, base, n_tab, S.cand_off[q], S.cand_mask[q]);
             } else {
                 // queue overflow (pattern hits nearly everywhere): rescan the tile and verify in place
                 for (int c = tid; c < kChunks && (c << 4) < tile_len; c += kThreads) {
@@ -507,17 +580,17 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
                     if (LM == 8) {
                         const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
                         const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
-                        if (S.lit_fp[r0 >> 26] == r0) verify_candidate(S, tb, P, base, n_tab, c << 4, S.lit_masks[r0 >> 26]);
-                        if (S.lit_fp[r1 >> 26] == r1) verify_candidate(S, tb, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                        if (S.lit_fp[r0 >> 26] == r0) verify_candidate(S, T, tb, P, base, n_tab, c << 4, S.lit_masks[r0 >> 26]);
+                        if (S.lit_fp[r1 >> 26] == r1) verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> 26]);
                     } else {
                         const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
                         for (int u = 0; u < 16; u += lit_unit) {
                             unsigned int word = wv[u >> 2];
                             unsigned int val = lit_unit == 4 ? word : (lit_unit == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu)
                                                                                      : ((word >> ((u & 3) * 8)) & 0xffu));
-                            for (int k = 0; k < lit_nkeys; ++k)
-                                if ((unsigned int)S.lit_keys[k] == val)
-                                    verify_candidate(S, tb, P, base, n_tab, (c << 4) + u, S.lit_masks[k]);
+                            for (int q = 0; q < lit_nkeys; ++q)
+                                if ((unsigned int)S.lit_keys[q] == val)
+                                    verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + u, S.lit_masks[q]);
                         }
                     }
                 }
@@ -525,27 +598,27 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
         }
         __syncthreads();
 
-        // ---- 5. publish the tile: count, line-class flags, '\n' table, line hits
+        // ---- 6. publish the tile: count, violations / line-class flags, '\n' table, line hits
         {
             uint4 *dst = reinterpret_cast<uint4 *>(P.tile_nl + t * (unsigned long long)kNlStride);
             const uint4 *src = reinterpret_cast<const uint4 *>(S.nlpos);
             for (int q = tid; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
-            if (LM != 0) {
+            const unsigned int any_hit = T.any_hit;
+            if (LM != 0 && !REDO) {
                 unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
                 const int nw = (n_tab >> 5) + 1;               // local line indices 0..n_tab
-                if (tid < nw) hd[tid] = S.any_hit ? S.linehit[tid] : 0u;
+                for (int w = tid; w < nw; w += kThreads) hd[w] = any_hit ? S.linehit[w] : 0u;
             }
             if (tid == 0) {
-                TileInfo ti;
-                ti.total = total;
-                ti.viol = S.viol;
-                ti.cls[0] = (unsigned short)S.cls[0]; ti.cls[1] = (unsigned short)S.cls[1];
-                ti.cls[2] = (unsigned short)S.cls[2]; ti.cls[3] = (unsigned short)S.cls[3];
+                const TileInfo ti = {total, T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),
+                                     {(unsigned short)T.cls[0], (unsigned short)T.cls[1], (unsigned short)T.cls[2], (unsigned short)T.cls[3]}};
                 P.info[t] = ti;
             }
+            __syncthreads();                     // everything of this tile is consumed: the tile buffer may be refilled
+            if (LM != 0 && any_hit) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
         }
-        __syncthreads();                         // everything of this tile is consumed: buffers may be reused
     }
+#undef FXG_TILE_OF
 }
 
 // ---------------------------------------------------------------- kernel 2a: exclusive scan of the tile counts
@@ -639,6 +712,17 @@ struct TileView {
     __device__ long long at(unsigned long long t, int i) const { return i >= 0 ? nl(t, i) : prev_nl(t, -i); }
 };
 
+// 2a': tiles whose guessed phase disagrees with the global line number go to the REDO list
+__global__ void __launch_bounds__(256) tile_phase_check_kernel(const ScanParams P)
+{
+    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= P.ntiles) return;
+    const unsigned int guess = P.info[t].viol >> 16;
+    if (!guess) return;
+    const unsigned long long lb = P.lbase[t] + P.bsum[t / kPrefixSpan];
+    if ((unsigned int)(lb & 3) != guess - 1) P.redo_list[atomicAdd(P.redo_count, 1u)] = (unsigned int)t;
+}
+
 // 2b: one THREAD per tile -- pick the phase, check the lines that straddle the tile's left edge,
 // turn line hits into record hits.
 __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
@@ -651,7 +735,9 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
     const unsigned long long base = t * (unsigned long long)kTileBytes;
     const int r = (int)(lb & 3);
     const int n_tab = ti.total < (unsigned int)kMaxTileLines ? (int)ti.total : kMaxTileLines;
-    unsigned int viol = ti.viol;
+    unsigned int viol = ti.viol & 0xffffu;
+    const unsigned int guess = ti.viol >> 16;            // 0: flags are per (line index mod 4); else guessed phase + 1
+    if (guess && (int)(guess - 1) != r) viol |= FXG_V_DENSE_LINES;   // cannot happen after the REDO launch; never pass silently
 #pragma unroll
     for (int k = 0; k < 4; ++k)                  // lines with local index == k (mod 4) have role (k + r) & 3
         viol |= role_kinds(ti.cls[k] & 0x7fu, (k + r) & 3) | role_kinds(ti.cls[k] >> 8, (k + 1 + r) & 3);
@@ -749,23 +835,24 @@ __global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
 
 size_t scan_smem_bytes() { return sizeof(ScanSmem); }
 
-template <int LM> static cudaError_t launch_scan_tiles(const ScanParams &P, cudaStream_t stream, int dev)
+template <int LM, bool REDO> static cudaError_t launch_scan_tiles(const ScanParams &P, cudaStream_t stream, int dev)
 {
     static bool attr_set[64] = {false};
     static int grid_cap[64] = {0};
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
     if (!attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(scan_tiles_kernel<LM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
+        cudaError_t e = cudaFuncSetAttribute(scan_tiles_kernel<LM, REDO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
         if (e != cudaSuccess) return e;
         int sms = 0, per_sm = 0;
         if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_tiles_kernel<LM>, kThreads, sizeof(ScanSmem))) != cudaSuccess) return e;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_tiles_kernel<LM, REDO>, kThreads, sizeof(ScanSmem))) != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
         grid_cap[dev] = sms * per_sm;            // persistent CTAs: one wave, 148 SMs x 2 on B200
         attr_set[dev] = true;
     }
-    const unsigned long long grid = P.ntiles < (unsigned long long)grid_cap[dev] ? P.ntiles : (unsigned long long)grid_cap[dev];
-    scan_tiles_kernel<LM><<<(unsigned int)grid, kThreads, sizeof(ScanSmem), stream>>>(P);
+    unsigned long long grid = P.ntiles < (unsigned long long)grid_cap[dev] ? P.ntiles : (unsigned long long)grid_cap[dev];
+    if (REDO && grid > 64) grid = 64;            // the list is normally empty: CTAs beyond its length exit at once
+    scan_tiles_kernel<LM, REDO><<<(unsigned int)grid, kThreads, sizeof(ScanSmem), stream>>>(P);
     return cudaGetLastError();
 }
 
@@ -775,17 +862,20 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
     cudaGetDevice(&dev);
     if (((uintptr_t)P.buf & 15) != 0) return cudaErrorMisalignedAddress;     // bulk copies need 16-byte alignment
     if (P.ntiles == 0) return cudaSuccess;
+    if (P.ntiles > 0xffffffffull) return cudaErrorInvalidValue;
     cudaError_t e;
-    if (!P.match_enabled) e = launch_scan_tiles<0>(P, stream, dev);
-    else if (P.lit_unit == 8) e = launch_scan_tiles<8>(P, stream, dev);
-    else e = launch_scan_tiles<1>(P, stream, dev);
+    if (!P.match_enabled) e = launch_scan_tiles<0, false>(P, stream, dev);
+    else if (P.lit_unit == 8) e = launch_scan_tiles<8, false>(P, stream, dev);
+    else e = launch_scan_tiles<1, false>(P, stream, dev);
     if (e != cudaSuccess) return e;
     if (after_scan) cudaEventRecord(after_scan, stream);
     const unsigned int nblk = (unsigned int)((P.ntiles + kPrefixSpan - 1) / kPrefixSpan);
     tile_prefix_local_kernel<<<nblk, kPrefixThreads, 0, stream>>>(P);
     tile_prefix_blocks_kernel<<<1, kPrefixThreads, 0, stream>>>(P, nblk);
+    tile_phase_check_kernel<<<(unsigned int)((P.ntiles + 255) / 256), 256, 0, stream>>>(P);
+    if ((e = launch_scan_tiles<0, true>(P, stream, dev)) != cudaSuccess) return e;
     tile_finalize_kernel<<<(unsigned int)((P.ntiles + 255) / 256), 256, 0, stream>>>(P);
-    if (launches) *launches += 4;
+    if (launches) *launches += 6;
     if (P.rec_start || P.fld_off) {
         tile_emit_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
         if (launches) *launches += 1;

@@ -208,3 +208,35 @@ def test_synth_device_equals_host_and_planting(fx):
     assert r.canonical_ok == 1 and r.n_records == 5000
     assert r.n_selected == want and 150 < want < 400
     ctx.close()
+
+
+def test_phase_guess_redo_path(fx):
+    """1-base reads whose quality line is "+" make the tile-local phase anchor (a line that is
+    exactly "+") ambiguous: tiles that anchor on the quality line are re-evaluated by the REDO
+    launch.  Output must still equal the oracle's, and real defects must still be caught."""
+    rng = random.Random(9)
+    recs = []
+    for i in range(30000):
+        name = "n%d_%s" % (i, "x" * rng.randint(20, 40))
+        if rng.random() < 0.7:
+            recs.append("@%s\n%s\n+\n+\n" % (name, rng.choice("ACGT")))
+        else:
+            n = rng.randint(2, 60)
+            recs.append("@%s\n%s\n+\n%s\n" % (name, helpers.rand_dna(rng, n), "+" * n))
+    data = "".join(recs).encode()
+    assert len(data) > 20 * 32768
+    for pat in (b"GATT", b"A", b"n77_"):
+        tgt = 1 if pat.startswith(b"n") else 0
+        flags = "H" if tgt else ""
+        pats = [pat, fxoracle.revcomp(pat)] if tgt else [pat]
+        want = fxoracle.run(data, flags, pattern=pat)
+        got = run_raw(fx, data, fx.MODE_LITERAL, pats, target=tgt)
+        assert got["ok"] == 1, got["violation"]
+        assert got["out"] == want
+    bad = data.replace(b"\n+\n+\n@n15000_", b"\n+\n++\n@n15000_", 1)
+    if bad != data:
+        got = run_raw(fx, bad, fx.MODE_LITERAL, [b"GATT"], count_only=True)
+        assert got["ok"] == 0
+    bad = data[:500000] + data[500000:].replace(b"\nA\n+\n+\n", b"\n9\n+\n+\n", 1)
+    got = run_raw(fx, bad, fx.MODE_LITERAL, [b"GATT"], count_only=True)
+    assert got["ok"] == 0
