@@ -42,6 +42,8 @@ struct fxg_ctx {
     fxg::LiteralTable *d_lit = nullptr;
     uint8_t *d_pat = nullptr; uint32_t *d_patoff = nullptr;
     uint8_t *d_cls = nullptr; int *d_next = nullptr; int *d_out = nullptr; int ac_ncls = 0, ac_nstates = 0;
+    unsigned int *d_kfilter = nullptr, *d_kkey = nullptr, *d_kval = nullptr;      // packed k-mer index (ACGT pattern sets)
+    unsigned int k_mask = 0, k_kmask = 0; int k_k = 0, k_stride = 0; bool kmer_ok = false;
     unsigned long long *d_slot_hash = nullptr; int *d_slot_pat = nullptr; unsigned int exact_mask = 0;
     // scan resources (shared; everything is ordered on one stream)
     size_t cap_bytes = 0; size_t rec_cap = 0; size_t ntiles_cap = 0; size_t nblocks_cap = 0;
@@ -49,7 +51,7 @@ struct fxg_ctx {
     unsigned long long *d_lbase = nullptr, *d_bsum = nullptr;
     unsigned int *d_redo = nullptr;      // [ntiles] list + [1] count at index ntiles_cap
     fxg::ScanCounters *d_ctr = nullptr; unsigned int *d_hitbits = nullptr;
-    unsigned long long *d_rec_start = nullptr, *d_fld_off = nullptr, *d_block_sums = nullptr, *d_counts = nullptr;
+    unsigned long long *d_fld_off = nullptr, *d_block_sums = nullptr, *d_counts = nullptr;
     unsigned int *d_fld_len = nullptr;
     // host path
     uint8_t *d_in = nullptr; size_t d_in_cap = 0;
@@ -203,6 +205,55 @@ static int build_ac(fxg_ctx *ctx)
     return FXG_OK;
 }
 
+// ---------------------------------------------------------------- packed k-mer index (host build)
+// Usable when every pattern is a string over {A,C,G,T} of length >= 12 (fxg_common.cuh: KmerDevice).
+static int build_kmer(fxg_ctx *ctx)
+{
+    ctx->kmer_ok = false;
+    const uint32_t n = ctx->npat;
+    uint32_t minlen = 0xffffffffu;
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t len = ctx->off[i + 1] - ctx->off[i];
+        if (len < minlen) minlen = len;
+        for (uint32_t j = ctx->off[i]; j < ctx->off[i + 1]; ++j) if (!fxg_is_acgt(ctx->blob[j])) return FXG_OK;
+    }
+    if (n == 0 || minlen < 12) return FXG_OK;
+    const int k = minlen < 16 ? (int)minlen : 16;
+    int stride = (int)minlen - k + 1;                 // any stride <= min length - k + 1 is complete; the kernel has 1, 2 and 4
+    stride = stride >= 4 ? 4 : (stride >= 2 ? 2 : 1);
+    const unsigned int kmask = k == 16 ? 0xffffffffu : ((1u << (2 * k)) - 1u);
+    size_t entries = (size_t)n * (size_t)stride, nslots = 16;
+    while (nslots < entries * 2) nslots <<= 1;
+    if (nslots > ((size_t)1 << 30)) return FXG_OK;
+    std::vector<unsigned int> filter(kKmerFilterWords, 0u), hk(nslots, 0u), hv(nslots, 0u);
+    const unsigned int mask = (unsigned int)(nslots - 1);
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint8_t *p = ctx->blob.data() + ctx->off[i];
+        for (int o = 0; o < stride; ++o) {
+            unsigned int key = 0;
+            for (int b = 0; b < k; ++b) key = ((key << 2) | fxg_base_code(p[o + b])) & kmask;
+            const unsigned int h = fxg_kmer_hash(key);
+            const unsigned int fb = h >> (32 - kKmerFilterBits);
+            filter[fb >> 5] |= 1u << (fb & 31);
+            const unsigned int gb = fxg_kmer_hash2(key) >> (32 - kKmerFilterBits);
+            filter[gb >> 5] |= 1u << (gb & 31);
+            unsigned int slot = (h >> 7) & mask;
+            while (hv[slot]) slot = (slot + 1) & mask;
+            hk[slot] = key; hv[slot] = ((i << 5) | (unsigned int)o) + 1u;
+        }
+    }
+    if (n >= (1u << 26)) return FXG_OK;
+    cudaError_t e;
+    if ((e = dev_realloc(ctx->d_kfilter, filter.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc k-mer filter");
+    if ((e = dev_realloc(ctx->d_kkey, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc k-mer table");
+    if ((e = dev_realloc(ctx->d_kval, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc k-mer table");
+    cudaMemcpy(ctx->d_kfilter, filter.data(), filter.size() * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(ctx->d_kkey, hk.data(), nslots * 4, cudaMemcpyHostToDevice);
+    if ((e = cudaMemcpy(ctx->d_kval, hv.data(), nslots * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload k-mer table");
+    ctx->k_mask = mask; ctx->k_kmask = kmask; ctx->k_k = k; ctx->k_stride = stride; ctx->kmer_ok = true;
+    return FXG_OK;
+}
+
 // ---------------------------------------------------------------- exact table (host build)
 static int build_exact(fxg_ctx *ctx)
 {
@@ -248,7 +299,6 @@ static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
     if (!ctx->d_ctr && (e = dev_realloc(ctx->d_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counters");
     if (!ctx->d_counts && (e = dev_realloc(ctx->d_counts, 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counts");
     if (!ctx->cfg.count_only) {
-        if ((e = dev_realloc(ctx->d_rec_start, rec_cap + 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc record starts");
         if ((e = dev_realloc(ctx->d_block_sums, nblocks)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc block sums");
     }
     if (ctx->cfg.mode != FXG_MODE_LITERAL) {
@@ -315,7 +365,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     memset(&P, 0, sizeof P);
     P.buf = d_buf; P.nbytes = nbytes; P.ntiles = ntiles; P.info = ctx->d_info; P.tile_nl = ctx->d_tile_nl;
     P.tile_hit = ctx->d_tile_hit; P.lbase = ctx->d_lbase; P.bsum = ctx->d_bsum; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
-    P.rec_start = emit ? ctx->d_rec_start : nullptr; P.rec_cap = rec_cap; P.one = 1;
+    P.rec_cap = rec_cap; P.one = 1;
     P.redo_list = ctx->d_redo; P.redo_count = ctx->d_redo + ctx->ntiles_cap;
     P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
@@ -329,7 +379,10 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
         src.base = d_buf; src.off64 = ctx->d_fld_off; src.len32 = ctx->d_fld_len; src.n_lines_dev = &ctx->d_ctr->n_lines;
         FieldOut O; memset(&O, 0, sizeof O);
         O.hitbits = ctx->d_hitbits; O.n_hits = &ctx->d_ctr->n_hits;
-        if (ctx->cfg.mode == FXG_MODE_MULTI) {
+        if (ctx->cfg.mode == FXG_MODE_MULTI && ctx->kmer_ok) {
+            KmerDevice K{ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_pat, ctx->d_patoff, ctx->k_mask, ctx->k_kmask, ctx->k_k, ctx->k_stride};
+            FXG_CUDA_OK(launch_fields_kmer(src, rec_cap, K, O, st));
+        } else if (ctx->cfg.mode == FXG_MODE_MULTI) {
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
             FXG_CUDA_OK(launch_fields_ac(src, rec_cap, A, O, st));
         } else {
@@ -341,7 +394,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     if (emit) {
         int inv = ctx->cfg.invert ? 1 : 0;
         if (literal && ctx->h_lit.all_match) inv ^= 1;     // every record matches: hit bits stay 0
-        FXG_CUDA_OK(launch_compact(ctx->d_hitbits, ctx->d_rec_start, ctx->d_ctr, rec_cap, ctx->d_block_sums, ctx->d_counts,
+        FXG_CUDA_OK(launch_compact(ctx->d_hitbits, P, ctx->d_ctr, rec_cap, ctx->d_block_sums, ctx->d_counts,
                                    s.d_runs, s.d_runs_cap, inv, st, &ctx->last_launches));
         if (ctx->profiling) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
         FXG_CUDA_OK(cudaMemcpyAsync(s.h_counts, ctx->d_counts, 16, cudaMemcpyDeviceToHost, st));
@@ -449,8 +502,8 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.done) cudaEventDestroy(s.done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat,
-                   ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_rec_start, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
+    void *dev[] = {ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat,
+                   ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_in, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -479,7 +532,7 @@ extern "C" int fxg_set_patterns(fxg_ctx *ctx, const uint8_t *blob, const uint32_
         if (!ctx->d_lit && (e = dev_realloc(ctx->d_lit, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc literal table");
         if ((e = cudaMemcpy(ctx->d_lit, &ctx->h_lit, sizeof(LiteralTable), cudaMemcpyHostToDevice)) != cudaSuccess)
             return set_cuda_error(ctx, e, "upload literal table");
-    } else if (ctx->cfg.mode == FXG_MODE_MULTI) rc = build_ac(ctx);
+    } else if (ctx->cfg.mode == FXG_MODE_MULTI) { rc = build_ac(ctx); if (rc == FXG_OK) rc = build_kmer(ctx); }
     else rc = build_exact(ctx);
     if (rc == FXG_OK) ctx->have_patterns = true;
     return rc;
@@ -600,6 +653,9 @@ extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *of
             L.n_patterns = (int)std::min<uint32_t>(ctx->npat, 2);
             for (int q = 0; q < L.n_patterns; ++q) { L.pat[q] = ctx->d_pat + ctx->off[q]; L.len[q] = (int)(ctx->off[q + 1] - ctx->off[q]); }
             FXG_CUDA_OK(launch_fields_literal(src, nrec, L, O, st));
+        } else if (ctx->cfg.mode == FXG_MODE_MULTI && ctx->kmer_ok && !ctx->cfg.want_pattern_id) {
+            KmerDevice K{ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_pat, ctx->d_patoff, ctx->k_mask, ctx->k_kmask, ctx->k_k, ctx->k_stride};
+            FXG_CUDA_OK(launch_fields_kmer(src, nrec, K, O, st));
         } else if (ctx->cfg.mode == FXG_MODE_MULTI) {
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
             FXG_CUDA_OK(launch_fields_ac(src, nrec, A, O, st));

@@ -78,7 +78,6 @@ struct ScanParams {
     unsigned long long *bsum;         // [ntiles / 4096 + 1] '\n' count before each span
     ScanCounters *ctr;
     unsigned int *hitbits;            // 1 bit per record
-    unsigned long long *rec_start;    // [rec_cap + 1] or nullptr (count-only)
     unsigned long long rec_cap;
     const LiteralTable *lit;          // device copy
     const uint8_t *pat_bytes;         // device copy of pattern bytes
@@ -101,6 +100,28 @@ struct AcDevice {              // byte-class compressed Aho-Corasick DFA
     int ncls;
     int nstates;
 };
+// Packed 2-bit k-mer index for pattern sets over {A,C,G,T} (north_star: "packed 2-bit k-mer hash for the ACGT
+// alphabet").  Every pattern contributes its first `stride` k-mers (offsets 0..stride-1, stride = min pattern
+// length - k + 1), so an occurrence is found by probing every stride-th text position only.  Probe = two bits of a
+// 2^19-bit filter held in shared memory, then an open-addressing table in L2, then byte verification.
+constexpr int kKmerFilterBits = 19;
+constexpr int kKmerFilterWords = 1 << (kKmerFilterBits - 5);
+struct KmerDevice {
+    const unsigned int *filter;            // [kKmerFilterWords]
+    const unsigned int *ht_key;            // [nslots] packed k-mer
+    const unsigned int *ht_val;            // [nslots] 0 = empty, else ((pattern id << 5) | offset) + 1
+    const uint8_t *blob;                   // pattern bytes
+    const unsigned int *off;               // [n+1]
+    unsigned int ht_mask;                  // nslots - 1
+    unsigned int kmask;                    // (1 << 2k) - 1
+    int k, stride;
+};
+// code of a base: A 0, C 1, T 2, G 3 ((byte >> 1) & 3); identical on host and device
+__host__ __device__ inline unsigned int fxg_base_code(unsigned int b) { return (b >> 1) & 3u; }
+__host__ __device__ inline bool fxg_is_acgt(unsigned int b) { return b == 'A' || b == 'C' || b == 'G' || b == 'T'; }
+__host__ __device__ inline unsigned int fxg_kmer_hash(unsigned int key) { return key * 0x9E3779B1u; }
+__host__ __device__ inline unsigned int fxg_kmer_hash2(unsigned int key) { return (key ^ (key >> 15)) * 0x85EBCA6Bu; }
+
 struct ExactDevice {           // open-addressing table over whole-field keys
     const unsigned long long *slot_hash;   // [nslots] 0 = empty
     const int *slot_pat;                   // [nslots] pattern id
@@ -154,12 +175,13 @@ struct LiteralFieldParams {
 // launchers (fxg_scan.cu / fxg_fields.cu / fxg_synth.cu)
 size_t scan_smem_bytes();
 cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launches, cudaEvent_t after_scan);
-cudaError_t launch_compact(const unsigned int *hitbits, const unsigned long long *rec_start, const ScanCounters *ctr,
+cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
                            fxg_run *runs, unsigned long long run_cap, int invert, cudaStream_t stream, int *launches);
 cudaError_t launch_fields_literal(const FieldSrc &src, unsigned long long n, const LiteralFieldParams &L,
                                   const FieldOut &O, cudaStream_t st);
 cudaError_t launch_fields_ac(const FieldSrc &src, unsigned long long n, const AcDevice &A, const FieldOut &O, cudaStream_t st);
+cudaError_t launch_fields_kmer(const FieldSrc &src, unsigned long long n, const KmerDevice &K, const FieldOut &O, cudaStream_t st);
 cudaError_t launch_fields_exact(const FieldSrc &src, unsigned long long n, const ExactDevice &E, const FieldOut &O, cudaStream_t st);
 cudaError_t launch_synth(const fxg_synth_spec &s, uint8_t *d_out, cudaStream_t st);
 

@@ -106,6 +106,130 @@ __global__ void __launch_bounds__(256) fields_ac_kernel(FieldSrc src, unsigned l
     }
 }
 
+// ---------------------------------------------------------------- multi, ACGT pattern sets: packed 2-bit k-mer index
+// Any-hit only (no first-hit pattern id): used when the caller does not route records per pattern.
+// One thread per field rolls a 2-bit packed k-mer over the field from 16-byte aligned loads; every
+// stride-th position probes a 2^19-bit filter in shared memory; filter hits go to the open-addressing
+// table (L2) and candidates are verified byte by byte, so there are no false positives.
+__device__ __noinline__ bool kmer_verify(const KmerDevice &K, unsigned int key, const uint8_t *kstart, const uint8_t *p,
+                                            const uint8_t *end)
+{
+    const unsigned int h = fxg_kmer_hash(key);
+    unsigned int slot = (h >> 7) & K.ht_mask;
+    for (;;) {
+        const unsigned int v = __ldg(&K.ht_val[slot]);
+        if (!v) return false;
+        if (__ldg(&K.ht_key[slot]) == key) {
+            const unsigned int q = (v - 1u) >> 5, o = (v - 1u) & 31u;
+            const unsigned int a = K.off[q], m = K.off[q + 1] - a;
+            const uint8_t *ts = kstart - o;
+            if (ts >= p && ts + m <= end) {
+                bool eq = true;
+                for (unsigned int i = 0; i < m; ++i) if (ts[i] != K.blob[a + i]) { eq = false; break; }
+                if (eq) return true;
+            }
+        }
+        slot = (slot + 1) & K.ht_mask;
+    }
+}
+
+// One thread per field.  The field is read with 16-byte aligned loads (one chunk prefetched ahead) and
+// walked in FIELD-RELATIVE 4-byte words -- funnel shift of two neighbouring aligned words by the byte
+// misalignment of the field start -- so that all lanes run the same instruction stream whatever the
+// alignment of their field: per word a SWAR "four bases?" test, one multiply to pack the four 2-bit
+// codes, and S-strided probes of a two-hash filter in shared memory.  S = probe stride (1, 2 or 4).
+__device__ __forceinline__ unsigned int pick_word(const uint4 &x, int i)
+{
+    return i == 0 ? x.x : (i == 1 ? x.y : (i == 2 ? x.z : x.w));
+}
+__device__ __forceinline__ bool kmer_probe(const unsigned int *filt, const KmerDevice &K, unsigned int key, const uint8_t *kend,
+                                           const uint8_t *p, const uint8_t *end)
+{
+    const unsigned int h = fxg_kmer_hash(key) >> (32 - kKmerFilterBits);
+    const unsigned int g = fxg_kmer_hash2(key) >> (32 - kKmerFilterBits);
+    if (!((filt[h >> 5] >> (h & 31)) & (filt[g >> 5] >> (g & 31)) & 1u)) return false;
+    return kmer_verify(K, key, kend - (K.k - 1), p, end);
+}
+
+#ifndef FXG_KM_THREADS
+#define FXG_KM_THREADS 384
+#endif
+#ifndef FXG_KM_CTAS
+#define FXG_KM_CTAS 3
+#endif
+template <int S>
+__global__ void __launch_bounds__(FXG_KM_THREADS, FXG_KM_CTAS) fields_kmer_kernel(FieldSrc src, unsigned long long n, KmerDevice K, FieldOut O)
+{
+    extern __shared__ __align__(16) unsigned int filt[];
+    for (int i = threadIdx.x; i < kKmerFilterWords; i += blockDim.x) filt[i] = K.filter[i];
+    __syncthreads();
+    n = src.count(n);
+    const unsigned long long stride_n = (unsigned long long)gridDim.x * blockDim.x;
+    const unsigned long long nround = (n + 31) & ~31ull;
+    const int k = K.k;
+    const unsigned int kmask = K.kmask;
+    const int j0 = (k - 1) & (S - 1);                  // probe positions inside a field-relative word: j0, j0 + S, ...
+    for (unsigned long long f = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; f < nround; f += stride_n) {
+        bool hit = false;
+        const uint8_t *p = src.base; unsigned int len = 0;
+        if (f < n) src.get(f, p, len);
+        if (len >= (unsigned int)(k + S - 1)) {
+            const uint8_t *end = p + len;
+            const uint8_t *ca = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)15);      // address of the chunk in xc
+            const int sh = (int)((uintptr_t)p & 3) * 8;
+            int ci = (int)(((uintptr_t)p & 15) >> 2);                                   // aligned word of xc that holds `lo`
+            uint4 xc = __ldg(reinterpret_cast<const uint4 *>(ca));
+            uint4 xn = ca + 16 < end ? __ldg(reinterpret_cast<const uint4 *>(ca + 16)) : xc;
+            unsigned int lo = pick_word(xc, ci);
+            unsigned int key = 0;
+            int run = 0;
+            const int nwords = (int)(len >> 2);
+            for (int r = 0; r <= nwords && !hit; ++r) {
+                if (++ci == 4) {                       // step to the next chunk; keep one more in flight
+                    ci = 0; ca += 16; xc = xn;
+                    if (ca + 16 < end) xn = __ldg(reinterpret_cast<const uint4 *>(ca + 16));
+                }
+                const unsigned int hi = pick_word(xc, ci);
+                const unsigned int w = __funnelshift_r(lo, hi, sh);
+                lo = hi;
+                const uint8_t *wa = p + 4 * r;
+                const unsigned int codes = (w >> 1) & 0x03030303u;
+                const unsigned int l1 = codes & 0x01010101u, h1 = (codes >> 1) & 0x01010101u;
+                const unsigned int expect = 0x41414141u + l1 * 2u + h1 * 0x13u - (l1 & h1) * 0x0fu;
+                if (r < nwords && expect == w) {                        // four bases inside the field
+                    const unsigned int c4 = (codes * 0x40100401u) >> 24;
+                    if (S == 4) {
+                        if (run + j0 + 1 >= k &&
+                            kmer_probe(filt, K, ((key << (2 * j0 + 2)) | (c4 >> (6 - 2 * j0))) & kmask, wa + j0, p, end)) hit = true;
+                    } else if (S == 2) {
+                        if (run + j0 + 1 >= k &&
+                            kmer_probe(filt, K, ((key << (2 * j0 + 2)) | (c4 >> (6 - 2 * j0))) & kmask, wa + j0, p, end)) hit = true;
+                        if (run + j0 + 3 >= k &&
+                            kmer_probe(filt, K, ((key << (2 * j0 + 6)) | (c4 >> (2 - 2 * j0))) & kmask, wa + j0 + 2, p, end)) hit = true;
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (run + j + 1 >= k &&
+                                kmer_probe(filt, K, ((key << (2 * j + 2)) | (c4 >> (6 - 2 * j))) & kmask, wa + j, p, end)) hit = true;
+                    }
+                    key = ((key << 8) | c4) & kmask;
+                    run += 4;
+                } else {                                                // a non-base byte, or the field's last 0..3 bytes
+                    const int lim = r < nwords ? 4 : (int)(len & 3);
+                    for (int j = 0; j < lim; ++j) {
+                        const unsigned int b = (w >> (8 * j)) & 0xffu;
+                        if (!fxg_is_acgt(b)) { run = 0; continue; }
+                        key = ((key << 2) | fxg_base_code(b)) & kmask;
+                        ++run;
+                        if (((j - j0) & (S - 1)) == 0 && run >= k && kmer_probe(filt, K, key, wa + j, p, end)) hit = true;
+                    }
+                }
+            }
+        }
+        emit_thread_per_field(O, f, n, hit, -1);
+    }
+}
+
 // ---------------------------------------------------------------- exact: thread per field, hash probe + verify
 __global__ void __launch_bounds__(256) fields_exact_kernel(FieldSrc src, unsigned long long n, ExactDevice E, FieldOut O)
 {
@@ -160,6 +284,24 @@ cudaError_t launch_fields_ac(const FieldSrc &src, unsigned long long n, const Ac
     if (n == 0) return cudaSuccess;
     fields_ac_kernel<<<grid_for(n, 256), 256, 0, st>>>(src, n, A, O);
     return cudaGetLastError();
+}
+template <int S> static cudaError_t launch_fields_kmer_s(const FieldSrc &src, unsigned long long n, const KmerDevice &K,
+                                                         const FieldOut &O, cudaStream_t st)
+{
+    const int smem = kKmerFilterWords * (int)sizeof(unsigned int);
+    cudaError_t e = cudaFuncSetAttribute(fields_kmer_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   // per device
+    if (e != cudaSuccess) return e;
+    unsigned long long b = (n + FXG_KM_THREADS - 1) / FXG_KM_THREADS;
+    if (b > 148ull * FXG_KM_CTAS) b = 148ull * FXG_KM_CTAS;            // persistent CTAs: the filter is loaded once per CTA
+    fields_kmer_kernel<S><<<(unsigned int)b, FXG_KM_THREADS, smem, st>>>(src, n, K, O);
+    return cudaGetLastError();
+}
+cudaError_t launch_fields_kmer(const FieldSrc &src, unsigned long long n, const KmerDevice &K, const FieldOut &O, cudaStream_t st)
+{
+    if (n == 0) return cudaSuccess;
+    if (K.stride >= 4) return launch_fields_kmer_s<4>(src, n, K, O, st);
+    if (K.stride >= 2) return launch_fields_kmer_s<2>(src, n, K, O, st);
+    return launch_fields_kmer_s<1>(src, n, K, O, st);
 }
 cudaError_t launch_fields_exact(const FieldSrc &src, unsigned long long n, const ExactDevice &E, const FieldOut &O, cudaStream_t st)
 {

@@ -810,7 +810,6 @@ __global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
         const int ph = (int)(j & 3);
         const unsigned long long rec = j >> 2;
         const long long pos = V.nl(t, i);
-        if (ph == 3 && P.rec_start && rec + 1 <= P.rec_cap) P.rec_start[rec + 1] = (unsigned long long)(pos + 1);
         if (P.fld_off && rec < P.rec_cap) {
             if ((ph == 3 && P.target == FXG_TARGET_QUAL) || (ph == 1 && P.target == FXG_TARGET_SEQ)) {
                 const long long prev = V.at(t, i - 1);
@@ -830,7 +829,6 @@ __global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
             }
         }
     }
-    if (t == 0 && lane == 0 && P.rec_start) P.rec_start[0] = 0;
 }
 
 size_t scan_smem_bytes() { return sizeof(ScanSmem); }
@@ -876,7 +874,7 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
     if ((e = launch_scan_tiles<0, true>(P, stream, dev)) != cudaSuccess) return e;
     tile_finalize_kernel<<<(unsigned int)((P.ntiles + 255) / 256), 256, 0, stream>>>(P);
     if (launches) *launches += 6;
-    if (P.rec_start || P.fld_off) {
+    if (P.fld_off) {
         tile_emit_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
         if (launches) *launches += 1;
     }
@@ -885,12 +883,29 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
 
 // ================================================================= K6: flags -> ordered runs
 // sel(k) = hit(k) XOR invert for k < n_records; a run is a maximal block of
-// consecutive selected records; runs[r] = {rec_start[first], rec_start[last+1]-rec_start[first]}.
+// consecutive selected records; runs[r] = {start(first), start(last+1) - start(first)}; record starts are
+// looked up in the tile tables (offset_after_line), not stored per record.
 // Replaces the per-record `pair.print(out)` of on_match (main.cpp:258-271, kseq.cpp:32-48)
 // for canonical FASTQ, where print(parse(bytes)) == bytes.
+// Byte offset just after the '\n' with global index L (L = -1: offset 0): binary search of the tile whose line
+// range holds L (tiles without a '\n' share their base with the next tile: the LAST tile with base <= L holds
+// it), then that tile's position table.
+__device__ unsigned long long offset_after_line(const ScanParams &P, long long L)
+{
+    if (L < 0) return 0ull;
+    unsigned long long lo = 0, hi = P.ntiles;
+    while (hi - lo > 1) {
+        const unsigned long long mid = (lo + hi) >> 1;
+        if (P.lbase[mid] + P.bsum[mid / kPrefixSpan] <= (unsigned long long)L) lo = mid; else hi = mid;
+    }
+    const unsigned long long k = (unsigned long long)L - (P.lbase[lo] + P.bsum[lo / kPrefixSpan]);
+    if (k >= (unsigned long long)kMaxTileLines) return 0ull;        // dense tile: the batch is rejected anyway
+    return lo * (unsigned long long)kTileBytes + P.tile_nl[lo * (unsigned long long)kNlStride + k] + 1ull;
+}
+
 struct CompactParams {
     const unsigned int *hitbits;
-    const unsigned long long *rec_start;
+    ScanParams P;                   // tile tables for the record-boundary look-ups
     const ScanCounters *ctr;        // n_lines -> n_records
     unsigned long long *block_sums; // [nblocks] run starts per block -> exclusive prefix
     unsigned long long *out_counts; // [0] = n_runs, [1] = n_selected
@@ -981,12 +996,12 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
         m &= m - 1;
         unsigned long long rec = w * 32ull + b;
         if (starts & (1u << b)) {
-            if (opened < C.run_cap) C.runs[opened].off = C.rec_start[rec];
+            if (opened < C.run_cap) C.runs[opened].off = offset_after_line(C.P, 4ll * (long long)rec - 1);
             ++opened;
         }
         if (ends & (1u << b)) {
             unsigned long long r = opened - 1;
-            if (r < C.run_cap) C.runs[r].len = C.rec_start[rec + 1];   // end offset; fixed up below
+            if (r < C.run_cap) C.runs[r].len = offset_after_line(C.P, 4ll * (long long)rec + 3);   // end offset; fixed up below
         }
     }
 }
@@ -999,12 +1014,12 @@ __global__ void compact_fixup_kernel(const CompactParams C)
         C.runs[i].len -= C.runs[i].off;
 }
 
-cudaError_t launch_compact(const unsigned int *hitbits, const unsigned long long *rec_start, const ScanCounters *ctr,
+cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
                            fxg_run *runs, unsigned long long run_cap, int invert, cudaStream_t stream, int *launches)
 {
     CompactParams C;
-    C.hitbits = hitbits; C.rec_start = rec_start; C.ctr = ctr; C.block_sums = block_sums;
+    C.hitbits = hitbits; C.P = P; C.ctr = ctr; C.block_sums = block_sums;
     C.out_counts = out_counts; C.runs = runs; C.run_cap = run_cap; C.invert = invert;
     unsigned long long words = (rec_cap + 31) / 32;
     unsigned int nblocks = (unsigned int)((words + kCompactThreads - 1) / kCompactThreads);

@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "_build", "libfxgpu.so")
+LIB_PATH = os.environ.get("FXGPU_LIB") or os.path.join(HERE, "_build", "libfxgpu.so")   # FXGPU_LIB: kernel-variant experiments only
 
 MODE_LITERAL, MODE_MULTI, MODE_EXACT = 0, 1, 2
 TARGET_SEQ, TARGET_NAME, TARGET_COMMENT, TARGET_QUAL = 0, 1, 2, 3

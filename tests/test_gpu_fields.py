@@ -95,3 +95,35 @@ def test_fields_exact(fx, seed):
     want = [lut.get(x, -1) for x in fields]
     assert ids == want
     assert nm == sum(1 for w in want if w >= 0)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_fields_multi_kmer_index(fx, seed):
+    """ACGT pattern sets of length >= 12 take the packed 2-bit k-mer index (any-hit, no pattern ids):
+    flags must equal plain substring search, also for hits at field edges, across non-ACGT bytes and for
+    back-to-back packed fields (no k-mer may straddle two fields)."""
+    rng = random.Random(300 + seed)
+    minlen = rng.choice([12, 13, 16, 17, 20, 24, 31])
+    pats = sorted(set(bytes(rng.choice(b"ACGT") for _ in range(rng.randint(minlen, minlen + rng.choice([0, 3, 20]))))
+                      for _ in range(rng.choice([1, 7, 300, 5000]))))
+    alpha = b"ACGT" if seed % 2 == 0 else b"ACGTACGTACGTNacgt"
+    fields = rand_fields(rng, rng.choice([40, 2000]), alpha, 0, 260)
+    for i in range(0, len(fields), 3):                   # plant: start, end, middle, split across two fields
+        p = rng.choice(pats)
+        f = fields[i]
+        mode = rng.randint(0, 3)
+        if mode == 0:
+            fields[i] = p + f
+        elif mode == 1:
+            fields[i] = f + p
+        elif mode == 2:
+            c = rng.randint(0, len(f))
+            fields[i] = f[:c] + p + f[c:]
+        elif i + 1 < len(fields):
+            c = rng.randint(1, len(p) - 1)
+            fields[i] = f + p[:c]
+            fields[i + 1] = p[c:] + fields[i + 1]
+    want = [int(any(p in x for p in pats)) for x in fields]
+    flags, _, nm = run_fields(fx, fx.MODE_MULTI, pats, fields)
+    assert flags == want
+    assert nm == sum(want) and 0 < nm

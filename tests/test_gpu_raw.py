@@ -176,15 +176,26 @@ def test_non_canonical_is_rejected(fx, data, name):
 def test_canonical_edge_shapes(fx):
     # shortest records, '@'/'+' opening quality lines, names without comments, long lines across tiles
     recs = [b"@\nA\n+\nI\n", b"@a\nAC\n+\n@+\n", b"@x y z\nACGTN\n+\n+@+@+\n"]
+    pad = b"@pad 1:N:0\n" + b"ACGT" * 30 + b"\n+\n" + b"I" * 120 + b"\n"     # keeps the line density below 1 per 8 bytes
     big = b"@long\n" + b"ACGT" * 30000 + b"\n+\n" + b"I" * 120000 + b"\n"
-    data = b"".join(recs) * 50 + big + b"".join(recs) * 7 + big * 2
+    grp = b"".join(recs) + pad
+    data = grp * 50 + big + grp * 7 + big * 2
     got = run_raw(fx, data, fx.MODE_LITERAL, [b"GTNXX"], invert=True)
     assert got["ok"] == 1, got
     assert got["out"] == data
-    assert got["n_records"] == 50 * 3 + 1 + 21 + 2
+    assert got["n_records"] == 50 * 4 + 1 + 28 + 2
     want = fxoracle.run(data, "", pattern=b"CGTACGTACGTACGTA")
     got = run_raw(fx, data, fx.MODE_LITERAL, [b"CGTACGTACGTACGTA"])
-    assert got["out"] == want and got["n_selected"] == 3
+    assert got["out"] == want and got["n_records"] == 231
+
+
+def test_dense_lines_are_rerouted_not_misparsed(fx):
+    """More than one line per 8 bytes over a whole tile is outside the raw path's table capacity:
+    the batch must be reported (FXG_V_DENSE_LINES) so the host re-routes it, never mis-parsed."""
+    recs = [b"@\nA\n+\nI\n", b"@a\nAC\n+\n@+\n"]
+    data = b"".join(recs) * 4000
+    got = run_raw(fx, data, fx.MODE_LITERAL, [b"AC"], count_only=True)
+    assert got["ok"] == 0 and got["violation"] & 256, got
 
 
 def test_synth_device_equals_host_and_planting(fx):
@@ -240,3 +251,19 @@ def test_phase_guess_redo_path(fx):
     bad = data[:500000] + data[500000:].replace(b"\nA\n+\n+\n", b"\n9\n+\n+\n", 1)
     got = run_raw(fx, bad, fx.MODE_LITERAL, [b"GATT"], count_only=True)
     assert got["ok"] == 0
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_multi_kmer_raw(fx, seed):
+    """Raw path + k-mer index second stage against the oracle (-f, -rf, -vf on sequences)."""
+    rng = random.Random(400 + seed)
+    data = helpers.make_fastq(rng, rng.choice([300, 6000]), seqlen=(30, 200))
+    pats = sorted(set(helpers.pick_substring(rng, data, lo=14, hi=30) for _ in range(rng.randint(2, 40))) |
+                  set(helpers.rand_dna(rng, 20).encode() for _ in range(50)))
+    pats = [p for p in pats if set(p) <= set(b"ACGT") and len(p) >= 12]
+    both = sorted(set(pats) | set(fxoracle.revcomp(p) for p in pats))
+    pf = b"\n".join(pats) + b"\n"
+    for flags, plist, inv in (("", pats, False), ("r", both, False), ("v", pats, True)):
+        want = fxoracle.run(data, flags, pattern_file=pf)
+        got = run_raw(fx, data, fx.MODE_MULTI, plist, invert=inv)
+        assert got["ok"] == 1 and got["out"] == want, (flags, len(got["out"]), len(want))
