@@ -307,7 +307,7 @@ def run_gpu_arm(args):
     with torch.cuda.stream(stream):
         d = torch.empty(nbytes + 64, dtype=torch.uint8, device="cuda")
         ctx = fx.Context(w["mode"], target=w["target"], invert=bool(w["invert"]), count_only=bool(w["count_only"]),
-                         batch_bytes=args.batch_mib << 20, stream=stream.cuda_stream)
+                         batch_bytes=args.batch_mib << 20, stream=stream.cuda_stream, device=local)
         ctx.set_patterns(pats)
         ctx.synth_device(spec, d.data_ptr())
         ctx.set_profiling(True)
@@ -453,8 +453,8 @@ def run_gpu_arm(args):
         except Exception:
             pass
     if e2e:
-        out["e2e"] = {"value": sums[1] / vals[1] / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(e2e["bytes"]),
-                      "d2h_bytes_per_step": int(e2e["d2h"]), "steps": e2e["steps"], "batch_bytes": args.batch_mib << 20,
+        out["e2e"] = {"value": sums[1] / vals[1] / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(sums[1]),
+                      "d2h_bytes_per_step": int(e2e["d2h"]) * world, "steps": e2e["steps"], "batch_bytes": args.batch_mib << 20,
                       "bytes_per_gpu": int(e2e["bytes"]), "selected_records_rank0": e2e["selected"]}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_leg(fx, w, args.cpu_records)
