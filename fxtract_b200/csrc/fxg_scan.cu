@@ -39,10 +39,10 @@ constexpr int kWarpChunks = kChunks / kWarps;       // chunks one warp covers (c
 
 struct __align__(128) ScanSmem {
     uint4 tile[2][kChunks];                   // staged tile bytes, double buffered (bulk-copy destinations)
-    unsigned short nlpos[kMaxTileLines];      // tile-relative '\n' positions, in order
+    unsigned short nlpos[kMaxTileLines + 16]; // tile-relative '\n' positions, in order (+ slack, see step 3)
     unsigned short wl[kWarps][kWarpChunks];   // per warp: its chunks that contain a byte < 0x21 ('\n' candidates)
     unsigned short wm[kWarps][kWarpChunks];   // per entry of wl: 16-bit mask of the bytes < 0x20 of that chunk
-    unsigned int wtot[kWarps];                // '\n' count of each warp's 2 KiB segment
+    unsigned int wtot[2][kWarps];             // '\n' count of each warp's 2 KiB segment (by tile parity)
     unsigned int below[17];                   // interleaved-layout mask of the bytes < p of a chunk
     unsigned int sbits[kChunks / 32];         // bit c: chunk c has a byte < 0x41 (not a sequence letter)
     unsigned int qbits[kChunks / 32];         // bit c: chunk c has a byte < 0x21 (not a quality char)
@@ -58,13 +58,12 @@ struct __align__(128) ScanSmem {
     struct TileState {
         unsigned int cls[4];                  // generic path: line flags OR-ed per (local line index mod 4)
         unsigned int n_cand, viol, any_hit;
-        unsigned int plus_idx;                // smallest local index of a line that is exactly "+" (phase anchor)
     } st[2];
 };
 typedef ScanSmem::TileState TileState;
 __device__ __forceinline__ void reset_state(TileState &T)
 {
-    T.n_cand = 0; T.viol = 0; T.any_hit = 0; T.plus_idx = 0xffffffffu;
+    T.n_cand = 0; T.viol = 0; T.any_hit = 0;
     T.cls[0] = T.cls[1] = T.cls[2] = T.cls[3] = 0;
 }
 
@@ -340,7 +339,7 @@ __device__ __forceinline__ unsigned int class_bad(const ScanSmem &S, const uint4
 // REDO = second launch over the (normally empty) list of tiles whose locally guessed line phase
 // turned out wrong: those are re-evaluated with the phase-free per-line path.
 template <int LM, bool REDO>
-__global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParams P)
+__global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const ScanParams P)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem &S = *reinterpret_cast<ScanSmem *>(smem_raw);
@@ -442,7 +441,8 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
                                      fma_add(x.w, one, kAdd21)) & kHi) != kHi;
                 const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
                 const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
-                if (lane == 0) { S.sbits[c >> 5] = sb; S.qbits[c >> 5] = qb; }
+                S.sbits[c >> 5] = sb;                                 // warp-uniform address and value: every lane stores
+                S.qbits[c >> 5] = qb;
                 if (q_any) my_list[wcount + __popc(qb & lt_mask)] = (unsigned short)c;
                 wcount += __popc(qb);
                 if (LM == 8) {
@@ -460,31 +460,41 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
             if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(T, FXG_V_BYTE_RANGE);
         }
 
-        // ---- 2. (warp local) exact '\n' masks of the listed chunks, '\n' count of the warp's segment
+        // ---- 2. (warp local) exact '\n' masks of the listed chunks, '\n' count of the warp's segment.  A byte
+        //         below 0x20 that is not '\n' is a violation: y = x ^ 0x0a.. is 0 exactly for '\n' and stays
+        //         below 0x20 for every other control byte, so (y + 0x7f..) has bit 7 set there.
         {
             __syncwarp();
-            unsigned int cnt = 0;
+            unsigned int cnt = 0, ctl = 0;
             for (unsigned int q = lane; q < wcount; q += 32) {
-                const unsigned int m16 = lin_mask(tile[my_list[q]], kAdd20);
+                const uint4 x = tile[my_list[q]];
+                const unsigned int h0 = ~(x.x + kAdd20) & kHi, h1 = ~(x.y + kAdd20) & kHi;
+                const unsigned int h2 = ~(x.z + kAdd20) & kHi, h3 = ~(x.w + kAdd20) & kHi;
+                ctl |= h0 & ((x.x ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
+                ctl |= h1 & ((x.y ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
+                ctl |= h2 & ((x.z ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
+                ctl |= h3 & ((x.w ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
+                const unsigned int m16 = ((h0 * 0x00204081u) >> 28) | (((h1 * 0x00204081u) >> 28) << 4) |
+                                         (((h2 * 0x00204081u) >> 28) << 8) | (((h3 * 0x00204081u) >> 28) << 12);
                 my_mask[q] = (unsigned short)m16;
                 cnt += __popc(m16);
             }
             cnt = __reduce_add_sync(0xffffffffu, cnt);
-            if (lane == 0) S.wtot[warp] = cnt;
+            if (lane == 0) S.wtot[cur][warp] = cnt;
+            if (__any_sync(0xffffffffu, ctl != 0) && lane == 0) note_violation(T, FXG_V_BYTE_RANGE);
         }
         __syncthreads();
 
-        // ---- 3. (warp local) ordered '\n' position table; a line that is exactly "+" anchors the phase
+        // ---- 3. (warp local) ordered '\n' position table
         unsigned int total;
         {
-            const unsigned int wt = lane < kWarps ? S.wtot[lane] : 0u;
+            const unsigned int wt = lane < kWarps ? S.wtot[cur][lane] : 0u;
             total = __reduce_add_sync(0xffffffffu, wt);
             unsigned int idx0 = __reduce_add_sync(0xffffffffu, lane < warp ? wt : 0u);
-            unsigned int plus = 0xffffffffu;
             for (unsigned int q0 = 0; q0 < wcount; q0 += 32) {
                 const unsigned int q = q0 + lane;
                 unsigned int m16 = q < wcount ? (unsigned int)my_mask[q] : 0u;
-                const int cb = q < wcount ? ((int)my_list[q] << 4) : 0;
+                const int cb = q < wcount ? ((int)my_list[q] << 4) - 1 : 0;
                 const unsigned int n = __popc(m16);
                 unsigned int inc = n;
 #pragma unroll
@@ -494,26 +504,32 @@ __global__ void __launch_bounds__(kThreads, 2) scan_tiles_kernel(const ScanParam
                 }
                 unsigned int idx = idx0 + inc - n;
                 idx0 += __shfl_sync(0xffffffffu, inc, 31);
+                // the table has 16 entries of slack: clamping the first index keeps every store inside it
+                unsigned short *dst = &S.nlpos[idx < (unsigned int)kMaxTileLines ? idx : (unsigned int)kMaxTileLines];
                 while (m16) {
-                    const int p = cb + __ffs(m16) - 1;
+                    *dst++ = (unsigned short)(cb + __ffs(m16));
                     m16 &= m16 - 1;
-                    if (tb[p] != '\n') note_violation(T, FXG_V_BYTE_RANGE);
-                    if (idx < (unsigned int)kMaxTileLines) S.nlpos[idx] = (unsigned short)p;
-                    if (p >= 2 && tb[p - 1] == '+' && tb[p - 2] == '\n' && idx < plus) plus = idx;
-                    ++idx;
                 }
-            }
-            if (!REDO) {
-                plus = __reduce_min_sync(0xffffffffu, plus);
-                if (lane == 0 && plus != 0xffffffffu) atomicMin(&T.plus_idx, plus);
             }
         }
         const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
         if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(T, FXG_V_DENSE_LINES);
         __syncthreads();
 
+        // ---- 3b. phase anchor: the first line among local lines 1..31 that is exactly "+" (every warp looks
+        //          for itself -- cheaper than a block-wide minimum and one more barrier)
+        unsigned int plus_idx = 0xffffffffu;
+        if (!REDO) {
+            bool is_plus = false;
+            if (lane >= 1 && lane < n_tab) {
+                const int e = S.nlpos[lane];
+                is_plus = e - (int)S.nlpos[lane - 1] == 2 && tb[e - 1] == '+';
+            }
+            const unsigned int pb = __ballot_sync(0xffffffffu, is_plus);
+            if (pb) plus_idx = (unsigned int)__ffs(pb) - 1u;
+        }
+
         // ---- 4. record structure and character classes
-        const unsigned int plus_idx = REDO ? 0xffffffffu : T.plus_idx;
         if (plus_idx != 0xffffffffu) {
             // fast path: the phase is taken from the "+" line (role 2): local line i has role (i + r) & 3.
             // One thread per half record: a structure line (header / plus) and the class line after it
