@@ -36,6 +36,7 @@ namespace fxg {
 
 constexpr int kWarps = kThreads / 32;
 constexpr int kWarpChunks = kChunks / kWarps;       // chunks one warp covers (contiguous)
+static_assert(kWarps % 4 == 0, "step 4 gives every line role its own warps");
 
 struct __align__(128) ScanSmem {
     uint4 tile[2][kChunks];                   // staged tile bytes, double buffered (bulk-copy destinations)
@@ -532,31 +533,31 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
         // ---- 4. record structure and character classes
         if (plus_idx != 0xffffffffu) {
             // fast path: the phase is taken from the "+" line (role 2): local line i has role (i + r) & 3.
-            // One thread per half record: a structure line (header / plus) and the class line after it
-            // (sequence / quality).  tile_finalize_kernel checks the guess against the global line
-            // number and sends the tile to the REDO launch if it was wrong (only a 1-base read whose
-            // quality line is "+" can cause that).
+            // tile_finalize_kernel checks the guess against the global line number and sends the tile to
+            // the REDO launch if it was wrong (only a 1-base read whose quality line is "+" can cause that).
+            // One thread per LINE, one line role per warp (role = warp & 3), so no lane of a warp diverges from
+            // its neighbours and the longest dependent chain of this step is one class check.
             const int r = (int)((2u - plus_idx) & 3u);
-            const int J = (n_tab + r + 2) >> 1;
+            const int role = warp & 3;                        // 0 header, 1 sequence, 2 plus, 3 quality
+            const int first = (role - r) & 3;                 // smallest local line index with that role
             unsigned int viol = 0;
-            for (int j = tid; j < J; j += kThreads) {
-                const int i0 = 2 * j - r, i1 = i0 + 1;
-                const bool upper = (j & 1) == 0;              // (header, sequence) vs (plus, quality)
-                if (i0 >= 1 && i0 < n_tab) {
-                    const int a0 = (int)S.nlpos[i0 - 1] + 1, e0 = (int)S.nlpos[i0];
-                    const int len0 = e0 - a0;
-                    if (upper) {
-                        if (len0 < 1 || tb[a0] != '@') viol |= FXG_V_HEADER_AT;
-                        else if (tb[e0 - 1] == ' ') viol |= FXG_V_HEADER_SPACE;
-                    } else if (len0 != 1 || tb[a0] != '+') viol |= FXG_V_PLUS_LINE;
-                }
-                if (i1 >= 0 && i1 <= n_tab) {
-                    const int a1 = i1 >= 1 ? (int)S.nlpos[i1 - 1] + 1 : 0;
-                    const int b1 = i1 < n_tab ? (int)S.nlpos[i1] : kTileBytes;
-                    if (class_bad(S, tile, a1, b1, upper)) viol |= upper ? FXG_V_SEQ_CLASS : FXG_V_QUAL_CLASS;
-                    if (i1 >= 1 && i1 < n_tab) {
-                        if (upper) { if (b1 - a1 < 1) viol |= FXG_V_EMPTY_SEQ; }
-                        else if (i1 >= 3 && b1 - a1 != (int)S.nlpos[i1 - 2] - (int)S.nlpos[i1 - 3] - 1) viol |= FXG_V_QUAL_LEN;
+            for (int i = first + 4 * ((warp >> 2) * 32 + lane); i <= n_tab; i += 4 * (kWarps / 4) * 32) {
+                const int a = i >= 1 ? (int)S.nlpos[i - 1] + 1 : 0;
+                const int e = i < n_tab ? (int)S.nlpos[i] : kTileBytes;
+                const bool whole = i >= 1 && i < n_tab;       // line starts and ends inside the tile
+                if (role == 0) {
+                    if (whole) {
+                        if (e - a < 1 || tb[a] != '@') viol |= FXG_V_HEADER_AT;
+                        else if (tb[e - 1] == ' ') viol |= FXG_V_HEADER_SPACE;
+                    }
+                } else if (role == 2) {
+                    if (whole && (e - a != 1 || tb[a] != '+')) viol |= FXG_V_PLUS_LINE;
+                } else {
+                    const bool seq = role == 1;
+                    if (class_bad(S, tile, a, e, seq)) viol |= seq ? FXG_V_SEQ_CLASS : FXG_V_QUAL_CLASS;
+                    if (whole) {
+                        if (seq) { if (e - a < 1) viol |= FXG_V_EMPTY_SEQ; }
+                        else if (i >= 3 && e - a != (int)S.nlpos[i - 2] - (int)S.nlpos[i - 3] - 1) viol |= FXG_V_QUAL_LEN;
                     }
                 }
             }
