@@ -58,13 +58,13 @@ struct __align__(128) ScanSmem {
     // thread 0 while the current one is in use (no extra barrier between "last read" and "first write")
     struct TileState {
         unsigned int cls[4];                  // generic path: line flags OR-ed per (local line index mod 4)
-        unsigned int n_cand, viol, any_hit;
+        unsigned int n_cand, viol;
     } st[2];
 };
 typedef ScanSmem::TileState TileState;
 __device__ __forceinline__ void reset_state(TileState &T)
 {
-    T.n_cand = 0; T.viol = 0; T.any_hit = 0;
+    T.n_cand = 0; T.viol = 0;
     T.cls[0] = T.cls[1] = T.cls[2] = T.cls[3] = 0;
 }
 
@@ -284,7 +284,7 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, TileState &T, const u
                 hit = (sp >= 0) && (p >= sp + 1);
             }
         }
-        if (hit) { atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31)); T.any_hit = 1; }
+        if (hit) atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31));
     }
 }
 
@@ -615,24 +615,27 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
         }
         __syncthreads();
 
-        // ---- 6. publish the tile: count, violations / line-class flags, '\n' table, line hits
+        // ---- 6. publish the tile: count, violations / line-class flags, '\n' table, line hits.  No barrier
+        //         after it: the next writers of anything read here (the bulk copy into this buffer, the table,
+        //         the hit words, this copy of the scalars) all come after the first barrier of the next tile.
         {
             uint4 *dst = reinterpret_cast<uint4 *>(P.tile_nl + t * (unsigned long long)kNlStride);
             const uint4 *src = reinterpret_cast<const uint4 *>(S.nlpos);
             for (int q = tid; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
-            const unsigned int any_hit = T.any_hit;
             if (LM != 0 && !REDO) {
                 unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
                 const int nw = (n_tab >> 5) + 1;               // local line indices 0..n_tab
-                for (int w = tid; w < nw; w += kThreads) hd[w] = any_hit ? S.linehit[w] : 0u;
+                for (int w = tid; w < nw; w += kThreads) {
+                    const unsigned int v = S.linehit[w];
+                    hd[w] = v;
+                    if (v) S.linehit[w] = 0;
+                }
             }
             if (tid == 0) {
                 const TileInfo ti = {total, T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),
                                      {(unsigned short)T.cls[0], (unsigned short)T.cls[1], (unsigned short)T.cls[2], (unsigned short)T.cls[3]}};
                 P.info[t] = ti;
             }
-            __syncthreads();                     // everything of this tile is consumed: the tile buffer may be refilled
-            if (LM != 0 && any_hit) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
         }
     }
 #undef FXG_TILE_OF
