@@ -14,21 +14,24 @@ int set_cuda_error(fxg_ctx *ctx, cudaError_t e, const char *what);
 // ---------------------------------------------------------------- geometry
 // (compile-time; -DFXG_TILE_BYTES / -DFXG_THREADS / -DFXG_MIN_CTAS build the variants compared in DESIGN.md)
 #ifndef FXG_TILE_BYTES
-#define FXG_TILE_BYTES 32768
+#define FXG_TILE_BYTES 24576
 #endif
 #ifndef FXG_THREADS
-#define FXG_THREADS 512
+#define FXG_THREADS 384
 #endif
 #ifndef FXG_MIN_CTAS
-#define FXG_MIN_CTAS 2
+#define FXG_MIN_CTAS 3
 #endif
 constexpr int kTileBytes = FXG_TILE_BYTES;     // bytes of input one CTA scans
-constexpr int kThreads = FXG_THREADS;          // threads per CTA (16 warps)
+constexpr int kThreads = FXG_THREADS;          // threads per CTA (12 warps)
 constexpr int kMinCtas = FXG_MIN_CTAS;         // resident CTAs per SM the scan kernel is compiled for
 static_assert(kTileBytes % (kThreads * 16) == 0 && kTileBytes <= 65536, "tile = whole 16-byte chunks per thread; u16 positions");
-constexpr int kChunks = kTileBytes / 16;       // 16-byte chunks per tile (2048)
+constexpr int kChunks = kTileBytes / 16;       // 16-byte chunks per tile (1536)
 constexpr int kChunksPerThread = kChunks / kThreads;   // 4
-constexpr int kMaxTileLines = 4096;            // newline-table capacity per tile
+#ifndef FXG_MAX_TILE_LINES
+#define FXG_MAX_TILE_LINES (FXG_TILE_BYTES / 8)
+#endif
+constexpr int kMaxTileLines = FXG_MAX_TILE_LINES;   // newline-table capacity per tile (denser tiles are reported, not parsed)
 constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
 
 // ---------------------------------------------------------------- per-tile results

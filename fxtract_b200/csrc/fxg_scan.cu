@@ -6,7 +6,7 @@
 //   strstr x1..2 (main.cpp:568-588)   ->  literal hit
 //   on_match (main.cpp:258-271)       ->  count / select
 // with a position-centric kernel that has NO cross-tile dependency.  Every CTA takes one
-// 32 KiB tile, pulls it into shared memory with one bulk async copy (TMA, mbarrier
+// 24 KiB tile, pulls it into shared memory with one bulk async copy (TMA, mbarrier
 // completion) and then
 //   1. main pass, 16 bytes per lane per step, SWAR only: count of bytes < 0x20, byte
 //      range check, per-chunk class summaries ("has a byte < 0x41", "has a byte < 0x21")
@@ -184,7 +184,7 @@ __device__ __forceinline__ void range_any2(const ScanSmem &S, int lo, int hi, un
 // ---------------------------------------------------------------- per-line checks (phase-free)
 // Flags of local line i (the line that ends at nlpos[i]) and class flags of the head of
 // line i+1 (the bytes after that '\n' inside the same 16-byte chunk).
-constexpr unsigned int kFA = 1, kFB = 2, kFC = 4, kFD = 8, kFS = 16, kFQ = 32, kFSP = 64;
+constexpr unsigned int kFA = 1, kFB = 2, kFC = 4, kFD = 8, kFS = 16, kFQ = 32, kFSP = 64, kFCTL = 128;
 //  kFA  not a header line: empty or first byte != '@'          (FXG_V_HEADER_AT)
 //  kFSP ends with ' ' (separator would not round-trip)          (FXG_V_HEADER_SPACE)
 //  kFB  empty line (as a sequence: FXG_V_EMPTY_SEQ)
@@ -192,11 +192,13 @@ constexpr unsigned int kFA = 1, kFB = 2, kFC = 4, kFD = 8, kFS = 16, kFQ = 32, k
 //  kFD  length differs from the line two above                  (FXG_V_QUAL_LEN)
 //  kFS  has a byte outside [0x41,0x7e]                          (FXG_V_SEQ_CLASS)
 //  kFQ  has a byte outside [0x21,0x7e]                          (FXG_V_QUAL_CLASS)
+//  kFCTL ends with a control byte other than '\n' (any role)    (FXG_V_BYTE_RANGE)
 __device__ __forceinline__ void line_flags(const ScanSmem &S, const uint4 *tile, int i, int n_tab, unsigned int &own,
                                            unsigned int &nxt)
 {
     const unsigned char *tb = reinterpret_cast<const unsigned char *>(tile);
     const int pos = S.nlpos[i];
+    const bool ctl = tb[pos] != '\n';             // a control byte posing as a line end
     const int prev = i > 0 ? (int)S.nlpos[i - 1] : -1;
     const int next = i + 1 < n_tab ? (int)S.nlpos[i + 1] : kTileBytes;
     const int c = pos >> 4, cb = c << 4, cp = prev >> 4;
@@ -211,6 +213,7 @@ __device__ __forceinline__ void line_flags(const ScanSmem &S, const uint4 *tile,
     range_any2(S, cp + 1, c, ms, mq);
     own = (((s16 & r_tail) | ms) ? kFS : 0u) | (((q16 & r_tail) | mq) ? kFQ : 0u);
     nxt = ((s16 & r_head) ? kFS : 0u) | ((q16 & r_head) ? kFQ : 0u);
+    if (ctl) own |= kFCTL;
     if (i >= 1) {                              // line starts inside the tile: structure is local
         const int llen = pos - prev - 1;
         const unsigned int fb = tb[prev + 1], lb = tb[pos - 1];
@@ -333,7 +336,7 @@ __device__ __forceinline__ unsigned int class_bad(const ScanSmem &S, const uint4
 }
 
 // ---------------------------------------------------------------- kernel 1: per-tile scan
-// Persistent CTAs (2 per SM, 16 warps each): tile t = blockIdx.x, += gridDim.x.  The next tile
+// Persistent CTAs (3 per SM, 12 warps each): tile t = blockIdx.x, += gridDim.x.  The next tile
 // is prefetched into the other shared-memory buffer while the current one is processed.
 // LM = literal filter mode: 0 none (multi / exact strategies), 8 = aligned 8-byte units with the
 // fingerprint table, 1 = short patterns (units of 4 / 2 / 1 bytes).
@@ -461,28 +464,18 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
             if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(T, FXG_V_BYTE_RANGE);
         }
 
-        // ---- 2. (warp local) exact '\n' masks of the listed chunks, '\n' count of the warp's segment.  A byte
-        //         below 0x20 that is not '\n' is a violation: y = x ^ 0x0a.. is 0 exactly for '\n' and stays
-        //         below 0x20 for every other control byte, so (y + 0x7f..) has bit 7 set there.
+        // ---- 2. (warp local) masks of the bytes < 0x20 of the listed chunks, their count in the warp's segment
+        //         (that every such byte is a '\n' is checked per line in step 4)
         {
             __syncwarp();
-            unsigned int cnt = 0, ctl = 0;
+            unsigned int cnt = 0;
             for (unsigned int q = lane; q < wcount; q += 32) {
-                const uint4 x = tile[my_list[q]];
-                const unsigned int h0 = ~(x.x + kAdd20) & kHi, h1 = ~(x.y + kAdd20) & kHi;
-                const unsigned int h2 = ~(x.z + kAdd20) & kHi, h3 = ~(x.w + kAdd20) & kHi;
-                ctl |= h0 & ((x.x ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
-                ctl |= h1 & ((x.y ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
-                ctl |= h2 & ((x.z ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
-                ctl |= h3 & ((x.w ^ 0x0a0a0a0au) + 0x7f7f7f7fu);
-                const unsigned int m16 = ((h0 * 0x00204081u) >> 28) | (((h1 * 0x00204081u) >> 28) << 4) |
-                                         (((h2 * 0x00204081u) >> 28) << 8) | (((h3 * 0x00204081u) >> 28) << 12);
+                const unsigned int m16 = lin_mask(tile[my_list[q]], kAdd20);
                 my_mask[q] = (unsigned short)m16;
                 cnt += __popc(m16);
             }
             cnt = __reduce_add_sync(0xffffffffu, cnt);
             if (lane == 0) S.wtot[cur][warp] = cnt;
-            if (__any_sync(0xffffffffu, ctl != 0) && lane == 0) note_violation(T, FXG_V_BYTE_RANGE);
         }
         __syncthreads();
 
@@ -545,6 +538,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
                 const int a = i >= 1 ? (int)S.nlpos[i - 1] + 1 : 0;
                 const int e = i < n_tab ? (int)S.nlpos[i] : kTileBytes;
                 const bool whole = i >= 1 && i < n_tab;       // line starts and ends inside the tile
+                if (i < n_tab && tb[e] != '\n') viol |= FXG_V_BYTE_RANGE;   // a control byte posing as a line end
                 if (role == 0) {
                     if (whole) {
                         if (e - a < 1 || tb[a] != '@') viol |= FXG_V_HEADER_AT;
@@ -760,7 +754,8 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
     if (guess && (int)(guess - 1) != r) viol |= FXG_V_DENSE_LINES;   // cannot happen after the REDO launch; never pass silently
 #pragma unroll
     for (int k = 0; k < 4; ++k)                  // lines with local index == k (mod 4) have role (k + r) & 3
-        viol |= role_kinds(ti.cls[k] & 0x7fu, (k + r) & 3) | role_kinds(ti.cls[k] >> 8, (k + 1 + r) & 3);
+        viol |= role_kinds(ti.cls[k] & 0x7fu, (k + r) & 3) | role_kinds(ti.cls[k] >> 8, (k + 1 + r) & 3) |
+                ((ti.cls[k] & kFCTL) ? (unsigned int)FXG_V_BYTE_RANGE : 0u);
     // structure of the first lines of the tile, whose predecessors lie in earlier tiles
     if (n_tab > 0) {
         long long p[6];                          // '\n' positions with local index -3 .. 2
@@ -865,7 +860,7 @@ template <int LM, bool REDO> static cudaError_t launch_scan_tiles(const ScanPara
         if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
         if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_tiles_kernel<LM, REDO>, kThreads, sizeof(ScanSmem))) != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
-        grid_cap[dev] = sms * per_sm;            // persistent CTAs: one wave, 148 SMs x 2 on B200
+        grid_cap[dev] = sms * per_sm;            // persistent CTAs: one wave, 148 SMs x 3 on B200
         attr_set[dev] = true;
     }
     unsigned long long grid = P.ntiles < (unsigned long long)grid_cap[dev] ? P.ntiles : (unsigned long long)grid_cap[dev];
