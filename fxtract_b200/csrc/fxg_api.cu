@@ -127,9 +127,11 @@ static void build_literal_table(fxg_ctx *ctx)
     T.n_keys = (int)keys.size();
     if (U == 8) {
         unsigned long long rng = 0x243F6A8885A308D3ull;
+        // the first 4096 attempts keep mul1 == 1 (fingerprint = lo + hi * mul2: one IMAD per unit in the scan
+        // kernel, variant LM 9); key sets whose slots cannot be separated that way fall through to two multipliers
         for (int attempt = 0; attempt < 1000000; ++attempt) {
             rng = rng * 6364136223846793005ull + 1442695040888963407ull;
-            unsigned int m1 = (unsigned int)(rng >> 32) | 1u;
+            unsigned int m1 = attempt < 4096 ? 1u : ((unsigned int)(rng >> 32) | 1u);
             rng = rng * 6364136223846793005ull + 1442695040888963407ull;
             unsigned int m2 = (unsigned int)(rng >> 32) | 1u;
             bool used[64] = {false}; bool ok = true;
@@ -370,7 +372,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;
-    P.lit_unit = ctx->h_lit.unit;
+    P.lit_unit = ctx->h_lit.unit == 8 && ctx->h_lit.mul1 == 1u ? 9 : ctx->h_lit.unit;
     if (!literal) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
     if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[1], st));
     FXG_CUDA_OK(launch_scan_raw(P, st, &ctx->last_launches, ctx->profiling ? s.ev[2] : nullptr));

@@ -339,7 +339,7 @@ __device__ __forceinline__ unsigned int class_bad(const ScanSmem &S, const uint4
 // Persistent CTAs (3 per SM, 12 warps each): tile t = blockIdx.x, += gridDim.x.  The next tile
 // is prefetched into the other shared-memory buffer while the current one is processed.
 // LM = literal filter mode: 0 none (multi / exact strategies), 8 = aligned 8-byte units with the
-// fingerprint table, 1 = short patterns (units of 4 / 2 / 1 bytes).
+// fingerprint table (9: same with first multiplier 1), 1 = short patterns (units of 4 / 2 / 1 bytes).
 // REDO = second launch over the (normally empty) list of tiles whose locally guessed line phase
 // turned out wrong: those are re-evaluated with the phase-free per-line path.
 template <int LM, bool REDO>
@@ -449,9 +449,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
                 S.qbits[c >> 5] = qb;
                 if (q_any) my_list[wcount + __popc(qb & lt_mask)] = (unsigned short)c;
                 wcount += __popc(qb);
-                if (LM == 8) {
-                    const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
-                    const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
+                if (LM == 8 || LM == 9) {
+                    const unsigned int r0 = LM == 9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
+                    const unsigned int r1 = LM == 9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
                     const bool c0 = S.lit_fp[r0 >> 26] == r0, c1 = S.lit_fp[r1 >> 26] == r1;
                     if (__any_sync(0xffffffffu, c0 || c1)) {          // rare: keep the hot loop branch-free
                         if (c0) push_candidate(S, T, c << 4, S.lit_masks[r0 >> 26]);
@@ -490,19 +490,36 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
                 unsigned int m16 = q < wcount ? (unsigned int)my_mask[q] : 0u;
                 const int cb = q < wcount ? ((int)my_list[q] << 4) - 1 : 0;
                 const unsigned int n = __popc(m16);
-                unsigned int inc = n;
+                unsigned int idx, round_total;
+                // exclusive prefix of the per-lane counts: two ballots while no chunk holds more than two '\n'
+                const unsigned int b1 = __ballot_sync(0xffffffffu, n >= 1u), b2 = __ballot_sync(0xffffffffu, n >= 2u);
+                if (!__any_sync(0xffffffffu, n >= 3u)) {
+                    idx = idx0 + __popc(b1 & lt_mask) + __popc(b2 & lt_mask);
+                    round_total = __popc(b1) + __popc(b2);
+                } else {
+                    unsigned int inc = n;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
-                    if (lane >= d) inc += o;
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                        if (lane >= d) inc += o;
+                    }
+                    idx = idx0 + inc - n;
+                    round_total = __shfl_sync(0xffffffffu, inc, 31);
                 }
-                unsigned int idx = idx0 + inc - n;
-                idx0 += __shfl_sync(0xffffffffu, inc, 31);
+                idx0 += round_total;
                 // the table has 16 entries of slack: clamping the first index keeps every store inside it
                 unsigned short *dst = &S.nlpos[idx < (unsigned int)kMaxTileLines ? idx : (unsigned int)kMaxTileLines];
-                while (m16) {
-                    *dst++ = (unsigned short)(cb + __ffs(m16));
+                if (m16) {
+                    dst[0] = (unsigned short)(cb + __ffs(m16));
                     m16 &= m16 - 1;
+                    if (m16) {
+                        dst[1] = (unsigned short)(cb + __ffs(m16));
+                        m16 &= m16 - 1;
+                        for (int k = 2; m16; ++k) {
+                            dst[k] = (unsigned short)(cb + __ffs(m16));
+                            m16 &= m16 - 1;
+                        }
+                    }
                 }
             }
         }
@@ -588,9 +605,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
                 // queue overflow (pattern hits nearly everywhere): rescan the tile and verify in place
                 for (int c = tid; c < kChunks && (c << 4) < tile_len; c += kThreads) {
                     const uint4 x = tile[c];
-                    if (LM == 8) {
-                        const unsigned int r0 = x.x * lit_mul1 + x.y * lit_mul2;
-                        const unsigned int r1 = x.z * lit_mul1 + x.w * lit_mul2;
+                    if (LM == 8 || LM == 9) {
+                        const unsigned int r0 = LM == 9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
+                        const unsigned int r1 = LM == 9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
                         if (S.lit_fp[r0 >> 26] == r0) verify_candidate(S, T, tb, P, base, n_tab, c << 4, S.lit_masks[r0 >> 26]);
                         if (S.lit_fp[r1 >> 26] == r1) verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> 26]);
                     } else {
@@ -878,6 +895,7 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
     if (P.ntiles > 0xffffffffull) return cudaErrorInvalidValue;
     cudaError_t e;
     if (!P.match_enabled) e = launch_scan_tiles<0, false>(P, stream, dev);
+    else if (P.lit_unit == 9) e = launch_scan_tiles<9, false>(P, stream, dev);
     else if (P.lit_unit == 8) e = launch_scan_tiles<8, false>(P, stream, dev);
     else e = launch_scan_tiles<1, false>(P, stream, dev);
     if (e != cudaSuccess) return e;
