@@ -127,26 +127,30 @@ static void build_literal_table(fxg_ctx *ctx)
     T.n_keys = (int)keys.size();
     if (U == 8) {
         unsigned long long rng = 0x243F6A8885A308D3ull;
-        // the first 4096 attempts keep mul1 == 1 (fingerprint = lo + hi * mul2: one IMAD per unit in the scan
-        // kernel, variant LM 9); key sets whose slots cannot be separated that way fall through to two multipliers
+        // Perfect hash of the keys into the fingerprint table, cheapest form first:
+        //   attempts    0.. 8191: mul1 == 1 (fingerprint = lo + hi * mul2: one IMAD per unit, kernel variant LM 9),
+        //                         32 slots (one per shared-memory bank: the look-up never conflicts);
+        //   attempts 8192..12287: mul1 == 1, 64 slots;   later: two multipliers, 64 slots.
+        T.shift = 26;
         for (int attempt = 0; attempt < 1000000; ++attempt) {
             rng = rng * 6364136223846793005ull + 1442695040888963407ull;
-            unsigned int m1 = attempt < 4096 ? 1u : ((unsigned int)(rng >> 32) | 1u);
+            unsigned int m1 = attempt < 12288 ? 1u : ((unsigned int)(rng >> 32) | 1u);
             rng = rng * 6364136223846793005ull + 1442695040888963407ull;
             unsigned int m2 = (unsigned int)(rng >> 32) | 1u;
+            const int shift = attempt < 8192 && keys.size() <= 32 ? 27 : 26;
             bool used[64] = {false}; bool ok = true;
             for (size_t i = 0; i < keys.size() && ok; ++i) {
                 unsigned int lo = (unsigned int)keys[i], hi = (unsigned int)(keys[i] >> 32);
-                unsigned int h = (lo * m1 + hi * m2) >> 26;
+                unsigned int h = (lo * m1 + hi * m2) >> shift;
                 if (used[h]) ok = false; else used[h] = true;
             }
-            if (ok) { T.mul1 = m1; T.mul2 = m2; break; }
+            if (ok) { T.mul1 = m1; T.mul2 = m2; T.shift = shift; break; }
         }
-        for (unsigned int h = 0; h < 64; ++h) T.fp[h] = (h ^ 1u) << 26;      // top bits != h: can never match
+        for (unsigned int h = 0; h < 64; ++h) T.fp[h] = (h ^ 1u) << T.shift;      // top bits != h: can never match
         for (size_t i = 0; i < keys.size(); ++i) {
             unsigned int lo = (unsigned int)keys[i], hi = (unsigned int)(keys[i] >> 32);
             unsigned int r = lo * T.mul1 + hi * T.mul2;
-            T.keys[r >> 26] = keys[i]; T.fp[r >> 26] = r; T.masks[r >> 26] = masks[i];
+            T.keys[r >> T.shift] = keys[i]; T.fp[r >> T.shift] = r; T.masks[r >> T.shift] = masks[i];
         }
     } else {
         for (size_t i = 0; i < keys.size() && i < 64; ++i) { T.keys[i] = keys[i]; T.masks[i] = masks[i]; }

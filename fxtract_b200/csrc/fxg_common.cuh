@@ -75,10 +75,11 @@ struct LiteralTable {
     int all_match;               // empty pattern: every record matches (strstr(hay,"") != NULL)
     int never;                   // pattern contains '\n': can never match a field
     unsigned int mul1, mul2;     // perfect-hash multipliers (unit == 8)
+    int shift;                   // unit == 8: slot = fingerprint >> shift (27: 32 slots, 26: 64 slots)
     int pat_len[2];
     int pat_off[2];              // offsets into pat_bytes
     unsigned long long keys[64]; // unit==8: 64-slot perfect hash; else first n_keys entries
-    unsigned int fp[64];         // unit==8: fp[h] = lo*mul1 + hi*mul2 of the key in slot h = fp >> 26 (else unmatchable)
+    unsigned int fp[64];         // unit==8: fp[h] = lo*mul1 + hi*mul2 of the key in slot h = fp >> shift (else unmatchable)
     unsigned short masks[64];    // bit (pattern*8 + shift) set if keys[i] == pat[shift..shift+U)
 };
 

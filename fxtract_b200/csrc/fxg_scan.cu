@@ -370,9 +370,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
     if (tid >= 128 && tid < 145) S.below[tid - 128] = kBelowTab[tid - 128];
     if (LM != 0) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
     int lit_unit = 0, lit_nkeys = 0;
-    unsigned int lit_mul1 = 0, lit_mul2 = 0;
+    unsigned int lit_mul1 = 0, lit_mul2 = 0, lit_shift = 26;
     if (LM != 0) {
-        lit_unit = lit->unit; lit_nkeys = lit->n_keys; lit_mul1 = lit->mul1; lit_mul2 = lit->mul2;
+        lit_unit = lit->unit; lit_nkeys = lit->n_keys; lit_mul1 = lit->mul1; lit_mul2 = lit->mul2; lit_shift = (unsigned int)lit->shift;
         if (tid >= 64 && tid < 128) {
             const int k = tid - 64;
             S.lit_keys[k] = lit->keys[k]; S.lit_fp[k] = lit->fp[k]; S.lit_masks[k] = lit->masks[k];
@@ -452,10 +452,10 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
                 if (LM == 8 || LM == 9) {
                     const unsigned int r0 = LM == 9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
                     const unsigned int r1 = LM == 9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
-                    const bool c0 = S.lit_fp[r0 >> 26] == r0, c1 = S.lit_fp[r1 >> 26] == r1;
+                    const bool c0 = S.lit_fp[r0 >> lit_shift] == r0, c1 = S.lit_fp[r1 >> lit_shift] == r1;
                     if (__any_sync(0xffffffffu, c0 || c1)) {          // rare: keep the hot loop branch-free
-                        if (c0) push_candidate(S, T, c << 4, S.lit_masks[r0 >> 26]);
-                        if (c1) push_candidate(S, T, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                        if (c0) push_candidate(S, T, c << 4, S.lit_masks[r0 >> lit_shift]);
+                        if (c1) push_candidate(S, T, (c << 4) + 8, S.lit_masks[r1 >> lit_shift]);
                     }
                 } else if (LM == 1) {
                     if ((c << 4) < tile_len) filter_small_units(S, T, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
@@ -608,8 +608,8 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
                     if (LM == 8 || LM == 9) {
                         const unsigned int r0 = LM == 9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
                         const unsigned int r1 = LM == 9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
-                        if (S.lit_fp[r0 >> 26] == r0) verify_candidate(S, T, tb, P, base, n_tab, c << 4, S.lit_masks[r0 >> 26]);
-                        if (S.lit_fp[r1 >> 26] == r1) verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> 26]);
+                        if (S.lit_fp[r0 >> lit_shift] == r0) verify_candidate(S, T, tb, P, base, n_tab, c << 4, S.lit_masks[r0 >> lit_shift]);
+                        if (S.lit_fp[r1 >> lit_shift] == r1) verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + 8, S.lit_masks[r1 >> lit_shift]);
                     } else {
                         const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
                         for (int u = 0; u < 16; u += lit_unit) {
