@@ -267,3 +267,32 @@ def test_multi_kmer_raw(fx, seed):
         want = fxoracle.run(data, flags, pattern_file=pf)
         got = run_raw(fx, data, fx.MODE_MULTI, plist, invert=inv)
         assert got["ok"] == 1 and got["out"] == want, (flags, len(got["out"]), len(want))
+
+
+def test_literal_fingerprint_table_forms(fx):
+    """The 8-byte-unit filter picks its perfect hash cheapest form first (fxg_api.cu, build_literal_table):
+    fingerprint lo + hi * mul2 in a 32-slot table, then 64 slots, then two multipliers.  Two keys that differ
+    only in byte 0 ("CAAAAAAA" / "AAAAAAAA") cannot be separated with mul1 == 1 and force the general form;
+    low-complexity and planted patterns must give the oracle's records in every form."""
+    rng = random.Random(77)
+    recs = []
+    plant = [b"CAAAAAAAAAAAAAAAAAAA", b"ACGTACGTACGTACGTACGT", b"TTTTTTTTTTTTTTTTTTTTTTTTT", b"GATTACAGATTACAGATTACAG"]
+    for i in range(6000):
+        seq = bytearray(helpers.rand_dna(rng, rng.randint(60, 180)).encode())
+        if i % 7 == 0:
+            p = plant[(i // 7) % len(plant)]
+            if rng.random() < 0.5:
+                p = fxoracle.revcomp(p)
+            o = rng.randint(0, len(seq) - len(p))
+            seq[o:o + len(p)] = p
+        qual = bytes(rng.randint(33, 73) for _ in range(len(seq)))
+        recs.append(b"@r%d x:%d\n" % (i, i) + bytes(seq) + b"\n+\n" + qual + b"\n")
+    data = b"".join(recs)
+    for pat in plant:
+        for use_rc in (False, True):
+            pats = [pat] + ([fxoracle.revcomp(pat)] if use_rc else [])
+            want = fxoracle.run(data, "r" if use_rc else "", pattern=pat)
+            got = run_raw(fx, data, fx.MODE_LITERAL, pats)
+            assert got["ok"] == 1
+            assert got["out"] == want, (pat, use_rc, len(got["out"]), len(want))
+            assert len(want) > 0
