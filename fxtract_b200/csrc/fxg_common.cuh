@@ -120,7 +120,10 @@ struct AcDevice {              // byte-class compressed Aho-Corasick DFA
 // alphabet").  Every pattern contributes its first `stride` k-mers (offsets 0..stride-1, stride = min pattern
 // length - k + 1), so an occurrence is found by probing every stride-th text position only.  Probe = two bits of a
 // 2^19-bit filter held in shared memory, then an open-addressing table in L2, then byte verification.
-constexpr int kKmerFilterBits = 19;
+#ifndef FXG_KMER_FILTER_BITS
+#define FXG_KMER_FILTER_BITS 19
+#endif
+constexpr int kKmerFilterBits = FXG_KMER_FILTER_BITS;
 constexpr int kKmerFilterWords = 1 << (kKmerFilterBits - 5);
 struct KmerDevice {
     const unsigned int *filter;            // [kKmerFilterWords]
