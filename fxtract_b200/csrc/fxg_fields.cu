@@ -157,6 +157,50 @@ __device__ __forceinline__ bool kmer_probe(const unsigned int *filt, const KmerD
 #ifndef FXG_KM_CTAS
 #define FXG_KM_CTAS 3
 #endif
+// One field-relative word: `w` = bytes 4r..4r+3 of the field, r in [0, nwords] (r == nwords: the last len & 3 bytes).
+template <int S>
+__device__ __forceinline__ void kmer_word(const unsigned int *filt, const KmerDevice &K, unsigned int w, int r, int nwords,
+                                          unsigned int len, const uint8_t *p, const uint8_t *end, int k, unsigned int kmask,
+                                          int j0, unsigned int &key, int &run, bool &hit)
+{
+    const uint8_t *wa = p + 4 * r;
+    const unsigned int codes = (w >> 1) & 0x03030303u;
+    const unsigned int l1 = codes & 0x01010101u, h1 = (codes >> 1) & 0x01010101u;
+    const unsigned int expect = 0x41414141u + l1 * 2u + h1 * 0x13u - (l1 & h1) * 0x0fu;
+    if (r < nwords && expect == w) {                        // four bases inside the field
+        const unsigned int c4 = (codes * 0x40100401u) >> 24;
+        if (S == 4) {
+            if (run + j0 + 1 >= k &&
+                kmer_probe(filt, K, ((key << (2 * j0 + 2)) | (c4 >> (6 - 2 * j0))) & kmask, wa + j0, p, end)) hit = true;
+        } else if (S == 2) {
+            if (run + j0 + 1 >= k &&
+                kmer_probe(filt, K, ((key << (2 * j0 + 2)) | (c4 >> (6 - 2 * j0))) & kmask, wa + j0, p, end)) hit = true;
+            if (run + j0 + 3 >= k &&
+                kmer_probe(filt, K, ((key << (2 * j0 + 6)) | (c4 >> (2 - 2 * j0))) & kmask, wa + j0 + 2, p, end)) hit = true;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (run + j + 1 >= k &&
+                    kmer_probe(filt, K, ((key << (2 * j + 2)) | (c4 >> (6 - 2 * j))) & kmask, wa + j, p, end)) hit = true;
+        }
+        key = ((key << 8) | c4) & kmask;
+        run += 4;
+    } else {                                                // a non-base byte, or the field's last 0..3 bytes
+        const int lim = r < nwords ? 4 : (int)(len & 3);
+        for (int j = 0; j < lim; ++j) {
+            const unsigned int b = (w >> (8 * j)) & 0xffu;
+            if (!fxg_is_acgt(b)) { run = 0; continue; }
+            key = ((key << 2) | fxg_base_code(b)) & kmask;
+            ++run;
+            if (((j - j0) & (S - 1)) == 0 && run >= k && kmer_probe(filt, K, key, wa + j, p, end)) hit = true;
+        }
+    }
+}
+
+// The walk steps through the ALIGNED 16-byte chunks that hold the field, all lanes in lock step (one 16-byte load
+// per chunk, no per-lane chunk bookkeeping): with G[g] the aligned words from the first chunk on and c0 the index
+// of the word that holds the field's first byte, field word r = funnelshift(G[c0 + r], G[c0 + r + 1], 8 * (p & 3)),
+// so aligned word g completes field word r = g - 1 - c0.  Only the range test of r differs between lanes.
 template <int S>
 __global__ void __launch_bounds__(FXG_KM_THREADS, FXG_KM_CTAS) fields_kmer_kernel(FieldSrc src, unsigned long long n, KmerDevice K, FieldOut O)
 {
@@ -175,55 +219,29 @@ __global__ void __launch_bounds__(FXG_KM_THREADS, FXG_KM_CTAS) fields_kmer_kerne
         if (f < n) src.get(f, p, len);
         if (len >= (unsigned int)(k + S - 1)) {
             const uint8_t *end = p + len;
-            const uint8_t *ca = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)15);      // address of the chunk in xc
+            const uint8_t *ca = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)15);      // first aligned chunk
             const int sh = (int)((uintptr_t)p & 3) * 8;
-            int ci = (int)(((uintptr_t)p & 15) >> 2);                                   // aligned word of xc that holds `lo`
-            uint4 xc = __ldg(reinterpret_cast<const uint4 *>(ca));
-            uint4 xn = ca + 16 < end ? __ldg(reinterpret_cast<const uint4 *>(ca + 16)) : xc;
-            unsigned int lo = pick_word(xc, ci);
-            unsigned int key = 0;
-            int run = 0;
             const int nwords = (int)(len >> 2);
-            for (int r = 0; r <= nwords && !hit; ++r) {
-                if (++ci == 4) {                       // step to the next chunk; keep one more in flight
-                    ci = 0; ca += 16; xc = xn;
-                    if (ca + 16 < end) xn = __ldg(reinterpret_cast<const uint4 *>(ca + 16));
-                }
-                const unsigned int hi = pick_word(xc, ci);
-                const unsigned int w = __funnelshift_r(lo, hi, sh);
-                lo = hi;
-                const uint8_t *wa = p + 4 * r;
-                const unsigned int codes = (w >> 1) & 0x03030303u;
-                const unsigned int l1 = codes & 0x01010101u, h1 = (codes >> 1) & 0x01010101u;
-                const unsigned int expect = 0x41414141u + l1 * 2u + h1 * 0x13u - (l1 & h1) * 0x0fu;
-                if (r < nwords && expect == w) {                        // four bases inside the field
-                    const unsigned int c4 = (codes * 0x40100401u) >> 24;
-                    if (S == 4) {
-                        if (run + j0 + 1 >= k &&
-                            kmer_probe(filt, K, ((key << (2 * j0 + 2)) | (c4 >> (6 - 2 * j0))) & kmask, wa + j0, p, end)) hit = true;
-                    } else if (S == 2) {
-                        if (run + j0 + 1 >= k &&
-                            kmer_probe(filt, K, ((key << (2 * j0 + 2)) | (c4 >> (6 - 2 * j0))) & kmask, wa + j0, p, end)) hit = true;
-                        if (run + j0 + 3 >= k &&
-                            kmer_probe(filt, K, ((key << (2 * j0 + 6)) | (c4 >> (2 - 2 * j0))) & kmask, wa + j0 + 2, p, end)) hit = true;
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (run + j + 1 >= k &&
-                                kmer_probe(filt, K, ((key << (2 * j + 2)) | (c4 >> (6 - 2 * j))) & kmask, wa + j, p, end)) hit = true;
-                    }
-                    key = ((key << 8) | c4) & kmask;
-                    run += 4;
-                } else {                                                // a non-base byte, or the field's last 0..3 bytes
-                    const int lim = r < nwords ? 4 : (int)(len & 3);
-                    for (int j = 0; j < lim; ++j) {
-                        const unsigned int b = (w >> (8 * j)) & 0xffu;
-                        if (!fxg_is_acgt(b)) { run = 0; continue; }
-                        key = ((key << 2) | fxg_base_code(b)) & kmask;
-                        ++run;
-                        if (((j - j0) & (S - 1)) == 0 && run >= k && kmer_probe(filt, K, key, wa + j, p, end)) hit = true;
-                    }
-                }
+            const int c0 = (int)(((uintptr_t)p & 15) >> 2);
+            const int glast = nwords + 1 + c0;                                          // aligned word that completes word `nwords`
+            unsigned int prev = 0, key = 0;
+            int run = 0;
+            uint4 x = __ldg(reinterpret_cast<const uint4 *>(ca));
+            for (int g = 0; g <= glast && !hit; g += 4) {
+                ca += 16;
+                uint4 xn = make_uint4(0, 0, 0, 0);                                     // chunks past the field are not read
+                if (ca < end) xn = __ldg(reinterpret_cast<const uint4 *>(ca));
+                const int r = g - 1 - c0;                                               // field word completed by x.x
+                if (r >= 0 && r <= nwords)
+                    kmer_word<S>(filt, K, __funnelshift_r(prev, x.x, sh), r, nwords, len, p, end, k, kmask, j0, key, run, hit);
+                if (r + 1 >= 0 && r + 1 <= nwords && !hit)
+                    kmer_word<S>(filt, K, __funnelshift_r(x.x, x.y, sh), r + 1, nwords, len, p, end, k, kmask, j0, key, run, hit);
+                if (r + 2 >= 0 && r + 2 <= nwords && !hit)
+                    kmer_word<S>(filt, K, __funnelshift_r(x.y, x.z, sh), r + 2, nwords, len, p, end, k, kmask, j0, key, run, hit);
+                if (r + 3 >= 0 && r + 3 <= nwords && !hit)
+                    kmer_word<S>(filt, K, __funnelshift_r(x.z, x.w, sh), r + 3, nwords, len, p, end, k, kmask, j0, key, run, hit);
+                prev = x.w;
+                x = xn;
             }
         }
         emit_thread_per_field(O, f, n, hit, -1);
