@@ -378,11 +378,13 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;
     P.lit_unit = ctx->h_lit.unit == 8 && ctx->h_lit.mul1 == 1u ? 9 : ctx->h_lit.unit;
     if (!literal) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
+    P.header_whole = ctx->cfg.mode == FXG_MODE_EXACT && ctx->cfg.target == FXG_TARGET_NAME;
     if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[1], st));
     FXG_CUDA_OK(launch_scan_raw(P, st, &ctx->last_launches, ctx->profiling ? s.ev[2] : nullptr));
     if (!literal) {
         FieldSrc src; memset(&src, 0, sizeof src);
         src.base = d_buf; src.off64 = ctx->d_fld_off; src.len32 = ctx->d_fld_len; src.n_lines_dev = &ctx->d_ctr->n_lines;
+        src.stop_at_space = P.header_whole;
         FieldOut O; memset(&O, 0, sizeof O);
         O.hitbits = ctx->d_hitbits; O.n_hits = &ctx->d_ctr->n_hits;
         if (ctx->cfg.mode == FXG_MODE_MULTI && ctx->kmer_ok) {

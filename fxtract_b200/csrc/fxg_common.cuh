@@ -106,6 +106,8 @@ struct ScanParams {
     // field table for the second-stage matchers (multi / exact): target field of record k
     unsigned long long *fld_off;      // [rec_cap] or nullptr
     unsigned int *fld_len;            // [rec_cap]
+    int header_whole;                 // name target, exact strategy: the field table holds the whole header line (after '@');
+                                      // the look-up kernel ends the name at the first ' ' while it hashes (FieldSrc::stop_at_space)
 };
 
 // ---------------------------------------------------------------- field engine
@@ -164,6 +166,7 @@ struct FieldSrc {
     const unsigned long long *off64;     // table layout: start offsets ...
     const unsigned int *len32;           // ... and lengths
     const unsigned long long *n_lines_dev; // raw path: field count = *n_lines_dev / 4 (capped by the launch's n)
+    int stop_at_space;                   // fields are header lines: the key is the name, up to the first ' ' (exact kernel)
     __device__ __forceinline__ unsigned long long count(unsigned long long cap) const
     {
         if (!n_lines_dev) return cap;

@@ -260,7 +260,19 @@ __global__ void __launch_bounds__(256) fields_exact_kernel(FieldSrc src, unsigne
         if (k < n) {
             const uint8_t *p; unsigned int len;
             src.get(k, p, len);
-            unsigned long long h = fxg_hash_bytes(p, len);
+            unsigned long long h;
+            if (src.stop_at_space) {                  // key = name = the header line up to its first ' '
+                h = 0xcbf29ce484222325ull;           // same arithmetic as fxg_hash_bytes
+                unsigned int i = 0;
+                for (; i < len; ++i) {
+                    const unsigned int b = p[i];
+                    if (b == ' ') break;
+                    h ^= b; h *= 0x100000001b3ull;
+                }
+                len = i;
+                h ^= h >> 32; h *= 0x9e3779b97f4a7c15ull; h ^= h >> 29;
+                h = h ? h : 1ull;
+            } else h = fxg_hash_bytes(p, len);
             unsigned int slot = (unsigned int)(h >> 20) & E.mask;
             for (;;) {
                 unsigned long long sh = __ldg(&E.slot_hash[slot]);

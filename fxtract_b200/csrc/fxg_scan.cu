@@ -848,6 +848,11 @@ __global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
                 P.fld_off[rec] = (unsigned long long)(prev + 1); P.fld_len[rec] = (unsigned int)(pos - prev - 1);
             } else if (ph == 0 && (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT)) {
                 const long long prev = V.at(t, i - 1);
+                if (P.header_whole) {                 // the exact look-up finds the end of the name while it hashes
+                    P.fld_off[rec] = (unsigned long long)(prev + 2);
+                    P.fld_len[rec] = (unsigned int)(pos > prev + 2 ? pos - (prev + 2) : 0);
+                    continue;
+                }
                 long long q = prev + 2, sp = -1;
                 for (; q < pos; ++q) if (P.buf[q] == ' ') { sp = q; break; }
                 if (P.target == FXG_TARGET_NAME) {
