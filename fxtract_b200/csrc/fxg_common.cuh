@@ -151,13 +151,30 @@ struct ExactDevice {           // open-addressing table over whole-field keys
     unsigned int mask;                     // nslots - 1
 };
 
-// 64-bit FNV-1a style hash with a final mix; identical on host and device.
+// 64-bit hash of a whole-field key, identical on host and device: the key is read as little-endian 8-byte words
+// (the last 1..7 bytes zero padded into one more word), each word is folded in with one multiply, the length goes
+// into the final mix.  Word-wise so that the look-up kernel hashes 8 bytes per step (fields_exact_kernel).
+constexpr unsigned long long kHashSeed = 0xcbf29ce484222325ull;
+__host__ __device__ inline unsigned long long fxg_hash_word(unsigned long long h, unsigned long long w)
+{
+    h = (h ^ w) * 0x9e3779b97f4a7c15ull;
+    return h ^ (h >> 32);
+}
+__host__ __device__ inline unsigned long long fxg_hash_finish(unsigned long long h, unsigned int n)
+{
+    h = (h ^ n) * 0xff51afd7ed558ccdull;
+    h ^= h >> 33;
+    return h ? h : 1ull;
+}
 __host__ __device__ inline unsigned long long fxg_hash_bytes(const uint8_t *p, unsigned int n)
 {
-    unsigned long long h = 0xcbf29ce484222325ull;
-    for (unsigned int i = 0; i < n; ++i) { h ^= p[i]; h *= 0x100000001b3ull; }
-    h ^= h >> 32; h *= 0x9e3779b97f4a7c15ull; h ^= h >> 29;
-    return h ? h : 1ull;
+    unsigned long long h = kHashSeed;
+    for (unsigned int i = 0; i < n; i += 8) {
+        unsigned long long w = 0;
+        for (unsigned int b = 0; b < 8 && i + b < n; ++b) w |= (unsigned long long)p[i + b] << (8 * b);
+        h = fxg_hash_word(h, w);
+    }
+    return fxg_hash_finish(h, n);
 }
 
 struct FieldSrc {
