@@ -141,7 +141,7 @@ struct KmerDevice {
 __host__ __device__ inline unsigned int fxg_base_code(unsigned int b) { return (b >> 1) & 3u; }
 __host__ __device__ inline bool fxg_is_acgt(unsigned int b) { return b == 'A' || b == 'C' || b == 'G' || b == 'T'; }
 __host__ __device__ inline unsigned int fxg_kmer_hash(unsigned int key) { return key * 0x9E3779B1u; }
-__host__ __device__ inline unsigned int fxg_kmer_hash2(unsigned int key) { return (key ^ (key >> 15)) * 0x85EBCA6Bu; }
+__host__ __device__ inline unsigned int fxg_kmer_hash2(unsigned int key) { return key * 0xC2B2AE35u; }   // top bits used
 
 struct ExactDevice {           // open-addressing table over whole-field keys
     const unsigned long long *slot_hash;   // [nslots] 0 = empty

@@ -165,9 +165,11 @@ __device__ __forceinline__ void kmer_word(const unsigned int *filt, const KmerDe
 {
     const uint8_t *wa = p + 4 * r;
     const unsigned int codes = (w >> 1) & 0x03030303u;
-    const unsigned int l1 = codes & 0x01010101u, h1 = (codes >> 1) & 0x01010101u;
-    const unsigned int expect = 0x41414141u + l1 * 2u + h1 * 0x13u - (l1 & h1) * 0x0fu;
-    if (r < nwords && expect == w) {                        // four bases inside the field
+    // four "bases": a SUPERSET test -- A, C, G, T differ from 0x40 in bits 0, 1, 2, 4 only, so the test admits
+    // 0x40..0x47 and 0x50..0x57 (not N) -- is enough for the fast path: a letter that is no base only makes a k-mer
+    // that no pattern has (every candidate is compared byte by byte); it can never hide an occurrence, whose bytes
+    // are all real bases and whose k-mer is probed whatever preceded it
+    if (r < nwords && ((w ^ 0x40404040u) & 0xe8e8e8e8u) == 0u) {
         const unsigned int c4 = (codes * 0x40100401u) >> 24;
         if (S == 4) {
             if (run + j0 + 1 >= k &&
