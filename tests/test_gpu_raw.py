@@ -296,3 +296,29 @@ def test_literal_fingerprint_table_forms(fx):
             assert got["ok"] == 1
             assert got["out"] == want, (pat, use_rc, len(got["out"]), len(want))
             assert len(want) > 0
+
+
+def test_multi_kmer_non_base_letters(fx):
+    """The k-mer walk takes words of 0x40..0x47 / 0x50..0x57 letters through its fast path (superset of A, C, G, T:
+    fxg_fields.cu, kmer_word).  Occurrences directly beside such letters (and beside N, lower case, IUPAC codes)
+    must still be found and nothing else may be reported."""
+    rng = random.Random(91)
+    pats = sorted(set(helpers.rand_dna(rng, rng.choice([16, 20, 24, 31])).encode() for _ in range(40)))
+    letters = b"ACGTACGTACGTNEQSUWBDFPRVacgtnMKY"
+    recs = []
+    for i in range(5000):
+        n = rng.randint(40, 190)
+        seq = bytearray(letters[rng.randrange(len(letters))] for _ in range(n))
+        if i % 3 == 0:
+            p = pats[rng.randrange(len(pats))]
+            if len(p) <= n:
+                o = rng.randint(0, n - len(p))
+                seq[o:o + len(p)] = p
+        qual = bytes(rng.randint(33, 73) for _ in range(n))
+        recs.append(b"@q%d\n" % i + bytes(seq) + b"\n+\n" + qual + b"\n")
+    data = b"".join(recs)
+    pf = b"\n".join(pats) + b"\n"
+    want = fxoracle.run(data, "", pattern_file=pf)
+    got = run_raw(fx, data, fx.MODE_MULTI, pats)
+    assert got["ok"] == 1 and got["out"] == want, (len(got["out"]), len(want))
+    assert want.count(b"\n") // 4 > 1000
