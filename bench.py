@@ -439,7 +439,7 @@ def run_gpu_arm(args):
                       "selected_records": int(sums[2]), "records": int(sums[3]), "runs_rank0": n_runs},
            "gpu_launches": launches_per_step * args.steps,
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                        "traffic": None, "kernel": "scan_raw_kernel", "kernel_ms": scan_avg_ms,
+                        "traffic": None, "kernel": "fxg::scan_tiles_kernel (fxg_scan.cu; <9,0> literal, <0,0> index only)", "kernel_ms": scan_avg_ms,
                         "pipeline_ms": sum(pipe_ms) / len(pipe_ms), "algorithmic_bytes": algo_bytes, "peak_source": peak_src},
            "clocks": sampler.summary(windows) if sampler else None}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
