@@ -121,9 +121,9 @@ struct AcDevice {              // byte-class compressed Aho-Corasick DFA
 // Packed 2-bit k-mer index for pattern sets over {A,C,G,T} (north_star: "packed 2-bit k-mer hash for the ACGT
 // alphabet").  Every pattern contributes its first `stride` k-mers (offsets 0..stride-1, stride = min pattern
 // length - k + 1), so an occurrence is found by probing every stride-th text position only.  Probe = two bits of a
-// 2^19-bit filter held in shared memory, then an open-addressing table in L2, then byte verification.
+// 2^20-bit filter (128 KB) held in shared memory, then an open-addressing table in L2, then byte verification.
 #ifndef FXG_KMER_FILTER_BITS
-#define FXG_KMER_FILTER_BITS 19
+#define FXG_KMER_FILTER_BITS 20
 #endif
 constexpr int kKmerFilterBits = FXG_KMER_FILTER_BITS;
 constexpr int kKmerFilterWords = 1 << (kKmerFilterBits - 5);

@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(256) fields_ac_kernel(FieldSrc src, unsigned l
 // ---------------------------------------------------------------- multi, ACGT pattern sets: packed 2-bit k-mer index
 // Any-hit only (no first-hit pattern id): used when the caller does not route records per pattern.
 // One thread per field rolls a 2-bit packed k-mer over the field from 16-byte aligned loads; every
-// stride-th position probes a 2^19-bit filter in shared memory; filter hits go to the open-addressing
+// stride-th position probes a 2^20-bit filter in shared memory; filter hits go to the open-addressing
 // table (L2) and candidates are verified byte by byte, so there are no false positives.
 __device__ __noinline__ bool kmer_verify(const KmerDevice &K, unsigned int key, const uint8_t *kstart, const uint8_t *p,
                                             const uint8_t *end)
@@ -152,10 +152,10 @@ __device__ __forceinline__ bool kmer_probe(const unsigned int *filt, const KmerD
 }
 
 #ifndef FXG_KM_THREADS
-#define FXG_KM_THREADS 384
+#define FXG_KM_THREADS 1024
 #endif
 #ifndef FXG_KM_CTAS
-#define FXG_KM_CTAS 3
+#define FXG_KM_CTAS 1
 #endif
 // One field-relative word: `w` = bytes 4r..4r+3 of the field, r in [0, nwords] (r == nwords: the last len & 3 bytes).
 template <int S>
