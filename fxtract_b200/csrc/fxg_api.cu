@@ -45,6 +45,7 @@ struct fxg_ctx {
     unsigned int *d_kfilter = nullptr, *d_kkey = nullptr, *d_kval = nullptr;      // packed k-mer index (ACGT pattern sets)
     unsigned int k_mask = 0, k_kmask = 0; int k_k = 0, k_stride = 0; bool kmer_ok = false;
     unsigned long long *d_slot_hash = nullptr; int *d_slot_pat = nullptr; unsigned int exact_mask = 0;
+    unsigned long long *d_key_words = nullptr; unsigned int *d_key_woff = nullptr;
     // scan resources (shared; everything is ordered on one stream)
     size_t cap_bytes = 0; size_t rec_cap = 0; size_t ntiles_cap = 0; size_t nblocks_cap = 0;
     fxg::TileInfo *d_info = nullptr; unsigned short *d_tile_nl = nullptr; unsigned int *d_tile_hit = nullptr;
@@ -281,6 +282,25 @@ static int build_exact(fxg_ctx *ctx)
     e = cudaMemcpy(ctx->d_slot_pat, sp.data(), nslots * 4, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
     ctx->exact_mask = mask;
+    // the keys once more as zero-padded little-endian words: the look-up kernel verifies 8 bytes per step
+    std::vector<unsigned long long> kw; std::vector<unsigned int> kwoff(n ? n : 1, 0u);
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint8_t *kp = ctx->blob.data() + ctx->off[i];
+        const uint32_t len = ctx->off[i + 1] - ctx->off[i];
+        kwoff[i] = (unsigned int)kw.size();
+        for (uint32_t o = 0; o < len; o += 8) {
+            unsigned long long w = 0;
+            for (uint32_t b = 0; b < 8 && o + b < len; ++b) w |= (unsigned long long)kp[o + b] << (8 * b);
+            kw.push_back(w);
+        }
+    }
+    if (kw.empty()) kw.push_back(0);
+    if (kw.size() > 0xffffffffull) return set_error(ctx, FXG_ERR_UNSUPPORTED, "key set too large for the exact table");
+    if ((e = dev_realloc(ctx->d_key_words, kw.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key words");
+    if ((e = dev_realloc(ctx->d_key_woff, kwoff.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key words");
+    cudaMemcpy(ctx->d_key_words, kw.data(), kw.size() * 8, cudaMemcpyHostToDevice);
+    e = cudaMemcpy(ctx->d_key_woff, kwoff.data(), kwoff.size() * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload key words");
     return FXG_OK;
 }
 
@@ -394,7 +414,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
             FXG_CUDA_OK(launch_fields_ac(src, rec_cap, A, O, st));
         } else {
-            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask};
+            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask, ctx->d_key_words, ctx->d_key_woff};
             FXG_CUDA_OK(launch_fields_exact(src, rec_cap, E, O, st));
         }
         ctx->last_launches += 1;
@@ -510,7 +530,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.done) cudaEventDestroy(s.done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat,
+    void *dev[] = {ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_key_words, ctx->d_key_woff,
                    ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_in, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
@@ -668,7 +688,7 @@ extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *of
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
             FXG_CUDA_OK(launch_fields_ac(src, nrec, A, O, st));
         } else {
-            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask};
+            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask, ctx->d_key_words, ctx->d_key_woff};
             FXG_CUDA_OK(launch_fields_exact(src, nrec, E, O, st));
         }
         ctx->last_launches = 1;

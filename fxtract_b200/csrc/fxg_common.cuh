@@ -149,6 +149,8 @@ struct ExactDevice {           // open-addressing table over whole-field keys
     const uint8_t *blob;                   // pattern bytes
     const unsigned int *off;               // [n+1]
     unsigned int mask;                     // nslots - 1
+    const unsigned long long *kw;          // keys again as zero-padded little-endian 8-byte words (word-wise verification)
+    const unsigned int *kwoff;             // [n] first word of key i
 };
 
 // 64-bit hash of a whole-field key, identical on host and device: the key is read as little-endian 8-byte words

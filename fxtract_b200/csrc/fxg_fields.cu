@@ -262,6 +262,7 @@ __global__ void __launch_bounds__(256) fields_exact_kernel(FieldSrc src, unsigne
         if (k < n) {
             const uint8_t *p; unsigned int len;
             src.get(k, p, len);
+            const uint8_t *fend = p + len;                           // no load starts at or past this address
             // fxg_hash_bytes of the key, 8 bytes per step from aligned loads (64-bit funnel by the field's byte
             // misalignment; nothing past the field's last byte is read).  With stop_at_space the key ends at the
             // first ' ' of the field (exact zero-byte test of word ^ 0x20..20).
@@ -302,8 +303,22 @@ __global__ void __launch_bounds__(256) fields_exact_kernel(FieldSrc src, unsigne
                     int cand = __ldg(&E.slot_pat[slot]);
                     unsigned int a = E.off[cand], b = E.off[cand + 1];
                     if (b - a == len) {
+                        // same aligned walk as the hash, compared with the key's zero-padded words
                         bool eq = true;
-                        for (unsigned int i = 0; i < len; ++i) if (E.blob[a + i] != p[i]) { eq = false; break; }
+                        if (len) {
+                            const unsigned long long *kw = E.kw + __ldg(&E.kwoff[cand]);
+                            const uint8_t *ga = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)7);
+                            const int fs = (int)((uintptr_t)p & 7) * 8;
+                            unsigned long long g0 = __ldg(reinterpret_cast<const unsigned long long *>(ga));
+                            for (unsigned int o = 0; o < len; o += 8) {
+                                ga += 8;
+                                const unsigned long long g1 = ga < fend ? __ldg(reinterpret_cast<const unsigned long long *>(ga)) : 0ull;
+                                unsigned long long w = fs ? (g0 >> fs) | (g1 << (64 - fs)) : g0;
+                                if (len - o < 8) w &= (1ull << (8 * (len - o))) - 1ull;
+                                if (w != __ldg(&kw[o >> 3])) { eq = false; break; }
+                                g0 = g1;
+                            }
+                        }
                         if (eq) { hit = true; pid = cand; break; }
                     }
                 }
