@@ -97,6 +97,30 @@ def test_fields_exact(fx, seed):
     assert nm == sum(1 for w in want if w >= 0)
 
 
+def test_fields_exact_word_boundaries(fx):
+    """Keys of every length 0..33 (the look-up hashes and verifies 8 bytes per step with a masked tail word),
+    each present at every byte misalignment of the packed buffer, next to near misses: one byte changed at each
+    position, one byte shorter, one byte longer."""
+    rng = random.Random(4242)
+    keys = [bytes(rng.choice(b"ACGT:01 ") for _ in range(n)) for n in range(34)]
+    keys = sorted(set(keys))
+    fields = []
+    for k in keys:
+        for pad in range(9):
+            fields.append(bytes(rng.choice(b"xyz") for _ in range(pad)))      # shifts the next field's alignment
+            fields.append(k)
+        for i in range(len(k)):
+            fields.append(k[:i] + bytes([k[i] ^ 1]) + k[i + 1:])
+        fields.append(k[:-1])
+        fields.append(k + b"A")
+        fields.append(k + b"\0")
+    lut = {k: i for i, k in enumerate(keys)}
+    want = [lut.get(x, -1) for x in fields]
+    flags, ids, nm = run_fields(fx, fx.MODE_EXACT, keys, fields, want_id=True)
+    assert ids == want
+    assert nm == sum(1 for w in want if w >= 0) and nm >= 9 * len(keys)
+
+
 @pytest.mark.parametrize("seed", range(8))
 def test_fields_multi_kmer_index(fx, seed):
     """ACGT pattern sets of length >= 12 take the packed 2-bit k-mer index (any-hit, no pattern ids):
