@@ -279,6 +279,7 @@ def run_gpu_arm(args):
     from fxtract_b200 import lib
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the search path has no CPU fallback)")
+    claim_stdout()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -458,8 +459,26 @@ def run_gpu_arm(args):
                       "bytes_per_gpu": int(e2e["bytes"]), "selected_records_rank0": e2e["selected"]}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_leg(fx, w, args.cpu_records)
-    print(json.dumps(out))
+    emit_line(out)
     return 0
+
+
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """Keep the process's stdout for the JSON line alone: native libraries write to fd 1 too (NCCL prints its
+    version banner there), so fd 1 is pointed at stderr and the line goes to a private copy of the old fd 1."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit_line(obj):
+    data = (json.dumps(obj) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_RESULT_FD if _RESULT_FD is not None else 1, data)
 
 
 def main():
