@@ -273,6 +273,44 @@ def cpu_baseline_leg(fx, w, budget_records):
 
 
 # ---------------------------------------------------------------- GPU arm
+def bind_to_gpu_numa_node(torch, local):
+    """Pin this rank to the CPUs of the NUMA node its GPU hangs off, before any pinned host buffer is allocated:
+    the e2e leg streams the whole shard from pinned memory, and first-touch placement on the far socket sends
+    every H2D byte across the inter-socket link.  Returns the node, or None when the box does not say."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bus = None
+        if hasattr(pr, "pci_bus_id"):
+            bus = "%04x:%02x:%02x.0" % (getattr(pr, "pci_domain_id", 0), pr.pci_bus_id, getattr(pr, "pci_device_id", 0))
+        else:
+            import pynvml
+            pynvml.nvmlInit()
+            for i in range(pynvml.nvmlDeviceGetCount()):
+                h = pynvml.nvmlDeviceGetHandleByIndex(i)
+                u = pynvml.nvmlDeviceGetUUID(h)
+                u = u.decode() if isinstance(u, bytes) else u
+                if u.replace("GPU-", "") == str(pr.uuid).replace("GPU-", ""):
+                    b = pynvml.nvmlDeviceGetPciInfo(h).busId
+                    b = b.decode() if isinstance(b, bytes) else b
+                    bus = b.lower()[-12:]
+        if bus is None:
+            return None
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 def run_gpu_arm(args):
     import torch
     import fxtract_b200 as fx
@@ -284,6 +322,7 @@ def run_gpu_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    numa_node = None if args.no_numa_bind else bind_to_gpu_numa_node(torch, local)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -456,7 +495,8 @@ def run_gpu_arm(args):
     if e2e:
         out["e2e"] = {"value": sums[1] / vals[1] / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(sums[1]),
                       "d2h_bytes_per_step": int(e2e["d2h"]) * world, "steps": e2e["steps"], "batch_bytes": args.batch_mib << 20,
-                      "bytes_per_gpu": int(e2e["bytes"]), "selected_records_rank0": e2e["selected"]}
+                      "bytes_per_gpu": int(e2e["bytes"]), "selected_records_rank0": e2e["selected"],
+                      "numa_node_rank0": numa_node}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_leg(fx, w, args.cpu_records)
     emit_line(out)
@@ -493,6 +533,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--e2e-gib", type=float, default=0, help="cap the e2e host shard (0 = whole shard if RAM allows)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not pin the rank to its GPU's NUMA node")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-records", type=int, default=4_000_000, help="records in the cpu_baseline sample")
     ap.add_argument("--ref-records", type=int, default=1_000_000, help="records per step of --impl reference")
