@@ -147,6 +147,10 @@ __device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int ad
 }
 
 __device__ __forceinline__ void note_violation(TileState &T, unsigned int bit) { atomicOr(&T.viol, bit); }
+// TileInfo::viol: bits 0..15 violations, 16..18 guessed phase + 1, bit 31 "some line of this tile has a hit"
+// (tile_finalize_kernel reads the tile's hit words only then)
+constexpr unsigned int kTileHasHit = 0x80000000u;
+constexpr unsigned int kGuessMask = 0x7u;
 
 // byte of the batch at global offset g: from the staged tile when inside it
 __device__ __forceinline__ unsigned int text_byte(const unsigned char *tb, const ScanParams &P,
@@ -287,7 +291,7 @@ __device__ __noinline__ void verify_candidate(ScanSmem &S, TileState &T, const u
                 hit = (sp >= 0) && (p >= sp + 1);
             }
         }
-        if (hit) atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31));
+        if (hit) { atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31)); atomicOr(&T.viol, kTileHasHit); }
     }
 }
 
@@ -643,7 +647,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) scan_tiles_kernel(const Sc
                 }
             }
             if (tid == 0) {
-                const TileInfo ti = {total, T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),
+                // the REDO launch re-checks structure only: the hit words of the first launch stand, and so does their flag
+                const unsigned int kept = REDO ? (P.info[t].viol & kTileHasHit) : 0u;
+                const TileInfo ti = {total, kept | T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),
                                      {(unsigned short)T.cls[0], (unsigned short)T.cls[1], (unsigned short)T.cls[2], (unsigned short)T.cls[3]}};
                 P.info[t] = ti;
             }
@@ -748,7 +754,7 @@ __global__ void __launch_bounds__(256) tile_phase_check_kernel(const ScanParams 
 {
     const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= P.ntiles) return;
-    const unsigned int guess = P.info[t].viol >> 16;
+    const unsigned int guess = (P.info[t].viol >> 16) & kGuessMask;
     if (!guess) return;
     const unsigned long long lb = P.lbase[t] + P.bsum[t / kPrefixSpan];
     if ((unsigned int)(lb & 3) != guess - 1) P.redo_list[atomicAdd(P.redo_count, 1u)] = (unsigned int)t;
@@ -767,7 +773,7 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
     const int r = (int)(lb & 3);
     const int n_tab = ti.total < (unsigned int)kMaxTileLines ? (int)ti.total : kMaxTileLines;
     unsigned int viol = ti.viol & 0xffffu;
-    const unsigned int guess = ti.viol >> 16;            // 0: flags are per (line index mod 4); else guessed phase + 1
+    const unsigned int guess = (ti.viol >> 16) & kGuessMask;   // 0: flags are per (line index mod 4); else guessed phase + 1
     if (guess && (int)(guess - 1) != r) viol |= FXG_V_DENSE_LINES;   // cannot happen after the REDO launch; never pass silently
 #pragma unroll
     for (int k = 0; k < 4; ++k)                  // lines with local index == k (mod 4) have role (k + r) & 3
@@ -801,7 +807,7 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
     if (viol) { atomicOr(&P.ctr->violation, viol); atomicMin(&P.ctr->first_bad, base); }
 
     // line hits -> record hits: only lines whose role is the target's count
-    if (P.match_enabled) {
+    if (P.match_enabled && (ti.viol & kTileHasHit)) {
         const int want = P.target == FXG_TARGET_SEQ ? 1 : (P.target == FXG_TARGET_QUAL ? 3 : 0);
         const unsigned int role_mask = 0x11111111u << ((want - r) & 3);     // 32 % 4 == 0: same mask for every word
         const unsigned int *hw = P.tile_hit + t * (unsigned long long)kHitWords;
@@ -968,6 +974,12 @@ __global__ void __launch_bounds__(kCompactThreads) compact_count_kernel(const Co
 {
     __shared__ unsigned long long red[2][kCompactThreads / 32];
     const unsigned long long nrec = C.ctr->n_lines >> 2;
+    // the grid covers the record capacity of the batch (bytes / smallest record); blocks past the records that
+    // exist leave at once
+    if ((unsigned long long)blockIdx.x * kCompactThreads * 32ull >= nrec) {
+        if (threadIdx.x == 0) C.block_sums[blockIdx.x] = 0ull;
+        return;
+    }
     const unsigned long long w = (unsigned long long)blockIdx.x * kCompactThreads + threadIdx.x;
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
@@ -1013,6 +1025,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
 {
     __shared__ unsigned long long wsum[kCompactThreads / 32];
     const unsigned long long nrec = C.ctr->n_lines >> 2;
+    if ((unsigned long long)blockIdx.x * kCompactThreads * 32ull >= nrec) return;   // no record, no run (block-uniform)
     const unsigned long long w = (unsigned long long)blockIdx.x * kCompactThreads + threadIdx.x;
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
