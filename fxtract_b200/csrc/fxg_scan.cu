@@ -1001,6 +1001,10 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const CompactParams 
     // single CTA: exclusive scan of block_sums in place; total -> out_counts[0]
     __shared__ unsigned long long carry;
     __shared__ unsigned long long wsum[32];
+    // only the blocks that hold records can have run starts (and only they read their prefix)
+    const unsigned long long nrec = C.ctr->n_lines >> 2;
+    const unsigned long long need = (nrec + 32ull * kCompactThreads - 1) / (32ull * kCompactThreads);
+    if (need < nblocks) nblocks = (unsigned int)need;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
     for (unsigned int b0 = 0; b0 < nblocks; b0 += 1024) {
