@@ -6,16 +6,20 @@ HOST := $(ROOT)fxtract_b200/host
 NVCC ?= nvcc
 CXX ?= g++
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -Wall
-CU := $(CSRC)/fxg_scan.cu $(CSRC)/fxg_fields.cu $(CSRC)/fxg_synth.cu $(CSRC)/fxg_api.cu
+CU := $(CSRC)/fxg_scan.cu $(CSRC)/fxg_scan_kmer.cu $(CSRC)/fxg_fields.cu $(CSRC)/fxg_synth.cu $(CSRC)/fxg_api.cu
+CUOBJ := $(patsubst $(CSRC)/%.cu,$(BLD)/%.o,$(CU))
+CUHDR := $(wildcard $(CSRC)/*.cuh) $(ROOT)include/fxgpu.h
 HOSTSRC := $(wildcard $(HOST)/*.cpp)
 
 .PHONY: all lib cli oracle clean fxtract_test ptxas
 all: lib cli
 
 lib: $(BLD)/libfxgpu.so
-$(BLD)/libfxgpu.so: $(CU) $(CSRC)/fxg_common.cuh $(ROOT)include/fxgpu.h
-	mkdir -p $(BLD)
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CU)
+$(BLD)/%.o: $(CSRC)/%.cu $(CUHDR)
+	@mkdir -p $(BLD)
+	$(NVCC) $(NVFLAGS) -c -o $@ $<
+$(BLD)/libfxgpu.so: $(CUOBJ)
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CUOBJ)
 
 cli: $(BLD)/fxtract
 $(BLD)/fxtract: $(HOSTSRC) $(wildcard $(HOST)/*.h) $(BLD)/libfxgpu.so

@@ -14,6 +14,8 @@ static std::string g_last_error;
 
 struct Slot {
     void *pinned = nullptr;             // input staging (host path)
+    uint8_t *d_in = nullptr; size_t d_in_cap = 0;   // device input buffer of this slot (host path: H2D target)
+    cudaEvent_t h2d_done = nullptr;     // recorded on the copy stream after the slot's H2D
     ScanCounters *h_ctr = nullptr;      // pinned result staging
     unsigned long long *h_counts = nullptr;   // [2]: n_runs, n_selected (K6)
     fxg_run *h_runs = nullptr; size_t h_runs_cap = 0;
@@ -42,8 +44,14 @@ struct fxg_ctx {
     fxg::LiteralTable *d_lit = nullptr;
     uint8_t *d_pat = nullptr; uint32_t *d_patoff = nullptr;
     uint8_t *d_cls = nullptr; int *d_next = nullptr; int *d_out = nullptr; int ac_ncls = 0, ac_nstates = 0;
-    unsigned int *d_kfilter = nullptr, *d_kkey = nullptr, *d_kval = nullptr;      // packed k-mer index (ACGT pattern sets)
+    unsigned int *d_kfilter = nullptr, *d_kkey = nullptr, *d_kval = nullptr;      // packed k-mer index of the field engine (ACGT pattern sets)
     unsigned int k_mask = 0, k_kmask = 0; int k_k = 0, k_stride = 0; bool kmer_ok = false;
+    unsigned int *d_ktfilter = nullptr, *d_ktkey = nullptr, *d_ktval = nullptr;   // window index of the fused scan matcher (KmerTile)
+    fxg::KmerTile kt = {}; bool kt_ok = false;
+    int scan_mode = 0;                  // kMode* the raw path runs with (fixed by fxg_set_patterns)
+    int tile_bytes = 0, nl_stride = 0, hit_words = 0;     // geometry of that mode
+    bool two_stage = false;             // FXG_TWO_STAGE=1: multi / exact keep the index pass + field matcher (A/B measurements)
+    cudaStream_t copy_stream = nullptr; // H2D of batch k+1 overlaps the kernels of batch k
     unsigned long long *d_slot_hash = nullptr; int *d_slot_pat = nullptr; unsigned int exact_mask = 0;
     unsigned long long *d_key_words = nullptr; unsigned int *d_key_woff = nullptr;
     // scan resources (shared; everything is ordered on one stream)
@@ -55,12 +63,12 @@ struct fxg_ctx {
     unsigned long long *d_fld_off = nullptr, *d_block_sums = nullptr, *d_counts = nullptr;
     unsigned int *d_fld_len = nullptr;
     // host path
-    uint8_t *d_in = nullptr; size_t d_in_cap = 0;
     uint8_t *d_flags = nullptr; int *d_pid = nullptr; uint32_t *d_off32 = nullptr; size_t d_fields_cap = 0;
     fxg::Slot slots[3];                 // 0,1: host path; 2: device-resident path
     std::deque<int> inflight;
     uint64_t total_selected = 0;
     int last_launches = 0;
+    uint64_t last_d2h_bytes = 0;        // bytes the last collected raw batch brought back (counters + runs)
     bool profiling = false;
     float last_scan_ms = 0.f, last_pipeline_ms = 0.f;
 };
@@ -204,10 +212,9 @@ static int build_ac(fxg_ctx *ctx)
     if ((e = dev_realloc(ctx->d_cls, 256)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc cls");
     if ((e = dev_realloc(ctx->d_next, next.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc dfa");
     if ((e = dev_realloc(ctx->d_out, out.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc dfa out");
-    cudaMemcpy(ctx->d_cls, cls.data(), 256, cudaMemcpyHostToDevice);
-    cudaMemcpy(ctx->d_next, next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice);
-    e = cudaMemcpy(ctx->d_out, out.data(), out.size() * sizeof(int), cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa");
+    if ((e = cudaMemcpy(ctx->d_cls, cls.data(), 256, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa classes");
+    if ((e = cudaMemcpy(ctx->d_next, next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa");
+    if ((e = cudaMemcpy(ctx->d_out, out.data(), out.size() * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa");
     ctx->ac_ncls = ncls; ctx->ac_nstates = (int)ns;
     return FXG_OK;
 }
@@ -254,10 +261,70 @@ static int build_kmer(fxg_ctx *ctx)
     if ((e = dev_realloc(ctx->d_kfilter, filter.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc k-mer filter");
     if ((e = dev_realloc(ctx->d_kkey, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc k-mer table");
     if ((e = dev_realloc(ctx->d_kval, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc k-mer table");
-    cudaMemcpy(ctx->d_kfilter, filter.data(), filter.size() * 4, cudaMemcpyHostToDevice);
-    cudaMemcpy(ctx->d_kkey, hk.data(), nslots * 4, cudaMemcpyHostToDevice);
+    if ((e = cudaMemcpy(ctx->d_kfilter, filter.data(), filter.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload k-mer filter");
+    if ((e = cudaMemcpy(ctx->d_kkey, hk.data(), nslots * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload k-mer table");
     if ((e = cudaMemcpy(ctx->d_kval, hv.data(), nslots * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload k-mer table");
     ctx->k_mask = mask; ctx->k_kmask = kmask; ctx->k_k = k; ctx->k_stride = stride; ctx->kmer_ok = true;
+    return FXG_OK;
+}
+
+// ---------------------------------------------------------------- window index of the fused scan matcher (host build)
+// Usable when every pattern is a string over {A,C,G,T} of length >= 12 (fxg_common.cuh: KmerTile).  Probe stride S
+// (16, 8, 4 or 2 bytes) and window length k <= 16 with k + S - 1 <= shortest pattern: every pattern contributes
+// the windows at its offsets 0..S-1.  The largest S is taken whose k keeps the share of text windows that hit an
+// index entry by chance (entries / 4^k) under 1/64 -- those cost a table walk and a byte comparison each.
+static int build_kmer_tile(fxg_ctx *ctx)
+{
+    ctx->kt_ok = false;
+    const uint32_t n = ctx->npat;
+    uint32_t minlen = 0xffffffffu;
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t len = ctx->off[i + 1] - ctx->off[i];
+        if (len < minlen) minlen = len;
+        for (uint32_t j = ctx->off[i]; j < ctx->off[i + 1]; ++j) if (!fxg_is_acgt(ctx->blob[j])) return FXG_OK;
+    }
+    if (n == 0 || minlen < 12 || n >= (1u << 26)) return FXG_OK;
+    int S = 0, k = 0;
+    for (int s = 16; s >= 2; s >>= 1) {
+        if ((int)minlen - s + 1 < 11) continue;
+        const int kk = std::min(16, (int)minlen - s + 1);
+        const double space = kk >= 16 ? 4294967296.0 : (double)(1ull << (2 * kk));
+        if ((double)n * s / space > 1.0 / 64) continue;
+        S = s; k = kk;
+        break;
+    }
+    if (!S) return FXG_OK;
+    const unsigned int kmask = k == 16 ? 0xffffffffu : ((1u << (2 * k)) - 1u);
+    const size_t entries = (size_t)n * (size_t)S;
+    size_t nslots = 16;
+    while (nslots < entries * 2) nslots <<= 1;
+    if (nslots > ((size_t)1 << 30)) return FXG_OK;
+    const int flw = entries <= 16384 ? 12 : 15;       // 16 KiB filter (2 CTAs / SM) or 128 KiB (1 CTA / SM)
+    std::vector<unsigned int> filter((size_t)1 << flw, 0u), hk(nslots, 0u), hv(nslots, 0u);
+    const unsigned int mask = (unsigned int)(nslots - 1);
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint8_t *p = ctx->blob.data() + ctx->off[i];
+        for (int o = 0; o < S; ++o) {
+            unsigned int key = 0;
+            for (int b = 0; b < k; ++b) key |= fxg_base_code(p[o + b]) << (2 * b);
+            key &= kmask;
+            filter[kmer_tile_filter_word(key, flw)] |= 1u << kmer_tile_filter_bit(key);
+            unsigned int slot = kmer_tile_slot(key, mask);
+            while (hv[slot]) slot = (slot + 1) & mask;
+            hk[slot] = key; hv[slot] = ((i << 5) | (unsigned int)o) + 1u;
+        }
+    }
+    cudaError_t e;
+    if ((e = dev_realloc(ctx->d_ktfilter, filter.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window filter");
+    if ((e = dev_realloc(ctx->d_ktkey, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window table");
+    if ((e = dev_realloc(ctx->d_ktval, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window table");
+    if ((e = cudaMemcpy(ctx->d_ktfilter, filter.data(), filter.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload window filter");
+    if ((e = cudaMemcpy(ctx->d_ktkey, hk.data(), nslots * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload window table");
+    if ((e = cudaMemcpy(ctx->d_ktval, hv.data(), nslots * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload window table");
+    KmerTile &K = ctx->kt;
+    K.filter = ctx->d_ktfilter; K.ht_key = ctx->d_ktkey; K.ht_val = ctx->d_ktval; K.blob = ctx->d_pat; K.off = ctx->d_patoff;
+    K.ht_mask = mask; K.kmask = kmask; K.k = k; K.stride = S; K.filter_log2_words = flw;
+    ctx->kt_ok = true;
     return FXG_OK;
 }
 
@@ -278,7 +345,7 @@ static int build_exact(fxg_ctx *ctx)
     cudaError_t e;
     if ((e = dev_realloc(ctx->d_slot_hash, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
     if ((e = dev_realloc(ctx->d_slot_pat, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
-    cudaMemcpy(ctx->d_slot_hash, sh.data(), nslots * 8, cudaMemcpyHostToDevice);
+    if ((e = cudaMemcpy(ctx->d_slot_hash, sh.data(), nslots * 8, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
     e = cudaMemcpy(ctx->d_slot_pat, sp.data(), nslots * 4, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
     ctx->exact_mask = mask;
@@ -298,7 +365,7 @@ static int build_exact(fxg_ctx *ctx)
     if (kw.size() > 0xffffffffull) return set_error(ctx, FXG_ERR_UNSUPPORTED, "key set too large for the exact table");
     if ((e = dev_realloc(ctx->d_key_words, kw.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key words");
     if ((e = dev_realloc(ctx->d_key_woff, kwoff.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key words");
-    cudaMemcpy(ctx->d_key_words, kw.data(), kw.size() * 8, cudaMemcpyHostToDevice);
+    if ((e = cudaMemcpy(ctx->d_key_words, kw.data(), kw.size() * 8, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload key words");
     e = cudaMemcpy(ctx->d_key_woff, kwoff.data(), kwoff.size() * 4, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload key words");
     return FXG_OK;
@@ -308,26 +375,29 @@ static int build_exact(fxg_ctx *ctx)
 static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
 {
     if (nbytes <= ctx->cap_bytes && ctx->d_info) return FXG_OK;
-    size_t cap = std::max(nbytes, (size_t)1 << 20);
-    size_t ntiles = (cap + kTileBytes - 1) / kTileBytes;
-    size_t rec_cap = cap / 48 + 64;
-    size_t words = (rec_cap + 31) / 32;
-    size_t nblocks = (words + 1023) / 1024 + 1;
+    const size_t cap = std::max(nbytes, (size_t)1 << 20);
+    const size_t ntiles = (cap + ctx->tile_bytes - 1) / ctx->tile_bytes;
+    // a tile holds at most nl_stride lines (denser ones raise FXG_V_DENSE_LINES and the batch is re-routed), so an
+    // accepted batch has at most ntiles * nl_stride / 4 records: every per-record buffer is sized with that
+    const size_t rec_cap = ntiles * (size_t)(ctx->nl_stride / 4) + 64;
+    const size_t words = (rec_cap + 31) / 32;
+    const size_t nblocks = (words + 1023) / 1024 + 1;
+    const bool field_stage = ctx->scan_mode == kModeIndex && ctx->cfg.mode != FXG_MODE_LITERAL;
     cudaError_t e;
     if ((e = dev_realloc(ctx->d_info, ntiles)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile info");
-    if ((e = dev_realloc(ctx->d_tile_nl, ntiles * (size_t)kNlStride)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line tables");
+    if ((e = dev_realloc(ctx->d_tile_nl, ntiles * (size_t)ctx->nl_stride)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line tables");
     if ((e = dev_realloc(ctx->d_lbase, ntiles + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile prefix");
     if ((e = dev_realloc(ctx->d_bsum, ntiles / 4096 + 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc span prefix");
     if ((e = dev_realloc(ctx->d_redo, ntiles + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc redo list");
-    if (ctx->cfg.mode == FXG_MODE_LITERAL &&
-        (e = dev_realloc(ctx->d_tile_hit, ntiles * (size_t)kHitWords)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line hits");
+    if (ctx->scan_mode != kModeIndex &&
+        (e = dev_realloc(ctx->d_tile_hit, ntiles * (size_t)ctx->hit_words)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line hits");
     if ((e = dev_realloc(ctx->d_hitbits, words + 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc hit bitset");
     if (!ctx->d_ctr && (e = dev_realloc(ctx->d_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counters");
     if (!ctx->d_counts && (e = dev_realloc(ctx->d_counts, 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counts");
     if (!ctx->cfg.count_only) {
         if ((e = dev_realloc(ctx->d_block_sums, nblocks)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc block sums");
     }
-    if (ctx->cfg.mode != FXG_MODE_LITERAL) {
+    if (field_stage) {
         if ((e = dev_realloc(ctx->d_fld_off, rec_cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc field table");
         if ((e = dev_realloc(ctx->d_fld_len, rec_cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc field table");
     }
@@ -344,6 +414,9 @@ static int ensure_slot_result(fxg_ctx *ctx, Slot &s)
     return FXG_OK;
 }
 
+// Selected runs come back in two parts: the first kRunPrefix of them ride with the counters (one small copy,
+// enqueued before the count is known); a batch with more runs fetches exactly n_runs once its count has arrived.
+constexpr size_t kRunPrefix = 1024;
 static int ensure_slot_runs(fxg_ctx *ctx, Slot &s)
 {
     size_t want = std::min<size_t>(ctx->rec_cap / 2 + 2, (size_t)1 << 26);
@@ -352,9 +425,9 @@ static int ensure_slot_runs(fxg_ctx *ctx, Slot &s)
         if ((e = dev_realloc(s.d_runs, want)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc runs");
         s.d_runs_cap = want;
     }
-    if (s.h_runs_cap < 65536) {
-        if ((e = host_realloc(s.h_runs, 65536)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned runs");
-        s.h_runs_cap = 65536;
+    if (s.h_runs_cap < kRunPrefix) {
+        if ((e = host_realloc(s.h_runs, kRunPrefix)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned runs");
+        s.h_runs_cap = kRunPrefix;
     }
     return FXG_OK;
 }
@@ -379,9 +452,9 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
         FXG_CUDA_OK(cudaEventRecord(s.ev[0], st));
     }
 
-    size_t ntiles = (nbytes + kTileBytes - 1) / kTileBytes;
-    size_t rec_cap = std::min(ctx->rec_cap, nbytes / 48 + 64);
-    size_t words = (rec_cap + 31) / 32;
+    const size_t ntiles = (nbytes + ctx->tile_bytes - 1) / ctx->tile_bytes;
+    const size_t rec_cap = std::min(ctx->rec_cap, ntiles * (size_t)(ctx->nl_stride / 4) + 64);
+    const size_t words = (rec_cap + 31) / 32;
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_hitbits, 0, (words + 4) * sizeof(unsigned int), st));
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, sizeof(ScanCounters), st));
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_counts, 0, 2 * sizeof(unsigned long long), st));
@@ -389,19 +462,28 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     FXG_CUDA_OK(cudaMemsetAsync(ctx->d_redo + ctx->ntiles_cap, 0, sizeof(unsigned int), st));
     ScanParams P;
     memset(&P, 0, sizeof P);
-    P.buf = d_buf; P.nbytes = nbytes; P.ntiles = ntiles; P.info = ctx->d_info; P.tile_nl = ctx->d_tile_nl;
+    P.buf = d_buf; P.nbytes = nbytes; P.ntiles = ntiles;
+    P.tile_bytes = ctx->tile_bytes; P.nl_stride = ctx->nl_stride; P.hit_words = ctx->hit_words;
+    P.info = ctx->d_info; P.tile_nl = ctx->d_tile_nl;
     P.tile_hit = ctx->d_tile_hit; P.lbase = ctx->d_lbase; P.bsum = ctx->d_bsum; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
     P.rec_cap = rec_cap; P.one = 1;
     P.redo_list = ctx->d_redo; P.redo_count = ctx->d_redo + ctx->ntiles_cap;
     P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
-    P.match_enabled = literal && !ctx->h_lit.all_match && !ctx->h_lit.never;
-    P.lit_unit = ctx->h_lit.unit == 8 && ctx->h_lit.mul1 == 1u ? 9 : ctx->h_lit.unit;
-    if (!literal) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
+    P.mode = ctx->scan_mode;
+    P.match_enabled = P.mode != kModeIndex;
+    P.lit_unit = ctx->h_lit.unit;
+    const bool field_stage = P.mode == kModeIndex && !literal;
+    if (field_stage) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
     P.header_whole = ctx->cfg.mode == FXG_MODE_EXACT && ctx->cfg.target == FXG_TARGET_NAME;
+    if (mode_is_kmer(P.mode)) P.kmer = ctx->kt;
+    if (P.mode == kModeExact) {
+        P.exact = ExactDevice{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask, ctx->d_key_words, ctx->d_key_woff};
+        P.redo_unanchored = 1;
+    }
     if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[1], st));
     FXG_CUDA_OK(launch_scan_raw(P, st, &ctx->last_launches, ctx->profiling ? s.ev[2] : nullptr));
-    if (!literal) {
+    if (field_stage) {
         FieldSrc src; memset(&src, 0, sizeof src);
         src.base = d_buf; src.off64 = ctx->d_fld_off; src.len32 = ctx->d_fld_len; src.n_lines_dev = &ctx->d_ctr->n_lines;
         src.stop_at_space = P.header_whole;
@@ -426,9 +508,8 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
                                    s.d_runs, s.d_runs_cap, inv, st, &ctx->last_launches));
         if (ctx->profiling) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
         FXG_CUDA_OK(cudaMemcpyAsync(s.h_counts, ctx->d_counts, 16, cudaMemcpyDeviceToHost, st));
-        FXG_CUDA_OK(cudaMemcpyAsync(s.h_runs, s.d_runs, std::min<size_t>(s.h_runs_cap, s.d_runs_cap) * sizeof(fxg_run),
-                                    cudaMemcpyDeviceToHost, st));
-        s.runs_copied = std::min<size_t>(s.h_runs_cap, s.d_runs_cap);
+        s.runs_copied = std::min<size_t>(kRunPrefix, s.d_runs_cap);
+        FXG_CUDA_OK(cudaMemcpyAsync(s.h_runs, s.d_runs, s.runs_copied * sizeof(fxg_run), cudaMemcpyDeviceToHost, st));
     }
     if (ctx->profiling && !s.timed) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
     FXG_CUDA_OK(cudaMemcpyAsync(s.h_ctr, ctx->d_ctr, sizeof(ScanCounters), cudaMemcpyDeviceToHost, st));
@@ -457,20 +538,29 @@ static int finish_raw(fxg_ctx *ctx, Slot &s, fxg_result *res)
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     res->n_matched = (literal && ctx->h_lit.all_match) ? res->n_records : c.n_hits;
     res->n_selected = ctx->cfg.invert ? res->n_records - res->n_matched : res->n_matched;
+    uint64_t d2h = sizeof(ScanCounters);
     if (!ctx->cfg.count_only && s.nbytes) {
+        d2h += 16 + s.runs_copied * sizeof(fxg_run);
         unsigned long long nr = s.h_counts[0];
         if (nr > s.d_runs_cap) return set_error(ctx, FXG_ERR_NOMEM, "selected-run list overflow; use smaller batches");
         if (nr > s.runs_copied) {
-            cudaError_t e;
+            // more runs than the prefix that rode with the counters: fetch the rest (d_runs of this slot is not
+            // touched again until the slot is resubmitted)
+            size_t from = s.runs_copied;
             if (s.h_runs_cap < nr) {
-                if ((e = host_realloc(s.h_runs, (size_t)nr)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned runs");
-                s.h_runs_cap = (size_t)nr;
+                cudaError_t e;
+                size_t want = std::max<size_t>((size_t)nr, s.h_runs_cap * 2);
+                if ((e = host_realloc(s.h_runs, want)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned runs");
+                s.h_runs_cap = want;
+                from = 0;
             }
-            // d_runs of this slot is not touched again until the slot is resubmitted
-            FXG_CUDA_OK(cudaMemcpy(s.h_runs, s.d_runs, (size_t)nr * sizeof(fxg_run), cudaMemcpyDeviceToHost));
+            FXG_CUDA_OK(cudaMemcpy(s.h_runs + from, s.d_runs + from, ((size_t)nr - from) * sizeof(fxg_run), cudaMemcpyDeviceToHost));
+            d2h += ((size_t)nr - from) * sizeof(fxg_run);
+            s.runs_copied = (size_t)nr;
         }
         res->n_runs = nr; res->runs = s.h_runs;
     }
+    ctx->last_d2h_bytes = d2h;
     return FXG_OK;
 }
 
@@ -518,6 +608,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->cfg.device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     for (Slot &s : ctx->slots) {
         if (s.pinned) cudaFreeHost(s.pinned);
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
@@ -527,13 +618,16 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h_pid) cudaFreeHost(s.h_pid);
         if (s.h_off) cudaFreeHost(s.h_off);
         if (s.d_runs) cudaFree(s.d_runs);
+        if (s.d_in) cudaFree(s.d_in);
         if (s.done) cudaEventDestroy(s.done);
+        if (s.h2d_done) cudaEventDestroy(s.h2d_done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_key_words, ctx->d_key_woff,
+    void *dev[] = {ctx->d_ktfilter, ctx->d_ktkey, ctx->d_ktval, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_key_words, ctx->d_key_woff,
                    ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
-                   ctx->d_fld_len, ctx->d_in, ctx->d_flags, ctx->d_pid, ctx->d_off32};
+                   ctx->d_fld_len, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -545,13 +639,15 @@ extern "C" int fxg_set_patterns(fxg_ctx *ctx, const uint8_t *blob, const uint32_
     if (ctx->cfg.mode == FXG_MODE_LITERAL && n > 2) return set_error(ctx, FXG_ERR_ARG, "literal mode takes 1 or 2 patterns");
     cudaSetDevice(ctx->cfg.device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     ctx->npat = n;
     ctx->off.assign(off, off + n + 1);
     ctx->blob.assign(blob, blob + off[n]);
     cudaError_t e;
     if ((e = dev_realloc(ctx->d_pat, ctx->blob.size() + 16)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc patterns");
     if ((e = dev_realloc(ctx->d_patoff, (size_t)n + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc patterns");
-    if (!ctx->blob.empty()) cudaMemcpy(ctx->d_pat, ctx->blob.data(), ctx->blob.size(), cudaMemcpyHostToDevice);
+    if (!ctx->blob.empty() && (e = cudaMemcpy(ctx->d_pat, ctx->blob.data(), ctx->blob.size(), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return set_cuda_error(ctx, e, "upload patterns");
     if ((e = cudaMemcpy(ctx->d_patoff, ctx->off.data(), ((size_t)n + 1) * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
         return set_cuda_error(ctx, e, "upload patterns");
     int rc = FXG_OK;
@@ -560,10 +656,35 @@ extern "C" int fxg_set_patterns(fxg_ctx *ctx, const uint8_t *blob, const uint32_
         if (!ctx->d_lit && (e = dev_realloc(ctx->d_lit, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc literal table");
         if ((e = cudaMemcpy(ctx->d_lit, &ctx->h_lit, sizeof(LiteralTable), cudaMemcpyHostToDevice)) != cudaSuccess)
             return set_cuda_error(ctx, e, "upload literal table");
-    } else if (ctx->cfg.mode == FXG_MODE_MULTI) { rc = build_ac(ctx); if (rc == FXG_OK) rc = build_kmer(ctx); }
-    else rc = build_exact(ctx);
-    if (rc == FXG_OK) ctx->have_patterns = true;
-    return rc;
+    } else if (ctx->cfg.mode == FXG_MODE_MULTI) {
+        rc = build_ac(ctx);
+        if (rc == FXG_OK) rc = build_kmer(ctx);
+        if (rc == FXG_OK) rc = build_kmer_tile(ctx);
+    } else rc = build_exact(ctx);
+    if (rc != FXG_OK) return rc;
+    // the scan kernel variant of the raw path
+    const char *ts = getenv("FXG_TWO_STAGE");
+    ctx->two_stage = ts && *ts && strcmp(ts, "0") != 0;
+    int mode = kModeIndex;
+    if (ctx->cfg.mode == FXG_MODE_LITERAL) {
+        if (!ctx->h_lit.all_match && !ctx->h_lit.never)
+            mode = ctx->h_lit.unit == 8 ? (ctx->h_lit.mul1 == 1u ? kModeLit9 : kModeLit8) : kModeLitSmall;
+    } else if (ctx->cfg.mode == FXG_MODE_MULTI) {
+        // fused window matcher: any-hit per line, so only whole-line targets (sequence / quality) use it;
+        // everything else keeps the index pass + field matcher (DFA)
+        if (ctx->kt_ok && !ctx->two_stage && (ctx->cfg.target == FXG_TARGET_SEQ || ctx->cfg.target == FXG_TARGET_QUAL)) {
+            int lg = 0;
+            while ((1 << lg) < ctx->kt.stride) ++lg;
+            mode = kModeKmer + lg;
+        }
+    } else if (!ctx->two_stage) mode = kModeExact;
+    if (mode != ctx->scan_mode || !ctx->tile_bytes) {         // geometry may change: tile tables are re-made on the next batch
+        ctx->scan_mode = mode;
+        scan_geometry(mode, &ctx->tile_bytes, &ctx->nl_stride, &ctx->hit_words);
+        ctx->cap_bytes = 0;
+    }
+    ctx->have_patterns = true;
+    return FXG_OK;
 }
 
 // ---------------------------------------------------------------- host path
@@ -590,25 +711,35 @@ extern "C" int fxg_acquire_buffer(fxg_ctx *ctx, void **pinned, size_t *cap)
     return FXG_OK;
 }
 
-static int ensure_d_in(fxg_ctx *ctx, size_t n)
+static int ensure_d_in(fxg_ctx *ctx, Slot &s, size_t n)
 {
-    if (ctx->d_in_cap >= n + 64) return FXG_OK;
+    cudaError_t e;
+    if (!s.h2d_done && (e = cudaEventCreateWithFlags(&s.h2d_done, cudaEventDisableTiming)) != cudaSuccess) return set_cuda_error(ctx, e, "event");
+    if (!ctx->copy_stream && (e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return set_cuda_error(ctx, e, "copy stream");
+    if (s.d_in_cap >= n + 64) return FXG_OK;
     size_t cap = std::max<size_t>(n, ctx->cfg.batch_bytes) + 64;
-    cudaError_t e = dev_realloc(ctx->d_in, cap);
-    if (e != cudaSuccess) return set_cuda_error(ctx, e, "alloc device input buffer");
-    ctx->d_in_cap = cap;
+    if ((e = dev_realloc(s.d_in, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc device input buffer");
+    s.d_in_cap = cap;
     return FXG_OK;
 }
 
+// Host path, one batch: H2D on the copy stream into the slot's own device buffer, kernels on the compute stream
+// behind an event.  With two slots the copy of batch k+1 runs while the kernels of batch k do (the slot's buffer
+// is free: its previous batch has been collected).
 static int submit_raw_common(fxg_ctx *ctx, int si, const void *src, size_t nbytes, int is_last)
 {
     Slot &s = ctx->slots[si];
     int rc;
     if (nbytes > ctx->cfg.batch_bytes) return set_error(ctx, FXG_ERR_ARG, "batch larger than batch_bytes");
-    if ((rc = ensure_d_in(ctx, nbytes)) != FXG_OK) return rc;
-    if (nbytes) FXG_CUDA_OK(cudaMemcpyAsync(ctx->d_in, src, nbytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (!ctx->have_patterns) return set_error(ctx, FXG_ERR_STATE, "fxg_set_patterns has not been called");
+    if ((rc = ensure_d_in(ctx, s, nbytes)) != FXG_OK) return rc;
+    if (nbytes) {
+        FXG_CUDA_OK(cudaMemcpyAsync(s.d_in, src, nbytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+        FXG_CUDA_OK(cudaEventRecord(s.h2d_done, ctx->copy_stream));
+        FXG_CUDA_OK(cudaStreamWaitEvent(ctx->stream, s.h2d_done, 0));
+    }
     s.is_last = is_last;
-    if ((rc = enqueue_raw(ctx, ctx->d_in, nbytes, s)) != FXG_OK) return rc;
+    if ((rc = enqueue_raw(ctx, s.d_in, nbytes, s)) != FXG_OK) return rc;
     s.state = 2;
     ctx->inflight.push_back(si);
     return FXG_OK;
@@ -647,7 +778,7 @@ extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *of
     int rc;
     cudaError_t e;
     if ((rc = ensure_slot_result(ctx, s)) != FXG_OK) return rc;
-    if ((rc = ensure_d_in(ctx, nbytes)) != FXG_OK) return rc;
+    if ((rc = ensure_d_in(ctx, s, nbytes)) != FXG_OK) return rc;
     if (s.fields_cap < (size_t)nrec + 1) {
         size_t cap = std::max<size_t>((size_t)nrec + 1, 1 << 16);
         if ((e = host_realloc(s.h_flags, cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned flags");
@@ -669,11 +800,11 @@ extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *of
     memset(s.h_ctr, 0, sizeof(ScanCounters));
     if (nrec) {
         memcpy(s.h_off, off, ((size_t)nrec + 1) * 4);
-        if (nbytes) FXG_CUDA_OK(cudaMemcpyAsync(ctx->d_in, s.pinned, nbytes, cudaMemcpyHostToDevice, st));
+        if (nbytes) FXG_CUDA_OK(cudaMemcpyAsync(s.d_in, s.pinned, nbytes, cudaMemcpyHostToDevice, st));
         FXG_CUDA_OK(cudaMemcpyAsync(ctx->d_off32, s.h_off, ((size_t)nrec + 1) * 4, cudaMemcpyHostToDevice, st));
         FXG_CUDA_OK(cudaMemsetAsync(ctx->d_ctr, 0, sizeof(ScanCounters), st));
         FieldSrc src; memset(&src, 0, sizeof src);
-        src.base = ctx->d_in; src.off32 = ctx->d_off32;
+        src.base = s.d_in; src.off32 = ctx->d_off32;
         FieldOut O; memset(&O, 0, sizeof O);
         O.flags = ctx->d_flags; O.pattern_id = ctx->cfg.want_pattern_id ? ctx->d_pid : nullptr; O.n_hits = &ctx->d_ctr->n_hits;
         if (ctx->cfg.mode == FXG_MODE_LITERAL) {
@@ -780,6 +911,7 @@ extern "C" int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res)
 }
 
 extern "C" int fxg_last_launch_count(const fxg_ctx *ctx) { return ctx ? ctx->last_launches : 0; }
+extern "C" uint64_t fxg_last_d2h_bytes(const fxg_ctx *ctx) { return ctx ? ctx->last_d2h_bytes : 0; }
 
 extern "C" int fxg_set_profiling(fxg_ctx *ctx, int enabled)
 {

@@ -12,26 +12,30 @@ namespace fxg {
 int set_cuda_error(fxg_ctx *ctx, cudaError_t e, const char *what);
 
 // ---------------------------------------------------------------- geometry
-// (compile-time; -DFXG_TILE_BYTES / -DFXG_THREADS / -DFXG_MIN_CTAS build the variants compared in DESIGN.md)
-#ifndef FXG_TILE_BYTES
-#define FXG_TILE_BYTES 24576
-#endif
-#ifndef FXG_THREADS
-#define FXG_THREADS 384
-#endif
-#ifndef FXG_MIN_CTAS
-#define FXG_MIN_CTAS 3
-#endif
-constexpr int kTileBytes = FXG_TILE_BYTES;     // bytes of input one CTA scans
-constexpr int kThreads = FXG_THREADS;          // threads per CTA (12 warps)
-constexpr int kMinCtas = FXG_MIN_CTAS;         // resident CTAs per SM the scan kernel is compiled for
-static_assert(kTileBytes % (kThreads * 16) == 0 && kTileBytes <= 65536, "tile = whole 16-byte chunks per thread; u16 positions");
-constexpr int kChunks = kTileBytes / 16;       // 16-byte chunks per tile (1536)
-constexpr int kChunksPerThread = kChunks / kThreads;   // 4
-#ifndef FXG_MAX_TILE_LINES
-#define FXG_MAX_TILE_LINES (FXG_TILE_BYTES / 8)
-#endif
-constexpr int kMaxTileLines = FXG_MAX_TILE_LINES;   // newline-table capacity per tile (denser tiles are reported, not parsed)
+// The scan kernel is compiled for two tile geometries (template parameter of scan_tiles_kernel):
+//   G24  24 KiB tiles, 12 warps, 3 CTAs / SM   literal, exact and index-only passes
+//   G32  32 KiB tiles, 16 warps, 2 CTAs / SM   fused k-mer matcher (room for its filter in shared memory;
+//                                              1 CTA / SM when the pattern set needs the 128 KiB filter)
+// Every warp owns a contiguous 2 KiB segment of its tile in both.  Kernels downstream of the scan (prefix,
+// finalize, compaction) read the geometry of the batch from ScanParams at run time.
+template <int TILE_BYTES, int THREADS, int MIN_CTAS> struct Geom {
+    static constexpr int kTileBytes = TILE_BYTES;           // bytes of input one CTA scans per step
+    static constexpr int kThreads = THREADS;
+    static constexpr int kMinCtas = MIN_CTAS;                // resident CTAs per SM the kernel is compiled for
+    static constexpr int kChunks = TILE_BYTES / 16;          // 16-byte chunks per tile
+    static constexpr int kWarps = THREADS / 32;
+    static constexpr int kWarpChunks = kChunks / kWarps;     // chunks one warp covers (contiguous)
+    static constexpr int kChunksPerThread = kChunks / THREADS;
+    // newline-table capacity per tile: one line per 12 bytes.  A denser tile raises FXG_V_DENSE_LINES (the batch is
+    // re-routed), so an accepted batch holds at most ntiles * kMaxTileLines / 4 records: the record capacity every
+    // per-record buffer is sized with (48 bytes per record).
+    static constexpr int kMaxTileLines = ((TILE_BYTES / 12) + 7) & ~7;
+    static constexpr int kHitWords = kMaxTileLines / 32 + 1; // line-hit words per tile (local line indices 0..kMaxTileLines)
+    static_assert(TILE_BYTES % (THREADS * 16) == 0 && TILE_BYTES <= 65536, "tile = whole 16-byte chunks per thread; u16 positions");
+    static_assert(kWarps % 4 == 0, "every line role has its own warps");
+};
+typedef Geom<24576, 384, 3> G24;
+typedef Geom<32768, 512, 2> G32;
 constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
 
 // ---------------------------------------------------------------- per-tile results
@@ -48,8 +52,6 @@ struct __align__(16) TileInfo {
     unsigned short cls[4];       // OR of the line flags of the lines with local index == k (mod 4): low byte = the
                                  // line itself, high byte = class flags of the head of the following line
 };
-constexpr int kNlStride = kMaxTileLines;           // u16 entries per tile in the global '\n' table
-constexpr int kHitWords = kMaxTileLines / 32 + 1;  // line-hit words per tile (local line indices 0..kMaxTileLines)
 constexpr long long kNoPos = -(1ll << 62);
 
 // ---------------------------------------------------------------- counters
@@ -83,13 +85,63 @@ struct LiteralTable {
     unsigned short masks[64];    // bit (pattern*8 + shift) set if keys[i] == pat[shift..shift+U)
 };
 
+// Scan modes (template parameter of scan_tiles_kernel)
+constexpr int kModeIndex = 0;        // record index + canonical predicate only (a second-stage field matcher follows)
+constexpr int kModeLitSmall = 1;     // literal, patterns shorter than 15 bytes: aligned units of 4 / 2 / 1 bytes
+constexpr int kModeLit8 = 8;         // literal, aligned 8-byte-unit fingerprints (two multipliers)
+constexpr int kModeLit9 = 9;         // ... first multiplier 1
+constexpr int kModeKmer = 16;        // + log2(probe stride): 17 (S=2), 18 (S=4), 19 (S=8), 20 (S=16): fused packed k-mer matcher
+constexpr int kModeExact = 30;       // fused whole-field hash look-up (FileManager::find)
+__host__ __device__ constexpr bool mode_is_kmer(int m) { return m >= 17 && m <= 20; }
+__host__ __device__ constexpr bool mode_is_literal(int m) { return m == 1 || m == 8 || m == 9; }
+
+// Fused multi-pattern matcher for pattern sets over {A,C,G,T} (north_star: "packed 2-bit k-mer hash for the ACGT
+// alphabet ... warp-cooperative scan over coalesced 16-byte loads with overlap handling at chunk edges").
+// Position-centric: every 16-byte chunk of the staged tile is packed to 32 bits (2 bits per byte), a window of k <= 16
+// bases that starts at a byte offset == 0 (mod S) is the funnel shift of two neighbouring chunk words (the neighbour
+// comes from the next lane by shuffle), and is looked up in a one-bit hashed filter in shared memory.  Every pattern
+// contributes its first S windows (offsets 0..S-1, k + S - 1 <= shortest pattern), so each occurrence contains one
+// probed window.  Filter hits are queued per warp and resolved after the newline table exists: open-addressing table
+// (L2) -> byte-wise verification against the pattern -> "local line i has a match" bit.  No false positives, no
+// false negatives; bytes that are not bases only make keys that no pattern has.
+struct KmerTile {
+    const unsigned int *filter;            // [1 << filter_log2_words] device copy, staged into shared memory per CTA
+    const unsigned int *ht_key;            // [nslots] packed window
+    const unsigned int *ht_val;            // [nslots] 0 = empty, else ((pattern id << 5) | offset) + 1
+    const uint8_t *blob;                   // pattern bytes
+    const unsigned int *off;               // [n+1]
+    unsigned int ht_mask;                  // nslots - 1
+    unsigned int kmask;                    // (1 << 2k) - 1
+    int k, stride;                         // stride in {2, 4, 8, 16}
+    int filter_log2_words;                 // 12 (16 KiB, 2 CTAs / SM) or 15 (128 KiB, 1 CTA / SM)
+};
+// window key of bases b[0..k): base i in bits 2i, 2i+1 (code = (byte >> 1) & 3); identical on host and device
+constexpr unsigned int kKmerHashMul = 0x9E3779B1u;
+__host__ __device__ inline unsigned int kmer_tile_filter_word(unsigned int key, int log2_words) { return (key * kKmerHashMul) >> (32 - log2_words); }
+__host__ __device__ inline unsigned int kmer_tile_filter_bit(unsigned int key) { return 31u - ((key * kKmerHashMul) & 31u); }
+__host__ __device__ inline unsigned int kmer_tile_slot(unsigned int key, unsigned int mask) { return ((key * kKmerHashMul) >> 7) & mask; }
+
+struct ExactDevice {           // open-addressing table over whole-field keys
+    const unsigned long long *slot_hash;   // [nslots] 0 = empty
+    const int *slot_pat;                   // [nslots] pattern id
+    const uint8_t *blob;                   // pattern bytes
+    const unsigned int *off;               // [n+1]
+    unsigned int mask;                     // nslots - 1
+    const unsigned long long *kw;          // keys again as zero-padded little-endian 8-byte words (word-wise verification)
+    const unsigned int *kwoff;             // [n] first word of key i
+};
+
 struct ScanParams {
     const uint8_t *buf;
     unsigned long long nbytes;
     unsigned long long ntiles;
+    // geometry of this batch (run-time copy of the Geom the scan kernel was launched with)
+    int tile_bytes;                   // Geom::kTileBytes
+    int nl_stride;                    // Geom::kMaxTileLines: u16 entries per tile in tile_nl
+    int hit_words;                    // Geom::kHitWords: words per tile in tile_hit
     TileInfo *info;                   // [ntiles]
-    unsigned short *tile_nl;          // [ntiles * kNlStride] tile-relative '\n' positions
-    unsigned int *tile_hit;           // [ntiles * kHitWords] line-hit bits (literal mode)
+    unsigned short *tile_nl;          // [ntiles * nl_stride] tile-relative '\n' positions
+    unsigned int *tile_hit;           // [ntiles * hit_words] line-hit bits (literal / k-mer / exact modes)
     unsigned long long *lbase;        // [ntiles] '\n' count before each tile, relative to its 4096-tile span
     unsigned long long *bsum;         // [ntiles / 4096 + 1] '\n' count before each span
     ScanCounters *ctr;
@@ -98,12 +150,17 @@ struct ScanParams {
     const LiteralTable *lit;          // device copy
     const uint8_t *pat_bytes;         // device copy of pattern bytes
     int target;
-    int match_enabled;                // 0: index/validate only (multi / exact use the field table)
-    int lit_unit;                     // host copy of lit->unit (selects the kernel variant)
+    int mode;                         // kMode*: selects the scan kernel variant
+    int match_enabled;                // 1: the scan kernel leaves line hits in tile_hit (literal / k-mer / exact);
+                                      // 0: index/validate only (a second-stage field matcher uses the field table)
+    int lit_unit;                     // host copy of lit->unit
     unsigned int one;                 // == 1 (lets the kernel issue adds as IMAD; see fma_add)
     unsigned int *redo_list;          // [ntiles] tiles whose locally guessed line phase was wrong (normally none)
     unsigned int *redo_count;         // [1]
-    // field table for the second-stage matchers (multi / exact): target field of record k
+    int redo_unanchored;              // exact mode: tiles without a phase anchor go to the REDO launch too
+    KmerTile kmer;                    // mode_is_kmer(mode)
+    ExactDevice exact;                // mode == kModeExact
+    // field table for the second-stage matchers (multi without k-mer index): target field of record k
     unsigned long long *fld_off;      // [rec_cap] or nullptr
     unsigned int *fld_len;            // [rec_cap]
     int header_whole;                 // name target, exact strategy: the field table holds the whole header line (after '@');
@@ -142,16 +199,6 @@ __host__ __device__ inline unsigned int fxg_base_code(unsigned int b) { return (
 __host__ __device__ inline bool fxg_is_acgt(unsigned int b) { return b == 'A' || b == 'C' || b == 'G' || b == 'T'; }
 __host__ __device__ inline unsigned int fxg_kmer_hash(unsigned int key) { return key * 0x9E3779B1u; }
 __host__ __device__ inline unsigned int fxg_kmer_hash2(unsigned int key) { return key * 0xC2B2AE35u; }   // top bits used
-
-struct ExactDevice {           // open-addressing table over whole-field keys
-    const unsigned long long *slot_hash;   // [nslots] 0 = empty
-    const int *slot_pat;                   // [nslots] pattern id
-    const uint8_t *blob;                   // pattern bytes
-    const unsigned int *off;               // [n+1]
-    unsigned int mask;                     // nslots - 1
-    const unsigned long long *kw;          // keys again as zero-padded little-endian 8-byte words (word-wise verification)
-    const unsigned int *kwoff;             // [n] first word of key i
-};
 
 // 64-bit hash of a whole-field key, identical on host and device: the key is read as little-endian 8-byte words
 // (the last 1..7 bytes zero padded into one more word), each word is folded in with one multiply, the length goes
@@ -214,8 +261,10 @@ struct LiteralFieldParams {
 
 
 // launchers (fxg_scan.cu / fxg_fields.cu / fxg_synth.cu)
-size_t scan_smem_bytes();
+void scan_geometry(int mode, int *tile_bytes, int *nl_stride, int *hit_words);
 cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launches, cudaEvent_t after_scan);
+cudaError_t launch_scan_kmer(const ScanParams &P, cudaStream_t stream, int dev);
+cudaError_t launch_scan_kmer_redo(const ScanParams &P, cudaStream_t stream, int dev);
 cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
                            fxg_run *runs, unsigned long long run_cap, int invert, cudaStream_t stream, int *launches);

@@ -1,0 +1,101 @@
+// fxg_exact.cuh -- whole-field key look-up, shared by the field engine (fxg_fields.cu: packed fields / field table in
+// global memory) and the fused scan kernel (fxg_scan_kernel.cuh: keys read from the staged tile in shared memory).
+//
+// Replaces manager.find(*data) of hash_search (main.cpp:315, fileManager.cpp:171-177: std::map<string,int>::find).
+// Open addressing over the 64-bit key hash of fxg_hash_bytes; a slot whose hash matches is verified word by word
+// against a zero-padded copy of the key, so no parity claim rests on the hash.
+#pragma once
+#include "fxg_common.cuh"
+
+namespace fxg {
+
+// Word loaders: aligned 32-bit word i of the byte space the key lives in.
+struct GlobalWords {
+    const unsigned int *w;          // 4-byte aligned base
+    long long limit;                // words with index >= limit are not read (they lie past the last byte of interest)
+    __device__ __forceinline__ unsigned int operator()(long long i) const { return i < limit ? __ldg(w + i) : 0u; }
+};
+struct TileWords {
+    const unsigned int *w;          // staged tile (shared memory); reads past the tile stay inside the CTA's allocation
+    __device__ __forceinline__ unsigned int operator()(long long i) const { return w[i]; }
+};
+
+// Key = bytes [start, start + len) of the loader's byte space; with stop_at_space it ends at the first ' ' before that
+// (the read name of a header line).  8 bytes per step: two funnel shifts by the key's byte misalignment.
+template <class LD>
+__device__ __forceinline__ bool exact_lookup(const ExactDevice &E, const LD &ld, long long start, unsigned int len,
+                                             bool stop_at_space, int &pid)
+{
+    const long long w0 = start >> 2;
+    const int sh = (int)(start & 3) * 8;
+    unsigned long long h = kHashSeed;
+    unsigned int used = 0;
+    if (len) {
+        long long wi = w0;
+        unsigned int g0 = ld(wi);
+        for (;;) {
+            const unsigned int g1 = ld(wi + 1), g2 = ld(wi + 2);
+            const unsigned long long w = (unsigned long long)__funnelshift_r(g0, g1, sh) |
+                                         ((unsigned long long)__funnelshift_r(g1, g2, sh) << 32);
+            unsigned int left = len - used;                  // key bytes still to come, this word included
+            bool last = left <= 8;
+            if (stop_at_space) {
+                const unsigned long long x = w ^ 0x2020202020202020ull;
+                const unsigned long long z = (x - 0x0101010101010101ull) & ~x & 0x8080808080808080ull;
+                if (z) {
+                    const unsigned int sp = (unsigned int)(__ffsll((long long)z) - 1) >> 3;
+                    if (sp < left) { left = sp; last = true; }
+                }
+            }
+            if (left >= 8) { h = fxg_hash_word(h, w); used += 8; }
+            else if (left) { h = fxg_hash_word(h, w & ((1ull << (8 * left)) - 1ull)); used += left; }
+            if (last) break;
+            g0 = g2;
+            wi += 2;
+        }
+    }
+    len = used;
+    h = fxg_hash_finish(h, len);
+    unsigned int slot = (unsigned int)(h >> 20) & E.mask;
+    for (;;) {
+        const unsigned long long sv = __ldg(&E.slot_hash[slot]);
+        if (sv == 0) return false;
+        if (sv == h) {
+            const int cand = __ldg(&E.slot_pat[slot]);
+            const unsigned int a = __ldg(&E.off[cand]), b = __ldg(&E.off[cand + 1]);
+            if (b - a == len) {
+                bool eq = true;
+                if (len) {
+                    const unsigned long long *kw = E.kw + __ldg(&E.kwoff[cand]);
+                    long long wi = w0;
+                    unsigned int g0 = ld(wi);
+                    for (unsigned int o = 0; o < len; o += 8) {
+                        const unsigned int g1 = ld(wi + 1), g2 = ld(wi + 2);
+                        unsigned long long w = (unsigned long long)__funnelshift_r(g0, g1, sh) |
+                                               ((unsigned long long)__funnelshift_r(g1, g2, sh) << 32);
+                        if (len - o < 8) w &= (1ull << (8 * (len - o))) - 1ull;
+                        if (w != __ldg(&kw[o >> 3])) { eq = false; break; }
+                        g0 = g2;
+                        wi += 2;
+                    }
+                }
+                if (eq) { pid = cand; return true; }
+            }
+        }
+        slot = (slot + 1) & E.mask;
+    }
+}
+
+// key in global memory: bytes [p, p + len) of a buffer whose last readable byte is at or after p + len - 1
+// rounded up to a 4-byte word (all library buffers carry 64 bytes of slack)
+__device__ __forceinline__ bool exact_lookup_global(const ExactDevice &E, const uint8_t *p, unsigned int len,
+                                                    bool stop_at_space, int &pid)
+{
+    const uintptr_t a = (uintptr_t)p;
+    GlobalWords ld;
+    ld.w = reinterpret_cast<const unsigned int *>(a & ~(uintptr_t)3);
+    ld.limit = (long long)(((a & 3) + len + 3) >> 2);
+    return exact_lookup(E, ld, (long long)(a & 3), len, stop_at_space, pid);
+}
+
+}  // namespace fxg

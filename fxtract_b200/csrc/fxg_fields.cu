@@ -13,6 +13,7 @@
 //   exact   : manager.find(field) on std::map<string,int>         fileManager.cpp:171-177
 //             open-addressing table, 64-bit hash + byte verification
 #include "fxg_common.cuh"
+#include "fxg_exact.cuh"
 
 namespace fxg {
 
@@ -251,6 +252,8 @@ __global__ void __launch_bounds__(FXG_KM_THREADS, FXG_KM_CTAS) fields_kmer_kerne
 }
 
 // ---------------------------------------------------------------- exact: thread per field, hash probe + verify
+// (exact_lookup of fxg_exact.cuh: fxg_hash_bytes of the key 8 bytes per step from aligned loads, nothing past the
+// field's last word is read; with stop_at_space the key ends at the first ' ' of the field)
 __global__ void __launch_bounds__(256) fields_exact_kernel(FieldSrc src, unsigned long long n, ExactDevice E, FieldOut O)
 {
     n = src.count(n);
@@ -262,68 +265,8 @@ __global__ void __launch_bounds__(256) fields_exact_kernel(FieldSrc src, unsigne
         if (k < n) {
             const uint8_t *p; unsigned int len;
             src.get(k, p, len);
-            const uint8_t *fend = p + len;                           // no load starts at or past this address
-            // fxg_hash_bytes of the key, 8 bytes per step from aligned loads (64-bit funnel by the field's byte
-            // misalignment; nothing past the field's last byte is read).  With stop_at_space the key ends at the
-            // first ' ' of the field (exact zero-byte test of word ^ 0x20..20).
-            unsigned long long h = kHashSeed;
-            unsigned int used = 0;
-            if (len) {
-                const uint8_t *end = p + len;
-                const uint8_t *ga = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)7);
-                const int sh = (int)((uintptr_t)p & 7) * 8;
-                unsigned long long g0 = __ldg(reinterpret_cast<const unsigned long long *>(ga));
-                for (;;) {
-                    ga += 8;
-                    const unsigned long long g1 = ga < end ? __ldg(reinterpret_cast<const unsigned long long *>(ga)) : 0ull;
-                    unsigned long long w = sh ? (g0 >> sh) | (g1 << (64 - sh)) : g0;
-                    unsigned int left = len - used;                  // key bytes still to come, this word included
-                    bool last = left <= 8;
-                    if (src.stop_at_space) {
-                        const unsigned long long x = w ^ 0x2020202020202020ull;
-                        const unsigned long long z = (x - 0x0101010101010101ull) & ~x & 0x8080808080808080ull;
-                        if (z) {
-                            const unsigned int sp = (unsigned int)(__ffsll((long long)z) - 1) >> 3;
-                            if (sp < left) { left = sp; last = true; }
-                        }
-                    }
-                    if (left >= 8) { h = fxg_hash_word(h, w); used += 8; }
-                    else if (left) { h = fxg_hash_word(h, w & ((1ull << (8 * left)) - 1ull)); used += left; }
-                    if (last) break;
-                    g0 = g1;
-                }
-            }
-            len = used;
-            h = fxg_hash_finish(h, len);
-            unsigned int slot = (unsigned int)(h >> 20) & E.mask;
-            for (;;) {
-                unsigned long long sh = __ldg(&E.slot_hash[slot]);
-                if (sh == 0) break;
-                if (sh == h) {
-                    int cand = __ldg(&E.slot_pat[slot]);
-                    unsigned int a = E.off[cand], b = E.off[cand + 1];
-                    if (b - a == len) {
-                        // same aligned walk as the hash, compared with the key's zero-padded words
-                        bool eq = true;
-                        if (len) {
-                            const unsigned long long *kw = E.kw + __ldg(&E.kwoff[cand]);
-                            const uint8_t *ga = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)7);
-                            const int fs = (int)((uintptr_t)p & 7) * 8;
-                            unsigned long long g0 = __ldg(reinterpret_cast<const unsigned long long *>(ga));
-                            for (unsigned int o = 0; o < len; o += 8) {
-                                ga += 8;
-                                const unsigned long long g1 = ga < fend ? __ldg(reinterpret_cast<const unsigned long long *>(ga)) : 0ull;
-                                unsigned long long w = fs ? (g0 >> fs) | (g1 << (64 - fs)) : g0;
-                                if (len - o < 8) w &= (1ull << (8 * (len - o))) - 1ull;
-                                if (w != __ldg(&kw[o >> 3])) { eq = false; break; }
-                                g0 = g1;
-                            }
-                        }
-                        if (eq) { hit = true; pid = cand; break; }
-                    }
-                }
-                slot = (slot + 1) & E.mask;
-            }
+            hit = exact_lookup_global(E, p, len, src.stop_at_space != 0, pid);
+            if (!hit) pid = -1;
         }
         emit_thread_per_field(O, k, n, hit, pid);
     }

@@ -1,0 +1,861 @@
+// fxg_scan_kernel.cuh -- the fused per-tile scan kernel of the raw FASTQ path (Path A), as a template over the
+// tile geometry and the matcher mode.  Instantiated in fxg_scan.cu (G24: literal / exact / index-only) and
+// fxg_scan_kmer.cu (G32: fused packed k-mer matcher).
+//
+// Replaces, for canonical 4-line FASTQ, the reference's per-record loop
+//   kstream::read (kseq.hpp:120-164)        ->  record boundaries
+//   prepare_data (main.cpp:291-304)         ->  target field
+//   strstr x1..2 (main.cpp:568-588)         ->  literal hit            (modes 1 / 8 / 9)
+//   ssearch_scan (main.cpp:406,426)         ->  multi-pattern hit      (modes 17..20, ACGT pattern sets)
+//   manager.find (main.cpp:315)             ->  whole-field look-up    (mode 30)
+//   on_match (main.cpp:258-271)             ->  count / select
+// with a position-centric kernel that has NO cross-tile dependency.  Every CTA takes one tile, pulls it into
+// shared memory with one bulk async copy (TMA engine, mbarrier completion) and then
+//   1. main pass, 16 bytes per lane per step, SWAR only: byte range check, per-chunk class summaries ("has a
+//      byte < 0x41", "has a byte < 0x21") as ballot bit rows, the list of chunks that can hold a '\n', and the
+//      matcher's filter (literal: fingerprint of aligned 8-byte units; k-mer: packed 2-bit windows against a
+//      hashed bit filter in shared memory);
+//   2. ordered table of the tile's '\n' positions (warp-local masks, ballot prefix);
+//   3. phase anchor: the first "+" line among local lines 1..31 gives the tile's guessed line phase;
+//   4. one thread per line, one line role per warp: record structure and character classes under the guessed
+//      phase (tiles without anchor: flags for all four phases at once); exact mode: the target-role warps hash
+//      their line's key from shared memory and probe the table;
+//   5. filter candidates are verified byte by byte and recorded as "local line i has a match";
+//   6. the tile publishes {count, violations + guess, '\n' table, line-hit bits}.
+// The epilogue kernels (fxg_scan.cu) turn counts into global line numbers, check every guess against the true
+// phase (wrong guess -> REDO launch), check the few lines that straddle tile edges and map line hits to record
+// hits.  The canonical-FASTQ predicate is what makes kseq-parse-then-print the identity on
+// the record bytes; a batch that violates it is reported (never silently mis-parsed) and the host re-routes it.
+#pragma once
+#include "fxg_common.cuh"
+#include "fxg_exact.cuh"
+
+namespace fxg {
+
+constexpr int kPrefixThreads = 1024;
+constexpr int kPrefixSpan = 4 * kPrefixThreads;
+
+struct TileState {
+    unsigned int cls[4];                  // generic path: line flags OR-ed per (local line index mod 4)
+    unsigned int n_cand, viol;
+};
+
+template <class G> struct __align__(128) ScanSmem {
+    // staged tile bytes, double buffered (bulk-copy destinations).  Chunk 0 of each buffer holds the 16 bytes in
+    // front of the tile (k-mer windows that start there end in this tile), chunks 1.. the tile itself.
+    uint4 tile[2][G::kChunks + 1];
+    unsigned short nlpos[G::kMaxTileLines + 16];      // tile-relative '\n' positions, in order (+ slack, see step 3)
+    unsigned short wl[G::kWarps][G::kWarpChunks];     // per warp: its chunks that contain a byte < 0x21 ('\n' candidates)
+    unsigned short wm[G::kWarps][G::kWarpChunks];     // per entry of wl: 16-bit mask of the bytes < 0x20 of that chunk
+    unsigned int wtot[2][G::kWarps];                  // '\n' count of each warp's 2 KiB segment (by tile parity)
+    unsigned int below[17];                           // interleaved-layout mask of the bytes < p of a chunk
+    unsigned int sbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x41 (not a sequence letter)
+    unsigned int qbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x21 (not a quality char)
+    unsigned int linehit[G::kHitWords];               // bit i: local line i has a (phase-conditional) match
+    union {
+        struct {
+            unsigned long long keys[64];
+            unsigned int fp[64];
+            unsigned short masks[64];
+            int cand_off[kCandCap];                   // tile-relative offset of a candidate unit
+            unsigned short cand_mask[kCandCap];       // (pattern,shift) bits to verify
+        } lit;
+        // k-mer mode: per warp, (chunk index within the warp's segment << 8) | filter-hit bits of that chunk
+        unsigned short kq[G::kWarps][G::kWarpChunks];
+    } m;
+    unsigned long long mbar[2];                       // bulk-copy completion barriers
+    // per-tile scalars, double buffered by tile parity: the copy of the previous tile is reset by
+    // thread 0 while the current one is in use (no extra barrier between "last read" and "first write")
+    TileState st[2];
+};
+
+__device__ __forceinline__ void reset_state(TileState &T)
+{
+    T.n_cand = 0; T.viol = 0;
+    T.cls[0] = T.cls[1] = T.cls[2] = T.cls[3] = 0;
+}
+
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ unsigned int smem_u32(const void *p) { return (unsigned int)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *mbar, unsigned int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(mbar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *mbar, unsigned int bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(bytes) : "memory");
+}
+// 1-D bulk async copy global -> shared (TMA engine), completion counted in bytes on the mbarrier
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned int bytes, unsigned long long *mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(mbar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *mbar, unsigned int parity)
+{
+    asm volatile("{\n"
+                 ".reg .pred P1;\n"
+                 "LAB_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+                 "@P1 bra DONE;\n"
+                 "bra LAB_WAIT;\n"
+                 "DONE:\n"
+                 "}" ::"r"(smem_u32(mbar)), "r"(parity) : "memory");
+}
+
+// ---------------------------------------------------------------- SWAR helpers (bytes < 0x80)
+constexpr unsigned int kHi = 0x80808080u;
+constexpr unsigned int kAdd20 = 0x60606060u;   // (w + kAdd20) has bit7 set per byte iff byte >= 0x20
+constexpr unsigned int kAdd21 = 0x5f5f5f5fu;   // ... iff byte >= 0x21
+constexpr unsigned int kAdd41 = 0x3f3f3f3fu;   // ... iff byte >= 0x41
+
+// x + k issued as IMAD (fma pipe) instead of IADD3 (alu pipe): the main pass is bound by the
+// alu pipe (LOP3/SHF/IADD3 share it at half rate), so the SWAR threshold adds go to the other
+// pipe.  `one` is a kernel parameter equal to 1 that ptxas cannot fold away.
+__device__ __forceinline__ unsigned int fma_add(unsigned int x, unsigned int one, unsigned int k)
+{
+    unsigned int r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(one), "r"(k));
+    return r;
+}
+
+// Interleaved-layout mask: bit (8k + 7 - i) set iff byte k of word i (byte 4i+k of the chunk) is
+// below the threshold encoded by `add`.  4 adds, 3 shifts, 4 LOP3 (bitwise selects).
+__device__ __forceinline__ unsigned int il_mask(const uint4 &x, unsigned int add)
+{
+    unsigned int t = x.x + add;
+    t = (t & 0x80808080u) | (((x.y + add) >> 1) & 0x40404040u);
+    t = (t & 0xc0c0c0c0u) | (((x.z + add) >> 2) & 0x20202020u);
+    t = (t & 0xe0e0e0e0u) | (((x.w + add) >> 3) & 0x10101010u);
+    return ~t & 0xf0f0f0f0u;
+}
+
+__constant__ unsigned int kBelowTab[17] = {
+    0x00000000u, 0x00000080u, 0x00008080u, 0x00808080u, 0x80808080u, 0x808080c0u, 0x8080c0c0u, 0x80c0c0c0u, 0xc0c0c0c0u,
+    0xc0c0c0e0u, 0xc0c0e0e0u, 0xc0e0e0e0u, 0xe0e0e0e0u, 0xe0e0e0f0u, 0xe0e0f0f0u, 0xe0f0f0f0u, 0xf0f0f0f0u};
+
+// 16-bit mask, bit b set iff byte b of the chunk is below the threshold encoded by `add`
+__device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int add)
+{
+    unsigned int n0 = ((~(x.x + add) & kHi) * 0x00204081u) >> 28;
+    unsigned int n1 = ((~(x.y + add) & kHi) * 0x00204081u) >> 28;
+    unsigned int n2 = ((~(x.z + add) & kHi) * 0x00204081u) >> 28;
+    unsigned int n3 = ((~(x.w + add) & kHi) * 0x00204081u) >> 28;
+    return n0 | (n1 << 4) | (n2 << 8) | (n3 << 12);
+}
+
+// 2-bit codes of the 16 bytes of a chunk, byte i in bits 2i, 2i+1 (code = (byte >> 1) & 3: A 0, C 1, T 2, G 3).
+// Per word: mask bits 1..2 of every byte, one multiply gathers the four codes in the top byte (the partial
+// products land on disjoint bits, so nothing carries), three byte permutes assemble the chunk word.
+__device__ __forceinline__ unsigned int pack16(const uint4 &x)
+{
+    const unsigned int m0 = (x.x & 0x06060606u) * 0x00820820u, m1 = (x.y & 0x06060606u) * 0x00820820u;
+    const unsigned int m2 = (x.z & 0x06060606u) * 0x00820820u, m3 = (x.w & 0x06060606u) * 0x00820820u;
+    return __byte_perm(__byte_perm(m0, m1, 0x0073), __byte_perm(m2, m3, 0x0073), 0x5410);
+}
+
+__device__ __forceinline__ void note_violation(TileState &T, unsigned int bit) { atomicOr(&T.viol, bit); }
+// TileInfo::viol: bits 0..15 violations, 16..18 guessed phase + 1, bit 31 "some line of this tile has a hit"
+// (tile_finalize_kernel reads the tile's hit words only then)
+constexpr unsigned int kTileHasHit = 0x80000000u;
+constexpr unsigned int kGuessMask = 0x7u;
+
+// byte of the batch at global offset g: from the staged tile when inside it
+template <class G>
+__device__ __forceinline__ unsigned int text_byte(const unsigned char *tb, const ScanParams &P, unsigned long long base, long long g)
+{
+    long long rel = g - (long long)base;
+    if (rel >= 0 && rel < G::kTileBytes) return tb[rel];
+    return P.buf[g];
+}
+
+// '\n' count in tile bytes [0, rel): lower bound in the finished position table
+template <class G> __device__ __forceinline__ unsigned int lines_before(const ScanSmem<G> &S, int n_tab, int rel)
+{
+    int lo = 0, hi = n_tab;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if ((int)S.nlpos[mid] < rel) lo = mid + 1; else hi = mid;
+    }
+    return (unsigned int)lo;
+}
+
+// any bit set in rows[lo, hi) (chunk indices) of both class bit rows
+template <class G>
+__device__ __forceinline__ void range_any2(const ScanSmem<G> &S, int lo, int hi, unsigned int &anyS, unsigned int &anyQ)
+{
+    anyS = 0; anyQ = 0;
+    if (lo >= hi) return;
+    const int wl = lo >> 5, wh = (hi - 1) >> 5;
+    const unsigned int ml = 0xffffffffu << (lo & 31), mh = 0xffffffffu >> (31 - ((hi - 1) & 31));
+    if (wl == wh) { anyS = S.sbits[wl] & ml & mh; anyQ = S.qbits[wl] & ml & mh; return; }
+    anyS = (S.sbits[wl] & ml) | (S.sbits[wh] & mh);
+    anyQ = (S.qbits[wl] & ml) | (S.qbits[wh] & mh);
+    for (int w = wl + 1; w < wh; ++w) { anyS |= S.sbits[w]; anyQ |= S.qbits[w]; }
+}
+
+// ---------------------------------------------------------------- per-line checks (phase-free)
+// Flags of local line i (the line that ends at nlpos[i]) and class flags of the head of
+// line i+1 (the bytes after that '\n' inside the same 16-byte chunk).
+constexpr unsigned int kFA = 1, kFB = 2, kFC = 4, kFD = 8, kFS = 16, kFQ = 32, kFSP = 64, kFCTL = 128;
+//  kFA  not a header line: empty or first byte != '@'          (FXG_V_HEADER_AT)
+//  kFSP ends with ' ' (separator would not round-trip)          (FXG_V_HEADER_SPACE)
+//  kFB  empty line (as a sequence: FXG_V_EMPTY_SEQ)
+//  kFC  not exactly "+"                                         (FXG_V_PLUS_LINE)
+//  kFD  length differs from the line two above                  (FXG_V_QUAL_LEN)
+//  kFS  has a byte outside [0x41,0x7e]                          (FXG_V_SEQ_CLASS)
+//  kFQ  has a byte outside [0x21,0x7e]                          (FXG_V_QUAL_CLASS)
+//  kFCTL ends with a control byte other than '\n' (any role)    (FXG_V_BYTE_RANGE)
+template <class G>
+__device__ __forceinline__ void line_flags(const ScanSmem<G> &S, const uint4 *tile, int i, int n_tab, unsigned int &own,
+                                           unsigned int &nxt)
+{
+    const unsigned char *tb = reinterpret_cast<const unsigned char *>(tile);
+    const int pos = S.nlpos[i];
+    const bool ctl = tb[pos] != '\n';             // a control byte posing as a line end
+    const int prev = i > 0 ? (int)S.nlpos[i - 1] : -1;
+    const int next = i + 1 < n_tab ? (int)S.nlpos[i + 1] : G::kTileBytes;
+    const int c = pos >> 4, cb = c << 4, cp = prev >> 4;
+    const uint4 x = tile[c];
+    const unsigned int s16 = il_mask(x, kAdd41), q16 = il_mask(x, kAdd21);
+    const int pb = pos - cb;
+    const int lo = prev + 1 > cb ? prev + 1 - cb : 0;
+    const unsigned int r_tail = S.below[pb] & ~S.below[lo];
+    const int hi = next - cb < 16 ? next - cb : 16;
+    const unsigned int r_head = S.below[hi] & ~S.below[pb + 1];
+    unsigned int ms, mq;
+    range_any2(S, cp + 1, c, ms, mq);
+    own = (((s16 & r_tail) | ms) ? kFS : 0u) | (((q16 & r_tail) | mq) ? kFQ : 0u);
+    nxt = ((s16 & r_head) ? kFS : 0u) | ((q16 & r_head) ? kFQ : 0u);
+    if (ctl) own |= kFCTL;
+    if (i >= 1) {                              // line starts inside the tile: structure is local
+        const int llen = pos - prev - 1;
+        const unsigned int fb = tb[prev + 1], lb = tb[pos - 1];
+        if (llen < 1) own |= kFA | kFB | kFC;
+        else {
+            if (fb != '@') own |= kFA;
+            if (lb == ' ') own |= kFSP;
+            if (llen != 1 || fb != '+') own |= kFC;
+        }
+        if (i >= 3 && llen != (int)S.nlpos[i - 2] - (int)S.nlpos[i - 3] - 1) own |= kFD;
+    }
+}
+
+// FXG_V_* bits of a line with flags f if its role is `role` (0 header, 1 sequence, 2 plus, 3 quality)
+__host__ __device__ inline unsigned int role_kinds(unsigned int f, int role)
+{
+    if (role == 0) return ((f & kFA) ? FXG_V_HEADER_AT : 0u) | ((f & kFSP) ? FXG_V_HEADER_SPACE : 0u);
+    if (role == 1) return ((f & kFB) ? FXG_V_EMPTY_SEQ : 0u) | ((f & kFS) ? FXG_V_SEQ_CLASS : 0u);
+    if (role == 2) return (f & kFC) ? FXG_V_PLUS_LINE : 0u;
+    return ((f & kFD) ? FXG_V_QUAL_LEN : 0u) | ((f & kFQ) ? FXG_V_QUAL_CLASS : 0u);
+}
+// line role the target field lives on
+__host__ __device__ inline int target_role(int target) { return target == FXG_TARGET_SEQ ? 1 : (target == FXG_TARGET_QUAL ? 3 : 0); }
+
+// ---------------------------------------------------------------- verification of one literal candidate
+// A verified occurrence is recorded on its local line; whether that line has the target's
+// role (sequence / quality / header) is decided by tile_finalize_kernel.  Header targets add
+// the geometric condition (inside the name / inside the comment), which is phase-free.
+template <class G>
+__device__ __noinline__ void verify_candidate(ScanSmem<G> &S, TileState &T, const unsigned char *tb, const ScanParams &P,
+                                              unsigned long long base, int n_tab, int unit_rel, unsigned int bits)
+{
+    const LiteralTable *lit = P.lit;
+    while (bits) {
+        int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        int pat = b >> 3, s = b & 7;
+        int len = lit->pat_len[pat];
+        long long p = (long long)base + unit_rel - s;
+        if (p < 0 || (unsigned long long)(p + len) > P.nbytes) continue;
+        const uint8_t *pb = P.pat_bytes + lit->pat_off[pat];
+        bool ok = true;
+        for (int k = 0; k < len; ++k) {
+            if (text_byte<G>(tb, P, base, p + k) != pb[k]) { ok = false; break; }
+        }
+        if (!ok) continue;
+        // local line: number of '\n' before p inside the tile (an occurrence that starts in the
+        // previous tile lies on this tile's line 0)
+        int rel = (int)(p - (long long)base);
+        unsigned int loc = rel > 0 ? lines_before(S, n_tab, rel) : 0u;
+        bool hit = true;
+        if (P.target == FXG_TARGET_NAME || P.target == FXG_TARGET_COMMENT) {
+            // header line: name = (ls, first ' ' or end), comment = after that ' '
+            long long ls;
+            if (loc >= 1 && loc <= (unsigned int)n_tab) ls = (long long)base + S.nlpos[loc - 1] + 1;
+            else {
+                long long q = (p < (long long)base ? p : (long long)base) - 1;
+                int guard = 1 << 20;
+                while (q >= 0 && P.buf[q] != '\n' && --guard) --q;
+                if (!guard) { note_violation(T, FXG_V_DENSE_LINES); continue; }
+                ls = q + 1;
+            }
+            long long q = ls + 1, sp = -1;
+            for (;; ++q) {
+                if ((unsigned long long)q >= P.nbytes) break;
+                unsigned int ch = text_byte<G>(tb, P, base, q);
+                if (ch == '\n') break;
+                if (ch == ' ') { sp = q; break; }
+            }
+            if (P.target == FXG_TARGET_NAME) {
+                long long name_end = sp >= 0 ? sp : q;
+                hit = (p >= ls + 1) && (p + len <= name_end);
+            } else {
+                hit = (sp >= 0) && (p >= sp + 1);
+            }
+        }
+        if (hit) { atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31)); atomicOr(&T.viol, kTileHasHit); }
+    }
+}
+
+template <class G> __device__ __forceinline__ void push_candidate(ScanSmem<G> &S, TileState &T, int unit_rel, unsigned int bits)
+{
+    unsigned int slot = atomicAdd(&T.n_cand, 1u);
+    if (slot < kCandCap) { S.m.lit.cand_off[slot] = unit_rel; S.m.lit.cand_mask[slot] = (unsigned short)bits; }
+}
+
+// generic (short-pattern) literal filter: units of 4, 2 or 1 bytes compared against every key
+template <class G>
+__device__ __noinline__ void filter_small_units(ScanSmem<G> &S, TileState &T, unsigned int x0, unsigned int x1, unsigned int x2,
+                                                unsigned int x3, int off, int U, int nkeys)
+{
+    for (int u = 0; u < 16; u += U) {
+        const int wi = u >> 2;
+        unsigned int word = wi == 0 ? x0 : (wi == 1 ? x1 : (wi == 2 ? x2 : x3));
+        unsigned int val = U == 4 ? word : (U == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu) : ((word >> ((u & 3) * 8)) & 0xffu));
+        for (int k = 0; k < nkeys; ++k)
+            if ((unsigned int)S.m.lit.keys[k] == val) push_candidate(S, T, off + u, S.m.lit.masks[k]);
+    }
+}
+
+// ---------------------------------------------------------------- k-mer mode: one filter hit -> table -> bytes
+// `win_rel` = tile-relative offset of the first byte of the window (>= -16), `key` its packed bases.  Every
+// pattern that holds this window at one of its first S offsets is compared byte by byte with the text; the first
+// one that matches marks the local line of the occurrence (all of them lie on the same line).
+template <class G>
+__device__ __noinline__ void kmer_resolve(ScanSmem<G> &S, TileState &T, const unsigned char *tb, const ScanParams &P,
+                                          unsigned long long base, int n_tab, int win_rel, unsigned int key)
+{
+    const KmerTile &K = P.kmer;
+    unsigned int slot = kmer_tile_slot(key, K.ht_mask);
+    for (;;) {
+        const unsigned int v = __ldg(&K.ht_val[slot]);
+        if (!v) return;
+        if (__ldg(&K.ht_key[slot]) == key) {
+            const unsigned int q = (v - 1u) >> 5, o = (v - 1u) & 31u;
+            const unsigned int a = __ldg(&K.off[q]), m = __ldg(&K.off[q + 1]) - a;
+            const long long p = (long long)base + win_rel - (long long)o;
+            if (p >= 0 && (unsigned long long)p + m <= P.nbytes) {
+                bool eq = true;
+                for (unsigned int i = 0; i < m; ++i)
+                    if (text_byte<G>(tb, P, base, p + i) != K.blob[a + i]) { eq = false; break; }
+                if (eq) {
+                    const long long rel = p - (long long)base;
+                    const unsigned int loc = rel > 0 ? lines_before(S, n_tab, (int)rel) : 0u;
+                    atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31));
+                    atomicOr(&T.viol, kTileHasHit);
+                    return;
+                }
+            }
+        }
+        slot = (slot + 1) & K.ht_mask;
+    }
+}
+
+// ---------------------------------------------------------------- exact mode: key of one whole line of the tile
+// Line = tile bytes [a, e).  Returns true when the target field of that line is a key of the table.
+__device__ __forceinline__ bool exact_line_tile(const ScanParams &P, const unsigned char *tb, int a, int e)
+{
+    int ks = a, ke = e;
+    bool stop = false;
+    if (P.target == FXG_TARGET_NAME) { ks = a + 1; stop = true; }            // name: after '@' up to the first ' '
+    else if (P.target == FXG_TARGET_COMMENT) {                               // comment: after the first ' '
+        int sp = e;
+        for (int q = a + 1; q < e; ++q) if (tb[q] == ' ') { sp = q + 1; break; }
+        ks = sp;
+    }
+    if (ks > ke) return false;
+    TileWords ld;
+    ld.w = reinterpret_cast<const unsigned int *>(tb);
+    int pid;
+    return exact_lookup(P.exact, ld, (long long)ks, (unsigned int)(ke - ks), stop, pid);
+}
+// the same over global memory: line = batch bytes [a, e)
+__device__ __forceinline__ bool exact_line_global(const ScanParams &P, long long a, long long e)
+{
+    long long ks = a, ke = e;
+    bool stop = false;
+    if (P.target == FXG_TARGET_NAME) { ks = a + 1; stop = true; }
+    else if (P.target == FXG_TARGET_COMMENT) {
+        long long sp = e;
+        for (long long q = a + 1; q < e; ++q) if (P.buf[q] == ' ') { sp = q + 1; break; }
+        ks = sp;
+    }
+    if (ks > ke) return false;
+    int pid;
+    return exact_lookup_global(P.exact, P.buf + ks, (unsigned int)(ke - ks), stop, pid);
+}
+
+// ---------------------------------------------------------------- class check of a byte range
+// any bit set in row[lo, hi) (chunk indices)
+__device__ __forceinline__ unsigned int row_any(const unsigned int *row, int lo, int hi)
+{
+    if (lo >= hi) return 0u;
+    const int wl = lo >> 5, wh = (hi - 1) >> 5;
+    const unsigned int ml = 0xffffffffu << (lo & 31), mh = 0xffffffffu >> (31 - ((hi - 1) & 31));
+    if (wl == wh) return row[wl] & ml & mh;
+    unsigned int any = (row[wl] & ml) | (row[wh] & mh);
+    for (int w = wl + 1; w < wh; ++w) any |= row[w];
+    return any;
+}
+// non-zero iff tile bytes [a, b) hold a byte below 0x41 (seq) / 0x21 (!seq)
+template <class G>
+__device__ __forceinline__ unsigned int class_bad(const ScanSmem<G> &S, const uint4 *tile, int a, int b, bool seq)
+{
+    if (b <= a) return 0u;
+    const unsigned int add = seq ? kAdd41 : kAdd21;
+    const unsigned int *row = seq ? S.sbits : S.qbits;
+    const int ca = a >> 4, cb = (b - 1) >> 4;
+    const unsigned int ma = il_mask(tile[ca], add) & ~S.below[a - (ca << 4)];
+    if (ca == cb) return ma & S.below[b - (ca << 4)];
+    const unsigned int mb = il_mask(tile[cb], add) & S.below[b - (cb << 4)];
+    return ma | mb | row_any(row, ca + 1, cb);
+}
+
+// ---------------------------------------------------------------- kernel 1: per-tile scan
+// Persistent CTAs: tile t = blockIdx.x, += gridDim.x.  The next tile is prefetched into the other shared-memory
+// buffer while the current one is processed.
+// MODE = kMode* (fxg_common.cuh).  REDO = second launch over the (normally empty) list of tiles whose locally
+// guessed line phase turned out wrong (exact mode: also the tiles without anchor): those are re-evaluated with the
+// phase-free per-line path, exact look-ups under the true phase.
+template <class G, int MODE, bool REDO>
+__global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(const ScanParams P)
+{
+    constexpr int kTileBytes = G::kTileBytes, kThreads = G::kThreads, kChunks = G::kChunks, kWarps = G::kWarps;
+    constexpr int kWarpChunks = G::kWarpChunks, kChunksPerThread = G::kChunksPerThread, kMaxTileLines = G::kMaxTileLines;
+    constexpr int kHitWords = G::kHitWords;
+    constexpr bool LIT8 = MODE == kModeLit8 || MODE == kModeLit9;
+    constexpr bool LIT = mode_is_literal(MODE);
+    constexpr bool KMER = mode_is_kmer(MODE);
+    constexpr bool EXACT = MODE == kModeExact;
+    constexpr int SB = KMER ? (1 << (MODE - kModeKmer)) : 16;          // probe stride (bytes == bases)
+    constexpr int NPROBE = 16 / SB;
+    constexpr bool HITS = MODE != kModeIndex && (!REDO || EXACT);     // this launch produces line-hit words
+    typedef ScanSmem<G> Smem;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem &S = *reinterpret_cast<Smem *>(smem_raw);
+    unsigned int *filt = reinterpret_cast<unsigned int *>(smem_raw + sizeof(Smem));   // k-mer filter (dynamic tail)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const LiteralTable *lit = P.lit;
+    const unsigned long long n_work = REDO ? (unsigned long long)*P.redo_count : P.ntiles;
+    if ((unsigned long long)blockIdx.x >= n_work) return;
+#define FXG_TILE_OF(k) (REDO ? (unsigned long long)P.redo_list[(k)] : (unsigned long long)(k))
+    // issue the bulk copy of tile `tt` into buffer `bf` (thread 0): with the 16 bytes in front of it in k-mer mode
+#define FXG_ISSUE_TILE(tt, bf)                                                                                          \
+    do {                                                                                                                \
+        const unsigned long long b__ = (tt) * (unsigned long long)kTileBytes;                                           \
+        const unsigned long long rem__ = P.nbytes - b__;                                                                \
+        const unsigned int bulk__ = (unsigned int)(rem__ < (unsigned long long)kTileBytes ? rem__ : (unsigned long long)kTileBytes) & ~15u; \
+        if (KMER && SB < 16 && (tt) > 0) {                                                                               \
+            mbar_expect_tx(&S.mbar[bf], bulk__ + 16u);                                                                  \
+            bulk_g2s(&S.tile[bf][0], P.buf + b__ - 16, bulk__ + 16u, &S.mbar[bf]);                                      \
+        } else if (bulk__) {                                                                                            \
+            mbar_expect_tx(&S.mbar[bf], bulk__);                                                                        \
+            bulk_g2s(&S.tile[bf][1], P.buf + b__, bulk__, &S.mbar[bf]);                                                 \
+        }                                                                                                               \
+    } while (0)
+
+    // ---- once per CTA: tables, barriers, first tile in flight
+    if (tid == 0) {
+        mbar_init(&S.mbar[0], 1);
+        mbar_init(&S.mbar[1], 1);
+        const unsigned long long t0 = FXG_TILE_OF(blockIdx.x);
+        FXG_ISSUE_TILE(t0, 0);
+        reset_state(S.st[0]);
+        reset_state(S.st[1]);
+    }
+    if (tid >= 128 && tid < 145) S.below[tid - 128] = kBelowTab[tid - 128];
+    if (MODE != kModeIndex) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
+    int lit_unit = 0, lit_nkeys = 0;
+    unsigned int lit_mul1 = 0, lit_mul2 = 0, lit_shift = 26;
+    if (LIT) {
+        lit_unit = lit->unit; lit_nkeys = lit->n_keys; lit_mul1 = lit->mul1; lit_mul2 = lit->mul2; lit_shift = (unsigned int)lit->shift;
+        if (tid >= 64 && tid < 128) {
+            const int k = tid - 64;
+            S.m.lit.keys[k] = lit->keys[k]; S.m.lit.fp[k] = lit->fp[k]; S.m.lit.masks[k] = lit->masks[k];
+        }
+    }
+    unsigned int kmask = 0, fshift = 0;
+    if (KMER && !REDO) {
+        kmask = P.kmer.kmask; fshift = 32u - (unsigned int)P.kmer.filter_log2_words;
+        const int nw = 1 << P.kmer.filter_log2_words;
+        const uint4 *src = reinterpret_cast<const uint4 *>(P.kmer.filter);
+        uint4 *dst = reinterpret_cast<uint4 *>(filt);
+        for (int w = tid; w < nw / 4; w += kThreads) dst[w] = __ldg(src + w);
+        // the tile at offset 0 has nothing in front of it: a line feed (no base) in every byte of the lead-in chunk
+        if (tid < 2) S.tile[tid][0] = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
+    }
+    const unsigned int one = P.one;
+    const unsigned int lt_mask = (1u << lane) - 1u;
+    unsigned short *my_list = S.wl[warp];
+    unsigned short *my_mask = S.wm[warp];
+    unsigned short *my_kq = S.m.kq[warp];
+    const int trole = target_role(P.target);
+    __syncthreads();
+
+    unsigned int it = 0;
+    for (unsigned long long k = blockIdx.x; k < n_work; k += gridDim.x, ++it) {
+        const unsigned long long t = FXG_TILE_OF(k);
+        const int cur = (int)(it & 1u);
+        const uint4 *tile = &S.tile[cur][1];
+        TileState &T = S.st[cur];
+        const unsigned char *tb = reinterpret_cast<const unsigned char *>(tile);
+        const unsigned long long base = t * (unsigned long long)kTileBytes;
+        const unsigned long long remain = P.nbytes - base;
+        const int tile_len = remain < (unsigned long long)kTileBytes ? (int)remain : kTileBytes;
+        const int bulk = tile_len & ~15;
+
+        // ---- prefetch the next tile of this CTA into the other buffer (free since the end of the
+        //      previous iteration); reset the other copy of the per-tile scalars
+        if (tid == 0) {
+            if (it) reset_state(S.st[cur ^ 1]);
+            const unsigned long long kn = k + gridDim.x;
+            if (kn < n_work) {
+                const unsigned long long tn = FXG_TILE_OF(kn);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                FXG_ISSUE_TILE(tn, cur ^ 1);
+            }
+        }
+        if (tile_len < kTileBytes) {             // ragged end of the batch: patch by hand, neutral filler
+            for (int b = bulk + tid * 16; b < kTileBytes; b += kThreads * 16) {
+                unsigned int w[4] = {0x78787878u, 0x78787878u, 0x78787878u, 0x78787878u};
+                for (int q = 0; q < 16 && b + q < tile_len; ++q) {
+                    unsigned int by = P.buf[base + b + q];
+                    w[q >> 2] = (w[q >> 2] & ~(0xffu << ((q & 3) * 8))) | (by << ((q & 3) * 8));
+                }
+                S.tile[cur][1 + (b >> 4)] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            __syncthreads();
+        }
+        if (bulk || (KMER && SB < 16 && t > 0)) mbar_wait(&S.mbar[cur], (it >> 1) & 1u);
+
+        // ---- 1. main pass: 16 bytes per lane per step, SWAR only.  Per chunk: byte range, "has a
+        //         byte < 0x41" / "< 0x21" ballot rows, list of the chunks with a byte < 0x21 (the only
+        //         ones that can hold a '\n'), matcher filter.
+        unsigned int wcount = 0, kqn = 0;
+        {
+            unsigned int hi_acc = 0;
+            // k-mer mode: packed word of the chunk in front of the lane's chunk (lane 0: carried from lane 31 of
+            // the previous step; first step: the chunk in front of the warp's segment)
+            unsigned int carry = 0;
+            if (KMER && !REDO && SB < 16) carry = pack16(tile[warp * kWarpChunks - 1]);
+#pragma unroll
+            for (int j = 0; j < kChunksPerThread; ++j) {
+                const int c = warp * kWarpChunks + j * 32 + lane;
+                const uint4 x = tile[c];
+                hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);     // bytes >= 0x7f anywhere
+                hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
+                hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
+                hi_acc |= x.w | fma_add(x.w, one, 0x01010101u);
+                const bool s_any = ((fma_add(x.x, one, kAdd41) & fma_add(x.y, one, kAdd41) & fma_add(x.z, one, kAdd41) &
+                                     fma_add(x.w, one, kAdd41)) & kHi) != kHi;
+                const bool q_any = ((fma_add(x.x, one, kAdd21) & fma_add(x.y, one, kAdd21) & fma_add(x.z, one, kAdd21) &
+                                     fma_add(x.w, one, kAdd21)) & kHi) != kHi;
+                const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
+                const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
+                S.sbits[c >> 5] = sb;                                 // warp-uniform address and value: every lane stores
+                S.qbits[c >> 5] = qb;
+                if (q_any) my_list[wcount + __popc(qb & lt_mask)] = (unsigned short)c;
+                wcount += __popc(qb);
+                if (LIT8 && !REDO) {
+                    const unsigned int r0 = MODE == kModeLit9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
+                    const unsigned int r1 = MODE == kModeLit9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
+                    const bool c0 = S.m.lit.fp[r0 >> lit_shift] == r0, c1 = S.m.lit.fp[r1 >> lit_shift] == r1;
+                    if (__any_sync(0xffffffffu, c0 || c1)) {          // rare: keep the hot loop branch-free
+                        if (c0) push_candidate(S, T, c << 4, S.m.lit.masks[r0 >> lit_shift]);
+                        if (c1) push_candidate(S, T, (c << 4) + 8, S.m.lit.masks[r1 >> lit_shift]);
+                    }
+                } else if (MODE == kModeLitSmall && !REDO) {
+                    if ((c << 4) < tile_len) filter_small_units(S, T, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
+                } else if (KMER && !REDO) {
+                    // windows of k bases that start at byte 0, SB, 2 SB, ... of the chunk IN FRONT of the lane's own
+                    // (SB == 16: of the lane's own chunk -- the window never leaves it)
+                    const unsigned int pk = pack16(x);
+                    unsigned int acc = 0;
+                    if (SB == 16) {
+                        const unsigned int h = (pk & kmask) * kKmerHashMul;
+                        acc = __funnelshift_l(0u, filt[h >> fshift], h) >> 31;
+                    } else {
+                        unsigned int pp = __shfl_up_sync(0xffffffffu, pk, 1);
+                        if (lane == 0) pp = carry;
+                        carry = __shfl_sync(0xffffffffu, pk, 31);
+#pragma unroll
+                        for (int s = 0; s < 16; s += SB) {
+                            const unsigned int key = (s ? __funnelshift_r(pp, pk, 2 * s) : pp) & kmask;
+                            const unsigned int h = key * kKmerHashMul;
+                            // filter bit 31 - (h & 31) of word h >> fshift, moved to the top and shifted into acc
+                            acc = __funnelshift_l(__funnelshift_l(0u, filt[h >> fshift], h), acc, 1);
+                        }
+                    }
+                    const unsigned int vb = __ballot_sync(0xffffffffu, acc != 0u);
+                    if (vb) {
+                        if (acc) my_kq[kqn + __popc(vb & lt_mask)] = (unsigned short)(((j * 32 + lane) << 8) | acc);
+                        kqn += __popc(vb);
+                    }
+                }
+            }
+            if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(T, FXG_V_BYTE_RANGE);
+        }
+
+        // ---- 2. (warp local) masks of the bytes < 0x20 of the listed chunks, their count in the warp's segment
+        //         (that every such byte is a '\n' is checked per line in step 4)
+        {
+            __syncwarp();
+            unsigned int cnt = 0;
+            for (unsigned int q = lane; q < wcount; q += 32) {
+                const unsigned int m16 = lin_mask(tile[my_list[q]], kAdd20);
+                my_mask[q] = (unsigned short)m16;
+                cnt += __popc(m16);
+            }
+            cnt = __reduce_add_sync(0xffffffffu, cnt);
+            if (lane == 0) S.wtot[cur][warp] = cnt;
+        }
+        __syncthreads();
+
+        // ---- 3. (warp local) ordered '\n' position table
+        unsigned int total;
+        {
+            const unsigned int wt = lane < kWarps ? S.wtot[cur][lane] : 0u;
+            total = __reduce_add_sync(0xffffffffu, wt);
+            unsigned int idx0 = __reduce_add_sync(0xffffffffu, lane < warp ? wt : 0u);
+            for (unsigned int q0 = 0; q0 < wcount; q0 += 32) {
+                const unsigned int q = q0 + lane;
+                unsigned int m16 = q < wcount ? (unsigned int)my_mask[q] : 0u;
+                const int cb = q < wcount ? ((int)my_list[q] << 4) - 1 : 0;
+                const unsigned int n = __popc(m16);
+                unsigned int idx, round_total;
+                // exclusive prefix of the per-lane counts: two ballots while no chunk holds more than two '\n'
+                const unsigned int b1 = __ballot_sync(0xffffffffu, n >= 1u), b2 = __ballot_sync(0xffffffffu, n >= 2u);
+                if (!__any_sync(0xffffffffu, n >= 3u)) {
+                    idx = idx0 + __popc(b1 & lt_mask) + __popc(b2 & lt_mask);
+                    round_total = __popc(b1) + __popc(b2);
+                } else {
+                    unsigned int inc = n;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                        if (lane >= d) inc += o;
+                    }
+                    idx = idx0 + inc - n;
+                    round_total = __shfl_sync(0xffffffffu, inc, 31);
+                }
+                idx0 += round_total;
+                // the table has 16 entries of slack: clamping the first index keeps every store inside it
+                unsigned short *dst = &S.nlpos[idx < (unsigned int)kMaxTileLines ? idx : (unsigned int)kMaxTileLines];
+                if (m16) {
+                    dst[0] = (unsigned short)(cb + __ffs(m16));
+                    m16 &= m16 - 1;
+                    if (m16) {
+                        dst[1] = (unsigned short)(cb + __ffs(m16));
+                        m16 &= m16 - 1;
+                        for (int k2 = 2; m16; ++k2) {
+                            dst[k2] = (unsigned short)(cb + __ffs(m16));
+                            m16 &= m16 - 1;
+                        }
+                    }
+                }
+            }
+        }
+        const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
+        if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(T, FXG_V_DENSE_LINES);
+        __syncthreads();
+
+        // ---- 3b. phase anchor: the first line among local lines 1..31 that is exactly "+" (every warp looks
+        //          for itself -- cheaper than a block-wide minimum and one more barrier)
+        unsigned int plus_idx = 0xffffffffu;
+        if (!REDO) {
+            bool is_plus = false;
+            if (lane >= 1 && lane < n_tab) {
+                const int e = S.nlpos[lane];
+                is_plus = e - (int)S.nlpos[lane - 1] == 2 && tb[e - 1] == '+';
+            }
+            const unsigned int pb = __ballot_sync(0xffffffffu, is_plus);
+            if (pb) plus_idx = (unsigned int)__ffs(pb) - 1u;
+        }
+
+        // ---- 4. record structure and character classes
+        if (plus_idx != 0xffffffffu) {
+            // fast path: the phase is taken from the "+" line (role 2): local line i has role (i + r) & 3.
+            // tile_finalize_kernel checks the guess against the global line number and sends the tile to
+            // the REDO launch if it was wrong (only a 1-base read whose quality line is "+" can cause that).
+            // One thread per LINE, one line role per warp (role = warp & 3), so no lane of a warp diverges from
+            // its neighbours and the longest dependent chain of this step is one class check.
+            const int r = (int)((2u - plus_idx) & 3u);
+            const int role = warp & 3;                        // 0 header, 1 sequence, 2 plus, 3 quality
+            const int first = (role - r) & 3;                 // smallest local line index with that role
+            unsigned int viol = 0;
+            bool any_hit = false;
+            for (int i = first + 4 * ((warp >> 2) * 32 + lane); i <= n_tab; i += 4 * (kWarps / 4) * 32) {
+                const int a = i >= 1 ? (int)S.nlpos[i - 1] + 1 : 0;
+                const int e = i < n_tab ? (int)S.nlpos[i] : kTileBytes;
+                const bool whole = i >= 1 && i < n_tab;       // line starts and ends inside the tile
+                if (i < n_tab && tb[e] != '\n') viol |= FXG_V_BYTE_RANGE;   // a control byte posing as a line end
+                if (role == 0) {
+                    if (whole) {
+                        if (e - a < 1 || tb[a] != '@') viol |= FXG_V_HEADER_AT;
+                        else if (tb[e - 1] == ' ') viol |= FXG_V_HEADER_SPACE;
+                    }
+                } else if (role == 2) {
+                    if (whole && (e - a != 1 || tb[a] != '+')) viol |= FXG_V_PLUS_LINE;
+                } else {
+                    const bool seq = role == 1;
+                    if (class_bad(S, tile, a, e, seq)) viol |= seq ? FXG_V_SEQ_CLASS : FXG_V_QUAL_CLASS;
+                    if (whole) {
+                        if (seq) { if (e - a < 1) viol |= FXG_V_EMPTY_SEQ; }
+                        else if (i >= 3 && e - a != (int)S.nlpos[i - 2] - (int)S.nlpos[i - 3] - 1) viol |= FXG_V_QUAL_LEN;
+                    }
+                }
+                // exact mode: the warps of the target's role look their (whole) lines up; the line that straddles
+                // the tile's left edge is left to tile_finalize_kernel
+                if (EXACT && role == trole && whole && exact_line_tile(P, tb, a, e)) {
+                    atomicOr(&S.linehit[i >> 5], 1u << (i & 31));
+                    any_hit = true;
+                }
+            }
+            viol = __reduce_or_sync(0xffffffffu, viol);
+            if (EXACT && __any_sync(0xffffffffu, any_hit)) viol |= kTileHasHit;
+            if (lane == 0 && viol) atomicOr(&T.viol, viol);
+        } else {
+            // generic path (no "+" line in the tile, or REDO): one thread per line, flags OR-ed per
+            // (local line index mod 4); tile_finalize_kernel maps them to roles once the phase is known.
+            unsigned int f_own = 0, f_nxt = 0;
+            for (int i = tid; i < n_tab; i += kThreads) {
+                unsigned int own, nxt;
+                line_flags(S, tile, i, n_tab, own, nxt);
+                f_own |= own;
+                f_nxt |= nxt;
+            }
+            unsigned int v = f_own | (f_nxt << 8);
+            v = __reduce_or_sync(0x11111111u << (lane & 3), v);
+            if (lane < 4 && v) atomicOr(&T.cls[lane], v);
+            if (tid == kThreads - 1) {           // bytes after the last '\n': an unterminated line of index n_tab
+                unsigned int ms, mq;
+                range_any2(S, n_tab ? (S.nlpos[n_tab - 1] >> 4) + 1 : 0, kChunks, ms, mq);
+                const unsigned int f = (ms ? kFS : 0u) | (mq ? kFQ : 0u);
+                if (f) atomicOr(&T.cls[n_tab & 3], f);
+            }
+            if (EXACT && REDO) {
+                // the true phase is known by now (prefix kernels ran before this launch): look the whole lines of
+                // the target's role up; line 0 is left to tile_finalize_kernel like in the first launch
+                const int r = (int)((P.lbase[t] + P.bsum[t / kPrefixSpan]) & 3ull);
+                bool any_hit = false;
+                for (int i = 1 + tid; i < n_tab; i += kThreads) {
+                    if (((i + r) & 3) != trole) continue;
+                    if (exact_line_tile(P, tb, (int)S.nlpos[i - 1] + 1, (int)S.nlpos[i])) {
+                        atomicOr(&S.linehit[i >> 5], 1u << (i & 31));
+                        any_hit = true;
+                    }
+                }
+                if (any_hit) atomicOr(&T.viol, kTileHasHit);
+            }
+        }
+
+        // ---- 5. verify the matcher's candidates (phase-free; line hits)
+        if (LIT && !REDO) {
+            const unsigned int nc_all = T.n_cand;
+            if (nc_all <= (unsigned int)kCandCap) {
+                for (unsigned int q = tid; q < nc_all; q += kThreads)
+                    verify_candidate(S, T, tb, P, base, n_tab, S.m.lit.cand_off[q], S.m.lit.cand_mask[q]);
+            } else {
+                // queue overflow (pattern hits nearly everywhere): rescan the tile and verify in place
+                for (int c = tid; c < kChunks && (c << 4) < tile_len; c += kThreads) {
+                    const uint4 x = tile[c];
+                    if (LIT8) {
+                        const unsigned int r0 = MODE == kModeLit9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
+                        const unsigned int r1 = MODE == kModeLit9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
+                        if (S.m.lit.fp[r0 >> lit_shift] == r0) verify_candidate(S, T, tb, P, base, n_tab, c << 4, S.m.lit.masks[r0 >> lit_shift]);
+                        if (S.m.lit.fp[r1 >> lit_shift] == r1) verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + 8, S.m.lit.masks[r1 >> lit_shift]);
+                    } else {
+                        const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
+                        for (int u = 0; u < 16; u += lit_unit) {
+                            unsigned int word = wv[u >> 2];
+                            unsigned int val = lit_unit == 4 ? word : (lit_unit == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu)
+                                                                                     : ((word >> ((u & 3) * 8)) & 0xffu));
+                            for (int q = 0; q < lit_nkeys; ++q)
+                                if ((unsigned int)S.m.lit.keys[q] == val)
+                                    verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + u, S.m.lit.masks[q]);
+                        }
+                    }
+                }
+            }
+        }
+        if (KMER && !REDO) {
+            // every warp resolves the filter hits of its own segment (queue written by this warp in step 1)
+            __syncwarp();
+            for (unsigned int q = lane; q < kqn; q += 32) {
+                const unsigned int e = my_kq[q];
+                const int ce = warp * kWarpChunks + (int)(e >> 8) - (SB < 16 ? 1 : 0);   // chunk the windows start in (-1: lead-in)
+                unsigned int bits = e & 0xffu;
+                const unsigned int p0 = pack16(tile[ce]);
+                const unsigned int p1 = SB < 16 ? pack16(tile[ce + 1]) : 0u;
+                while (bits) {
+                    const int bi = 31 - __clz(bits);
+                    bits &= ~(1u << bi);
+                    const int s = (NPROBE - 1 - bi) * SB;             // first probe of a chunk ends up in the highest bit
+                    const unsigned int key = (s ? __funnelshift_r(p0, p1, 2 * s) : p0) & kmask;
+                    kmer_resolve(S, T, tb, P, base, n_tab, (ce << 4) + s, key);
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- 6. publish the tile: count, violations / line-class flags, '\n' table, line hits.  No barrier
+        //         after it: the next writers of anything read here (the bulk copy into this buffer, the table,
+        //         the hit words, this copy of the scalars) all come after the first barrier of the next tile.
+        {
+            uint4 *dst = reinterpret_cast<uint4 *>(P.tile_nl + t * (unsigned long long)kMaxTileLines);
+            const uint4 *src = reinterpret_cast<const uint4 *>(S.nlpos);
+            for (int q = tid; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
+            if (HITS) {
+                unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
+                const int nw = (n_tab >> 5) + 1;               // local line indices 0..n_tab
+                for (int w = tid; w < nw; w += kThreads) {
+                    const unsigned int v = S.linehit[w];
+                    hd[w] = v;
+                    if (v) S.linehit[w] = 0;
+                }
+            }
+            if (tid == 0) {
+                // a REDO launch that re-checks structure only keeps the hit words of the first launch, and their flag
+                const unsigned int kept = (REDO && !EXACT) ? (P.info[t].viol & kTileHasHit) : 0u;
+                const TileInfo ti = {total, kept | T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),
+                                     {(unsigned short)T.cls[0], (unsigned short)T.cls[1], (unsigned short)T.cls[2], (unsigned short)T.cls[3]}};
+                P.info[t] = ti;
+            }
+        }
+    }
+#undef FXG_TILE_OF
+#undef FXG_ISSUE_TILE
+}
+
+// ---------------------------------------------------------------- launcher (one per instantiation)
+// Persistent grid: one wave of CTAs (SMs x resident CTAs for this kernel and its shared memory).  The per-device
+// attribute / occupancy cache is guarded: contexts on different host threads may launch concurrently.
+cudaError_t scan_launch_config(const void *func, int threads, size_t smem, int dev, int *grid_cap);
+
+template <class G, int MODE, bool REDO>
+cudaError_t launch_scan_tiles(const ScanParams &P, size_t extra_smem, cudaStream_t stream, int dev, unsigned long long max_grid)
+{
+    const size_t smem = sizeof(ScanSmem<G>) + extra_smem;
+    int cap = 0;
+    cudaError_t e = scan_launch_config((const void *)scan_tiles_kernel<G, MODE, REDO>, G::kThreads, smem, dev, &cap);
+    if (e != cudaSuccess) return e;
+    unsigned long long grid = P.ntiles < (unsigned long long)cap ? P.ntiles : (unsigned long long)cap;
+    if (max_grid && grid > max_grid) grid = max_grid;
+    scan_tiles_kernel<G, MODE, REDO><<<(unsigned int)grid, G::kThreads, smem, stream>>>(P);
+    return cudaGetLastError();
+}
+
+}  // namespace fxg

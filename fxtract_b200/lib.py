@@ -40,7 +40,7 @@ class SynthSpec(C.Structure):
 EXPORTS = ["fxg_device_count", "fxg_create", "fxg_destroy", "fxg_last_error", "fxg_set_patterns",
            "fxg_acquire_buffer", "fxg_submit_raw", "fxg_submit_raw_from", "fxg_submit_fields", "fxg_collect",
            "fxg_count", "fxg_find_record_cut", "fxg_scan_device_async", "fxg_scan_device_finish",
-           "fxg_last_launch_count", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
+           "fxg_last_launch_count", "fxg_last_d2h_bytes", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
            "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free", "fxg_copy_to_host"]
 
 _lib = None
@@ -71,6 +71,8 @@ def load_library():
     lib.fxg_scan_device_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.fxg_scan_device_finish.argtypes = [C.c_void_p, C.POINTER(Result)]
     lib.fxg_last_launch_count.argtypes = [C.c_void_p]
+    lib.fxg_last_d2h_bytes.argtypes = [C.c_void_p]
+    lib.fxg_last_d2h_bytes.restype = C.c_uint64
     lib.fxg_set_profiling.argtypes = [C.c_void_p, C.c_int]
     lib.fxg_last_kernel_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.fxg_synth_bytes.argtypes = [C.POINTER(SynthSpec)]
@@ -201,6 +203,9 @@ class Context:
 
     def last_launch_count(self):
         return self.lib.fxg_last_launch_count(self.h)
+
+    def last_d2h_bytes(self):
+        return self.lib.fxg_last_d2h_bytes(self.h)
 
     def set_profiling(self, on=True):
         self._check(self.lib.fxg_set_profiling(self.h, int(on)))

@@ -128,6 +128,8 @@ int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes);
 int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res);
 /* Number of kernel launches the last *_async / submit_* call enqueued. */
 int fxg_last_launch_count(const fxg_ctx *ctx);
+/* Bytes the last collected / finished raw batch brought back to the host (counters + selected runs). */
+uint64_t fxg_last_d2h_bytes(const fxg_ctx *ctx);
 /* Measurement aid: when enabled, every raw-path enqueue brackets its kernels with
  * CUDA events on the context's stream.  After the batch has been collected /
  * finished, fxg_last_kernel_ms() returns the device time of the dominant kernel
