@@ -11,8 +11,14 @@ CUOBJ := $(patsubst $(CSRC)/%.cu,$(BLD)/%.o,$(CU))
 CUHDR := $(wildcard $(CSRC)/*.cuh) $(ROOT)include/fxgpu.h
 HOSTSRC := $(wildcard $(HOST)/*.cpp)
 
-.PHONY: all lib cli oracle clean fxtract_test ptxas
-all: lib cli
+.PHONY: all lib cli tools oracle clean fxtract_test ptxas
+all: lib cli tools
+
+# stand-alone generator of the synthetic workload (no CUDA): bench.py's reference arm and the verification legs
+tools: $(BLD)/fxsynth
+$(BLD)/fxsynth: $(ROOT)fxtract_b200/tools/fxsynth.cpp $(CSRC)/fxg_synth_core.h
+	@mkdir -p $(BLD)
+	$(CXX) -O2 -std=c++17 -Wall -pthread -o $@ $<
 
 lib: $(BLD)/libfxgpu.so
 $(BLD)/%.o: $(CSRC)/%.cu $(CUHDR)

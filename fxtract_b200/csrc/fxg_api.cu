@@ -940,13 +940,22 @@ extern "C" int fxg_synth_device(fxg_ctx *ctx, const fxg_synth_spec *s, void *d_o
 extern "C" int fxg_host_alloc(void **p, size_t n)
 {
     if (!p) return FXG_ERR_ARG;
-    cudaError_t e = cudaHostAlloc(p, n, cudaHostAllocDefault);
+    cudaError_t e = cudaHostAlloc(p, n, cudaHostAllocPortable);      // pinned for every device of the process
     if (e != cudaSuccess) { *p = nullptr; return set_cuda_error(nullptr, e, "cudaHostAlloc"); }
     return FXG_OK;
 }
 extern "C" int fxg_host_free(void *p)
 {
     if (p) cudaFreeHost(p);
+    return FXG_OK;
+}
+
+extern "C" int fxg_copy_to_device(fxg_ctx *ctx, void *d_dst, const void *host_src, size_t n)
+{
+    if (!ctx || !d_dst || !host_src) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    FXG_CUDA_OK(cudaMemcpyAsync(d_dst, host_src, n, cudaMemcpyHostToDevice, ctx->stream));
+    FXG_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     return FXG_OK;
 }
 

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <deque>
 #include <map>
+#include <memory>
 #include <string>
 #include <vector>
 #include <zlib.h>
@@ -142,6 +143,7 @@ public:
     void acquire(void **pinned, size_t *cap);                   // next device in turn
     void submit_fields(size_t nbytes, const uint32_t *off, uint32_t n);
     void submit_raw(size_t nbytes, bool is_last);
+    void submit_raw_from(const void *host, size_t nbytes, bool is_last);   // caller-owned pinned memory, next device in turn
     void collect(fxg_result *res);                              // oldest submitted batch
     void grow(size_t batch_bytes);                              // re-create the contexts with larger buffers (idle only)
 private:
@@ -165,6 +167,7 @@ struct Job {
     std::string pattern;            // single command-line pattern (main.cpp:657)
     long matched_records = 0;       // main.cpp:80 (cumulative over inputs)
     bool stats = false;
+    std::unique_ptr<DevicePool> pool;   // one set of device contexts (pattern tables, staging) for all inputs
 };
 // One input (pair of) file(s): picks the strategy (main.cpp:707-757) and runs it.  Returns the
 // process exit status contribution (0 ok).

@@ -82,6 +82,14 @@ void DevicePool::submit_raw(size_t nbytes, bool is_last)
     lent_ = -1;
 }
 
+void DevicePool::submit_raw_from(const void *host, size_t nbytes, bool is_last)
+{
+    fxg_ctx *c = ctx_[turn_];
+    if (fxg_submit_raw_from(c, host, nbytes, is_last ? 1 : 0) != FXG_OK) fail(c, "fxg_submit_raw_from");
+    order_.push_back(turn_);
+    turn_ = (turn_ + 1) % (int)ctx_.size();
+}
+
 void DevicePool::collect(fxg_result *res)
 {
     if (order_.empty()) { fprintf(stderr, "fxtract: internal error: collect() with nothing in flight\n"); exit(1); }

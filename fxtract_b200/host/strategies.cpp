@@ -11,8 +11,13 @@
 //                  printing and routing on the host exactly as the reference does.
 // The POSIX-regex strategies (main.cpp:462-514) are outside the graft and stay on the CPU.
 #include "fxhost.h"
+#include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <cstdlib>
+#include <mutex>
+#include <set>
+#include <thread>
 #include <cstring>
 #include <fcntl.h>
 #include <memory>
@@ -166,7 +171,92 @@ bool run_fields(Job &job, Strategy st, PairSource &src, bool paired, DevicePool 
 }
 
 // ------------------------------------------------------------------ raw path
-struct RawPending { const uint8_t *host; uint64_t file_off; size_t nbytes; };
+// Host ingest of the raw path (hard part 5): the file is read in fixed windows by a team of
+// reader threads (pread of 8 MiB slices) straight into pinned buffers, several windows ahead of the GPU.  A window
+// becomes a batch once the unconsumed tail of its predecessor (a partial record, copied into the pad in front of
+// the window) is known and the last record boundary inside it is found; batches go to the devices round-robin and
+// come back in order, and the selected byte runs are written from the pinned copy.
+class RawIngest {
+public:
+    static constexpr size_t kPad = 1u << 20;        // room in front of a window for the carried partial record
+    static constexpr size_t kSlice = 8u << 20;
+    RawIngest(int fd, uint64_t file_size, size_t window, int nbuf, int nthreads)
+        : fd_(fd), size_(file_size), window_(window), nbuf_(nbuf)
+    {
+        nwin_ = (size_ + window_ - 1) / window_;
+        bufs_.resize(nbuf_);
+        for (Buf &b : bufs_) {
+            void *p = nullptr;
+            if (fxg_host_alloc(&p, kPad + window_ + 64) != FXG_OK) { fprintf(stderr, "fxtract: cannot allocate pinned staging memory: %s\n", fxg_last_error(nullptr)); exit(1); }
+            b.mem = (uint8_t *)p;
+        }
+        done_.assign(nwin_, 0);
+        for (int t = 0; t < nthreads; ++t) threads_.emplace_back([this] { work(); });
+    }
+    ~RawIngest()
+    {
+        { std::lock_guard<std::mutex> l(mu_); stop_ = true; }
+        cv_.notify_all();
+        for (std::thread &t : threads_) t.join();
+        for (Buf &b : bufs_) fxg_host_free(b.mem);
+    }
+    uint64_t windows() const { return nwin_; }
+    // blocks until window k is in memory; returns its first byte (kPad bytes of pad lie in front of it) and length
+    uint8_t *wait_window(uint64_t k, size_t *len)
+    {
+        std::unique_lock<std::mutex> l(mu_);
+        const size_t want = slices_in(k);
+        cv_.wait(l, [&] { return done_[k] == want || failed_; });
+        if (failed_) { perror("fxtract: read"); exit(1); }
+        *len = win_len(k);
+        return bufs_[k % nbuf_].mem + kPad;
+    }
+    // window k's buffer may be overwritten (by window k + nbuf)
+    void release_window(uint64_t k)
+    {
+        { std::lock_guard<std::mutex> l(mu_); released_.insert(k); while (released_.count(low_)) { released_.erase(low_); ++low_; } }
+        cv_.notify_all();
+    }
+private:
+    struct Buf { uint8_t *mem = nullptr; };
+    size_t win_len(uint64_t k) const { const uint64_t o = k * window_; return (size_t)std::min<uint64_t>(window_, size_ - o); }
+    size_t slices_in(uint64_t k) const { return (win_len(k) + kSlice - 1) / kSlice; }
+    void work()
+    {
+        for (;;) {
+            uint64_t k; size_t s;
+            {
+                std::unique_lock<std::mutex> l(mu_);
+                cv_.wait(l, [&] { return stop_ || failed_ || (next_win_ < nwin_ && next_win_ < low_ + (uint64_t)nbuf_); });
+                if (stop_ || failed_) return;
+                k = next_win_; s = next_slice_;
+                if (++next_slice_ >= slices_in(k)) { next_slice_ = 0; ++next_win_; }
+            }
+            uint8_t *dst = bufs_[k % nbuf_].mem + kPad + s * kSlice;
+            const uint64_t off = k * window_ + (uint64_t)s * kSlice;
+            size_t want = std::min(kSlice, win_len(k) - s * kSlice), have = 0;
+            bool bad = false;
+            while (have < want) {
+                ssize_t got = pread(fd_, dst + have, want - have, (off_t)(off + have));
+                if (got <= 0) { bad = true; break; }          // the file shrank under us, or an I/O error
+                have += (size_t)got;
+            }
+            { std::lock_guard<std::mutex> l(mu_); if (bad) failed_ = true; ++done_[k]; }
+            cv_.notify_all();
+        }
+    }
+    int fd_; uint64_t size_; size_t window_; int nbuf_;
+    uint64_t nwin_ = 0;
+    std::vector<Buf> bufs_;
+    std::vector<size_t> done_;
+    std::vector<std::thread> threads_;
+    std::mutex mu_; std::condition_variable cv_;
+    uint64_t next_win_ = 0, low_ = 0; size_t next_slice_ = 0;     // low_: every window below it has been released
+    std::set<uint64_t> released_;
+    bool stop_ = false, failed_ = false;
+};
+
+struct RawPending { const uint8_t *host; uint64_t file_off; size_t nbytes; uint64_t window; };
 
 bool raw_path_allowed(const Job &job, const char *file2)
 {
@@ -175,6 +265,14 @@ bool raw_path_allowed(const Job &job, const char *file2)
     const CliOptions &o = job.opt;
     if (file2 || o.I || o.l) return false;           // mates and -l need per-pair rules: fields path
     return job.router.all_stdout();                  // per-pattern output files need first-hit ids: fields path
+}
+
+int reader_threads_from_env()
+{
+    const char *e = getenv("FXTRACT_READERS");
+    int n = e ? atoi(e) : 0;
+    if (n <= 0) { n = (int)std::thread::hardware_concurrency(); if (n > 16) n = 16; }
+    return n < 1 ? 1 : n;
 }
 
 // Returns: -1 = raw path not applicable (nothing consumed), otherwise the byte offset from which
@@ -186,53 +284,58 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
     unsigned char magic[2] = {0, 0};
     if (pread(fd, magic, 2, 0) < 1 || magic[0] != '@') return -1;      // FASTA, gzip (1f 8b), empty, ...: general reader
     const CliOptions &o = job.opt;
+    const uint64_t file_size = (uint64_t)sb.st_size;
+    if (pool.batch_bytes() <= 2 * RawIngest::kPad) return -1;
+    const size_t window = pool.batch_bytes() - RawIngest::kPad;       // a batch = carried tail + one window <= batch_bytes
+    const int nbuf = (int)pool.capacity() + 2;                         // in flight on the devices + being filled / cut
+    RawIngest ingest(fd, file_size, window, nbuf, reader_threads_from_env());
     std::deque<RawPending> pending;
-    uint64_t file_pos = 0;            // next byte to read from the file
-    const uint8_t *carry = nullptr;   // unconsumed tail of the previous batch (a partial record)
-    size_t carry_n = 0;
-    uint64_t batch_start = 0;         // file offset of the first byte of the batch being filled
-    bool eof = false;
     int64_t reroute_at = -1;
     auto finish_oldest = [&]() {
         fxg_result r;
         pool.collect(&r);
         RawPending p = pending.front();
         pending.pop_front();
-        if (reroute_at >= 0) return;                                   // results after a rejected batch are discarded
-        if (!r.canonical_ok) { reroute_at = (int64_t)p.file_off; stats.rerouted++; return; }
-        if (o.c) job.matched_records += (long)r.n_selected;
-        else for (uint64_t k = 0; k < r.n_runs; ++k) fwrite(p.host + r.runs[k].off, 1, r.runs[k].len, stdout);
-        stats.records += r.n_records;
-    };
-    while (!eof && reroute_at < 0) {
-        if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute_at >= 0) break; }
-        void *pin; size_t cap;
-        pool.acquire(&pin, &cap);
-        uint8_t *dst = (uint8_t *)pin;
-        size_t have = 0;
-        if (carry_n) { memmove(dst, carry, carry_n); have = carry_n; }
-        batch_start = file_pos - carry_n;
-        while (have < cap) {
-            ssize_t got = pread(fd, dst + have, cap - have, (off_t)file_pos);
-            if (got < 0) { perror("fxtract: read"); exit(1); }
-            if (got == 0) { eof = true; break; }
-            have += (size_t)got; file_pos += (uint64_t)got;
-        }
-        size_t n = have;
-        if (!eof) {
-            n = fxg_find_record_cut(dst, have);
-            if (n == 0) {                           // no record boundary in a whole buffer: not the fast path's business
-                pool.submit_raw(0, false);          // hands the lent buffer back
-                pending.push_back(RawPending{dst, batch_start, 0});
-                while (!pending.empty()) finish_oldest();
-                if (reroute_at < 0) reroute_at = (int64_t)batch_start;
-                break;
+        if (reroute_at < 0) {
+            if (!r.canonical_ok) { reroute_at = (int64_t)p.file_off; stats.rerouted++; }
+            else {
+                if (o.c) job.matched_records += (long)r.n_selected;
+                else for (uint64_t k = 0; k < r.n_runs; ++k) fwrite(p.host + r.runs[k].off, 1, r.runs[k].len, stdout);
+                stats.records += r.n_records;
             }
+        }                                                              // results after a rejected batch are discarded
+        ingest.release_window(p.window);
+    };
+    const uint8_t *carry = nullptr;      // unconsumed tail of the previous window's batch (a partial record)
+    size_t carry_n = 0;
+    uint64_t consumed = 0;               // file offset up to which batches have been cut
+    for (uint64_t k = 0; k < ingest.windows() && reroute_at < 0; ++k) {
+        if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute_at >= 0) break; }
+        size_t wlen;
+        uint8_t *w = ingest.wait_window(k, &wlen);
+        if (carry_n > RawIngest::kPad) {                // a record longer than the pad: not the fast path's business
+            while (!pending.empty()) finish_oldest();
+            if (reroute_at < 0) reroute_at = (int64_t)consumed;
+            break;
         }
-        carry = dst + n; carry_n = have - n;
-        pool.submit_raw(n, eof);
-        pending.push_back(RawPending{dst, batch_start, n});
+        uint8_t *batch = w - carry_n;
+        if (carry_n) memcpy(batch, carry, carry_n);
+        const size_t have = carry_n + wlen;
+        const bool last = k + 1 == ingest.windows();
+        size_t n = have;
+        if (!last) n = fxg_find_record_cut(batch, have);
+        if (!last && n == 0) {                          // no record boundary in a whole window
+            while (!pending.empty()) finish_oldest();
+            if (reroute_at < 0) reroute_at = (int64_t)consumed;
+            break;
+        }
+        carry = batch + n; carry_n = have - n;
+        pool.submit_raw_from(batch, n, last);
+        pending.push_back(RawPending{batch, consumed, n, k});
+        consumed += n;
         stats.raw_bytes += n; stats.raw_batches++;
+        // the carried tail lives in window k's buffer: it is copied into window k + 1's pad before window k can be
+        // released, which happens only when batch k has been collected -- at least one loop iteration later
     }
     while (!pending.empty()) finish_oldest();
     if (reroute_at >= 0) {
@@ -243,7 +346,7 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
         }
         return reroute_at;
     }
-    return (int64_t)file_pos;
+    return (int64_t)file_size;
 }
 
 // ------------------------------------------------------------------ POSIX regex (outside the graft; CPU, main.cpp:462-514)
@@ -333,7 +436,8 @@ int run_input(Job &job, const char *file1, const char *file2)
     pc.invert = o.v; pc.count_only = o.c; pc.want_pattern_id = st != S_LITERAL;
     pc.batch_bytes = batch_bytes_from_env();
     pc.devices = devices_from_env();
-    DevicePool pool(pc, pats);
+    if (!job.pool) job.pool.reset(new DevicePool(pc, pats));     // strategy, flags and patterns are the same for every input
+    DevicePool &pool = *job.pool;
 
     Stats stats;
     const auto t0 = std::chrono::steady_clock::now();

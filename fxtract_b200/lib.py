@@ -41,7 +41,7 @@ EXPORTS = ["fxg_device_count", "fxg_create", "fxg_destroy", "fxg_last_error", "f
            "fxg_acquire_buffer", "fxg_submit_raw", "fxg_submit_raw_from", "fxg_submit_fields", "fxg_collect",
            "fxg_count", "fxg_find_record_cut", "fxg_scan_device_async", "fxg_scan_device_finish",
            "fxg_last_launch_count", "fxg_last_d2h_bytes", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
-           "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free", "fxg_copy_to_host"]
+           "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free", "fxg_copy_to_host", "fxg_copy_to_device"]
 
 _lib = None
 
@@ -86,6 +86,7 @@ def load_library():
     lib.fxg_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
     lib.fxg_host_free.argtypes = [C.c_void_p]
     lib.fxg_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    lib.fxg_copy_to_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
     lib.fxg_device_count.argtypes = [C.POINTER(C.c_int)]
     _lib = lib
     return lib
@@ -217,6 +218,9 @@ class Context:
 
     def copy_to_host(self, host_ptr, dptr, n):
         self._check(self.lib.fxg_copy_to_host(self.h, C.c_void_p(host_ptr), C.c_void_p(dptr), n))
+
+    def copy_to_device(self, dptr, host_ptr, n):
+        self._check(self.lib.fxg_copy_to_device(self.h, C.c_void_p(dptr), C.c_void_p(host_ptr), n))
 
     def synth_device(self, spec, dptr):
         self._check(self.lib.fxg_synth_device(self.h, C.byref(spec), C.c_void_p(dptr)))

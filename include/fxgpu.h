@@ -123,7 +123,9 @@ size_t fxg_find_record_cut(const uint8_t *buf, size_t n);
 
 /* ---- device-resident path (inputs already in HBM) ------------------------ */
 /* Enqueues the raw scan over d_buf[0..nbytes) (whole records, ends in '\n') on the
- * context's stream; fxg_scan_device_finish() synchronises and fills res. */
+ * context's stream; fxg_scan_device_finish() synchronises and fills res.
+ * d_buf must be 16-byte aligned (the tiles are fetched with bulk copies; FXG_ERR_CUDA / misaligned address
+ * otherwise) and readable for 16 bytes past nbytes (edge look-ups read whole aligned words). */
 int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes);
 int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res);
 /* Number of kernel launches the last *_async / submit_* call enqueued. */
@@ -164,6 +166,9 @@ int fxg_host_free(void *p);
 /* synchronous device -> host copy on the context's stream (bench / tests: materialise a
  * device-generated synthetic shard in host memory) */
 int fxg_copy_to_host(fxg_ctx *ctx, void *host_dst, const void *d_src, size_t n);
+/* synchronous host -> device copy on the context's stream (bench: the pinned-H2D probe that gives the end-to-end
+ * figure its PCIe / host-ingest bound) */
+int fxg_copy_to_device(fxg_ctx *ctx, void *d_dst, const void *host_src, size_t n);
 
 #ifdef __cplusplus
 }

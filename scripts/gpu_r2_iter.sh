@@ -3,9 +3,16 @@
 # usage: RECORDS=20000000 WORKLOADS="c2 c3 c4 c5v c5c" TESTS="tests" bash scripts/gpu_r2_iter.sh
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv,noheader > gpurun_out/gpu.txt 2>&1
-if [ -n "${TESTS:-tests}" ]; then
-  timeout 1500 python -m pytest ${TESTS:-tests} -m gpu -q -x --timeout 600 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-  tail -25 gpurun_out/pytest_gpu.log
+if [ "${TESTS-all}" != "" ]; then
+  : > gpurun_out/pytest_gpu.log
+  for f in ${TESTS:-tests/test_gpu_fused.py tests/test_gpu_raw.py tests/test_gpu_fields.py tests/test_cli_golden.py}; do
+    # one process per file: a faulting kernel poisons only its own file
+    timeout 1200 python -m pytest $f -m gpu -q --timeout 600 > gpurun_out/pytest_$(basename $f .py).log 2>&1
+    echo "$f rc=$?" >> gpurun_out/pytest_gpu.log
+    tail -4 gpurun_out/pytest_$(basename $f .py).log >> gpurun_out/pytest_gpu.log
+    grep -E "^(FAILED|ERROR)" gpurun_out/pytest_$(basename $f .py).log | cut -c1-200 >> gpurun_out/pytest_gpu.log
+  done
+  cat gpurun_out/pytest_gpu.log
 fi
 : > gpurun_out/workloads.txt
 for w in ${WORKLOADS:-c2 c3 c4 c5v c5c}; do

@@ -86,7 +86,18 @@ int fxg_submit_raw(fxg_ctx *c, size_t nbytes, int is_last)
     return FXG_OK;
 }
 
-int fxg_submit_raw_from(fxg_ctx *c, const void *h, size_t n, int l) { (void)c; (void)h; (void)n; (void)l; g_err = "shim: unsupported"; return FXG_ERR_UNSUPPORTED; }
+int fxg_submit_raw_from(fxg_ctx *c, const void *h, size_t n, int l)
+{
+    (void)h; (void)l;
+    for (int i = 0; i < 2; ++i) if (c->state[i] == 0) {
+        c->raw[i] = n ? 1 : 2; c->state[i] = 2; c->fifo[c->nfifo++] = i;
+        return FXG_OK;
+    }
+    g_err = "both slots are in flight";
+    return FXG_ERR_STATE;
+}
+int fxg_host_alloc(void **p, size_t n) { *p = malloc(n); return *p ? FXG_OK : FXG_ERR_NOMEM; }
+int fxg_host_free(void *p) { free(p); return FXG_OK; }
 
 static const uint8_t *find_bytes(const uint8_t *h, size_t hn, const uint8_t *p, size_t pn)
 {
