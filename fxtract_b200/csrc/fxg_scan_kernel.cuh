@@ -41,9 +41,10 @@ struct TileState {
 };
 
 template <class G> struct __align__(128) ScanSmem {
-    // staged tile bytes, double buffered (bulk-copy destinations).  Chunk 0 of each buffer holds the 16 bytes in
-    // front of the tile (k-mer windows that start there end in this tile), chunks 1.. the tile itself.
-    uint4 tile[2][G::kChunks + 1];
+    // staged tile bytes, double buffered (bulk-copy destinations).  One more chunk behind each tile: the first 16
+    // bytes of the next tile, where the k-mer windows that start in the tile's last chunk end.  The pad keeps the
+    // second buffer 128-byte aligned.
+    uint4 tile[2][G::kChunks + 8];
     unsigned short nlpos[G::kMaxTileLines + 16];      // tile-relative '\n' positions, in order (+ slack, see step 3)
     unsigned short wl[G::kWarps][G::kWarpChunks];     // per warp: its chunks that contain a byte < 0x21 ('\n' candidates)
     unsigned short wm[G::kWarps][G::kWarpChunks];     // per entry of wl: 16-bit mask of the bytes < 0x20 of that chunk
@@ -331,7 +332,7 @@ __device__ __noinline__ void filter_small_units(ScanSmem<G> &S, TileState &T, un
 }
 
 // ---------------------------------------------------------------- k-mer mode: one filter hit -> table -> bytes
-// `win_rel` = tile-relative offset of the first byte of the window (>= -16), `key` its packed bases.  Every
+// `win_rel` = tile-relative offset of the first byte of the window, `key` its packed bases.  Every
 // pattern that holds this window at one of its first S offsets is compared byte by byte with the text; the first
 // one that matches marks the local line of the occurrence (all of them lie on the same line).
 template <class G>
@@ -452,18 +453,16 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     const unsigned long long n_work = REDO ? (unsigned long long)*P.redo_count : P.ntiles;
     if ((unsigned long long)blockIdx.x >= n_work) return;
 #define FXG_TILE_OF(k) (REDO ? (unsigned long long)P.redo_list[(k)] : (unsigned long long)(k))
-    // issue the bulk copy of tile `tt` into buffer `bf` (thread 0): with the 16 bytes in front of it in k-mer mode
+    // issue the bulk copy of tile `tt` into buffer `bf` (thread 0); in k-mer mode with the 16 bytes that follow it
+    constexpr unsigned int kFetch = (unsigned int)kTileBytes + ((KMER && SB < 16) ? 16u : 0u);
 #define FXG_ISSUE_TILE(tt, bf)                                                                                          \
     do {                                                                                                                \
         const unsigned long long b__ = (tt) * (unsigned long long)kTileBytes;                                           \
         const unsigned long long rem__ = P.nbytes - b__;                                                                \
-        const unsigned int bulk__ = (unsigned int)(rem__ < (unsigned long long)kTileBytes ? rem__ : (unsigned long long)kTileBytes) & ~15u; \
-        if (KMER && SB < 16 && (tt) > 0) {                                                                               \
-            mbar_expect_tx(&S.mbar[bf], bulk__ + 16u);                                                                  \
-            bulk_g2s(&S.tile[bf][0], P.buf + b__ - 16, bulk__ + 16u, &S.mbar[bf]);                                      \
-        } else if (bulk__) {                                                                                            \
+        const unsigned int bulk__ = (unsigned int)(rem__ < (unsigned long long)kFetch ? rem__ : (unsigned long long)kFetch) & ~15u; \
+        if (bulk__) {                                                                                                   \
             mbar_expect_tx(&S.mbar[bf], bulk__);                                                                        \
-            bulk_g2s(&S.tile[bf][1], P.buf + b__, bulk__, &S.mbar[bf]);                                                 \
+            bulk_g2s(&S.tile[bf][0], P.buf + b__, bulk__, &S.mbar[bf]);                                                 \
         }                                                                                                               \
     } while (0)
 
@@ -494,8 +493,6 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         const uint4 *src = reinterpret_cast<const uint4 *>(P.kmer.filter);
         uint4 *dst = reinterpret_cast<uint4 *>(filt);
         for (int w = tid; w < nw / 4; w += kThreads) dst[w] = __ldg(src + w);
-        // the tile at offset 0 has nothing in front of it: a line feed (no base) in every byte of the lead-in chunk
-        if (tid < 2) S.tile[tid][0] = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
     }
     const unsigned int one = P.one;
     const unsigned int lt_mask = (1u << lane) - 1u;
@@ -509,7 +506,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     for (unsigned long long k = blockIdx.x; k < n_work; k += gridDim.x, ++it) {
         const unsigned long long t = FXG_TILE_OF(k);
         const int cur = (int)(it & 1u);
-        const uint4 *tile = &S.tile[cur][1];
+        const uint4 *tile = S.tile[cur];
         TileState &T = S.st[cur];
         const unsigned char *tb = reinterpret_cast<const unsigned char *>(tile);
         const unsigned long long base = t * (unsigned long long)kTileBytes;
@@ -535,11 +532,11 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                     unsigned int by = P.buf[base + b + q];
                     w[q >> 2] = (w[q >> 2] & ~(0xffu << ((q & 3) * 8))) | (by << ((q & 3) * 8));
                 }
-                S.tile[cur][1 + (b >> 4)] = make_uint4(w[0], w[1], w[2], w[3]);
+                S.tile[cur][b >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
             }
             __syncthreads();
         }
-        if (bulk || (KMER && SB < 16 && t > 0)) mbar_wait(&S.mbar[cur], (it >> 1) & 1u);
+        if (bulk) mbar_wait(&S.mbar[cur], (it >> 1) & 1u);
 
         // ---- 1. main pass: 16 bytes per lane per step, SWAR only.  Per chunk: byte range, "has a
         //         byte < 0x41" / "< 0x21" ballot rows, list of the chunks with a byte < 0x21 (the only
@@ -547,14 +544,17 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         unsigned int wcount = 0, kqn = 0;
         {
             unsigned int hi_acc = 0;
-            // k-mer mode: packed word of the chunk in front of the lane's chunk (lane 0: carried from lane 31 of
-            // the previous step; first step: the chunk in front of the warp's segment)
-            unsigned int carry = 0;
-            if (KMER && !REDO && SB < 16) carry = pack16(tile[warp * kWarpChunks - 1]);
+            // k-mer mode: the lane's chunk and its packed word are fetched one step ahead, because the windows that
+            // start in lane 31's chunk end in lane 0's chunk of the NEXT step (last step: the chunk behind the warp's
+            // segment -- the next warp's first chunk, or the 16 bytes staged behind the tile)
+            uint4 xn = make_uint4(0u, 0u, 0u, 0u);
+            unsigned int pkn = 0;
+            if (KMER && !REDO && SB < 16) { xn = tile[warp * kWarpChunks + lane]; pkn = pack16(xn); }
 #pragma unroll
             for (int j = 0; j < kChunksPerThread; ++j) {
                 const int c = warp * kWarpChunks + j * 32 + lane;
-                const uint4 x = tile[c];
+                uint4 x;
+                if (KMER && !REDO && SB < 16) x = xn; else x = tile[c];
                 hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);     // bytes >= 0x7f anywhere
                 hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
                 hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
@@ -580,20 +580,22 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                 } else if (MODE == kModeLitSmall && !REDO) {
                     if ((c << 4) < tile_len) filter_small_units(S, T, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
                 } else if (KMER && !REDO) {
-                    // windows of k bases that start at byte 0, SB, 2 SB, ... of the chunk IN FRONT of the lane's own
-                    // (SB == 16: of the lane's own chunk -- the window never leaves it)
-                    const unsigned int pk = pack16(x);
+                    // windows of k bases that start at byte 0, SB, 2 SB, ... of the lane's chunk; they end in it or in
+                    // the next chunk, whose packed word comes from the next lane
                     unsigned int acc = 0;
                     if (SB == 16) {
-                        const unsigned int h = (pk & kmask) * kKmerHashMul;
+                        const unsigned int h = (pack16(x) & kmask) * kKmerHashMul;
                         acc = __funnelshift_l(0u, filt[h >> fshift], h) >> 31;
                     } else {
-                        unsigned int pp = __shfl_up_sync(0xffffffffu, pk, 1);
-                        if (lane == 0) pp = carry;
-                        carry = __shfl_sync(0xffffffffu, pk, 31);
+                        const unsigned int pk = pkn;
+                        xn = tile[c + 32];                            // lane's chunk of the next step (see above)
+                        pkn = pack16(xn);
+                        unsigned int pq = __shfl_down_sync(0xffffffffu, pk, 1);
+                        const unsigned int first_next = __shfl_sync(0xffffffffu, pkn, 0);
+                        if (lane == 31) pq = first_next;
 #pragma unroll
                         for (int s = 0; s < 16; s += SB) {
-                            const unsigned int key = (s ? __funnelshift_r(pp, pk, 2 * s) : pp) & kmask;
+                            const unsigned int key = (s ? __funnelshift_r(pk, pq, 2 * s) : pk) & kmask;
                             const unsigned int h = key * kKmerHashMul;
                             // filter bit 31 - (h & 31) of word h >> fshift, moved to the top and shifted into acc
                             acc = __funnelshift_l(__funnelshift_l(0u, filt[h >> fshift], h), acc, 1);
@@ -796,7 +798,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
             __syncwarp();
             for (unsigned int q = lane; q < kqn; q += 32) {
                 const unsigned int e = my_kq[q];
-                const int ce = warp * kWarpChunks + (int)(e >> 8) - (SB < 16 ? 1 : 0);   // chunk the windows start in (-1: lead-in)
+                const int ce = warp * kWarpChunks + (int)(e >> 8);    // chunk the windows start in
                 unsigned int bits = e & 0xffu;
                 const unsigned int p0 = pack16(tile[ce]);
                 const unsigned int p1 = SB < 16 ? pack16(tile[ce + 1]) : 0u;
@@ -805,7 +807,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                     bits &= ~(1u << bi);
                     const int s = (NPROBE - 1 - bi) * SB;             // first probe of a chunk ends up in the highest bit
                     const unsigned int key = (s ? __funnelshift_r(p0, p1, 2 * s) : p0) & kmask;
-                    kmer_resolve(S, T, tb, P, base, n_tab, (ce << 4) + s, key);
+                    kmer_resolve(S, T, tb, P, base, n_tab, ce * 16 + s, key);
                 }
             }
         }

@@ -178,16 +178,16 @@ bool run_fields(Job &job, Strategy st, PairSource &src, bool paired, DevicePool 
 // come back in order, and the selected byte runs are written from the pinned copy.
 class RawIngest {
 public:
-    static constexpr size_t kPad = 1u << 20;        // room in front of a window for the carried partial record
     static constexpr size_t kSlice = 8u << 20;
-    RawIngest(int fd, uint64_t file_size, size_t window, int nbuf, int nthreads)
-        : fd_(fd), size_(file_size), window_(window), nbuf_(nbuf)
+    // `pad` = room in front of every window for the carried partial record
+    RawIngest(int fd, uint64_t file_size, size_t window, size_t pad, int nbuf, int nthreads)
+        : fd_(fd), size_(file_size), window_(window), pad_(pad), nbuf_(nbuf)
     {
         nwin_ = (size_ + window_ - 1) / window_;
         bufs_.resize(nbuf_);
         for (Buf &b : bufs_) {
             void *p = nullptr;
-            if (fxg_host_alloc(&p, kPad + window_ + 64) != FXG_OK) { fprintf(stderr, "fxtract: cannot allocate pinned staging memory: %s\n", fxg_last_error(nullptr)); exit(1); }
+            if (fxg_host_alloc(&p, pad_ + window_ + 64) != FXG_OK) { fprintf(stderr, "fxtract: cannot allocate pinned staging memory: %s\n", fxg_last_error(nullptr)); exit(1); }
             b.mem = (uint8_t *)p;
         }
         done_.assign(nwin_, 0);
@@ -201,7 +201,7 @@ public:
         for (Buf &b : bufs_) fxg_host_free(b.mem);
     }
     uint64_t windows() const { return nwin_; }
-    // blocks until window k is in memory; returns its first byte (kPad bytes of pad lie in front of it) and length
+    // blocks until window k is in memory; returns its first byte (`pad` bytes lie in front of it) and length
     uint8_t *wait_window(uint64_t k, size_t *len)
     {
         std::unique_lock<std::mutex> l(mu_);
@@ -209,7 +209,7 @@ public:
         cv_.wait(l, [&] { return done_[k] == want || failed_; });
         if (failed_) { perror("fxtract: read"); exit(1); }
         *len = win_len(k);
-        return bufs_[k % nbuf_].mem + kPad;
+        return bufs_[k % nbuf_].mem + pad_;
     }
     // window k's buffer may be overwritten (by window k + nbuf)
     void release_window(uint64_t k)
@@ -232,7 +232,7 @@ private:
                 k = next_win_; s = next_slice_;
                 if (++next_slice_ >= slices_in(k)) { next_slice_ = 0; ++next_win_; }
             }
-            uint8_t *dst = bufs_[k % nbuf_].mem + kPad + s * kSlice;
+            uint8_t *dst = bufs_[k % nbuf_].mem + pad_ + s * kSlice;
             const uint64_t off = k * window_ + (uint64_t)s * kSlice;
             size_t want = std::min(kSlice, win_len(k) - s * kSlice), have = 0;
             bool bad = false;
@@ -245,7 +245,7 @@ private:
             cv_.notify_all();
         }
     }
-    int fd_; uint64_t size_; size_t window_; int nbuf_;
+    int fd_; uint64_t size_; size_t window_, pad_; int nbuf_;
     uint64_t nwin_ = 0;
     std::vector<Buf> bufs_;
     std::vector<size_t> done_;
@@ -285,10 +285,10 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
     if (pread(fd, magic, 2, 0) < 1 || magic[0] != '@') return -1;      // FASTA, gzip (1f 8b), empty, ...: general reader
     const CliOptions &o = job.opt;
     const uint64_t file_size = (uint64_t)sb.st_size;
-    if (pool.batch_bytes() <= 2 * RawIngest::kPad) return -1;
-    const size_t window = pool.batch_bytes() - RawIngest::kPad;       // a batch = carried tail + one window <= batch_bytes
+    const size_t pad = std::min<size_t>((size_t)1 << 20, pool.batch_bytes() / 4) & ~(size_t)63;
+    const size_t window = pool.batch_bytes() - pad;                    // a batch = carried tail + one window <= batch_bytes
     const int nbuf = (int)pool.capacity() + 2;                         // in flight on the devices + being filled / cut
-    RawIngest ingest(fd, file_size, window, nbuf, reader_threads_from_env());
+    RawIngest ingest(fd, file_size, window, pad, nbuf, reader_threads_from_env());
     std::deque<RawPending> pending;
     int64_t reroute_at = -1;
     auto finish_oldest = [&]() {
@@ -313,7 +313,7 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
         if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute_at >= 0) break; }
         size_t wlen;
         uint8_t *w = ingest.wait_window(k, &wlen);
-        if (carry_n > RawIngest::kPad) {                // a record longer than the pad: not the fast path's business
+        if (carry_n > pad) {                            // a record longer than the pad: not the fast path's business
             while (!pending.empty()) finish_oldest();
             if (reroute_at < 0) reroute_at = (int64_t)consumed;
             break;

@@ -7,11 +7,14 @@
  * It is built by tests/test_cli_host.py into tests/cpu_shim/_build/ and reaches the CLI only
  * through an explicit LD_LIBRARY_PATH set by that test.  It is never installed, never on the
  * product's rpath, and proves nothing about the CUDA kernels: GPU parity is tests -m gpu.
- * The raw path always answers "not canonical", which forces (and thereby tests) the re-route.
+ * The raw path answers "not canonical", which forces (and thereby tests) the re-route -- unless FXSHIM_RAW=1 is
+ * set: then literal / sequence-target batches are walked on the CPU so that the host's threaded ingest (windows,
+ * carried partial records, ordering over several contexts) can be tested without a GPU.
  */
 #include "../../include/fxgpu.h"
 #include "../../oracle/fxo_ac.h"
 #include <stdlib.h>
+#include <stdio.h>
 #include <string.h>
 
 struct fxg_ctx {
@@ -21,6 +24,7 @@ struct fxg_ctx {
     uint8_t *buf[2]; int state[2];          /* 0 free 1 lent 2 submitted */
     uint8_t *flags[2]; int32_t *pid[2]; uint64_t nrec[2], nhit[2]; int raw[2];
     int fifo[2]; int nfifo;
+    const uint8_t *rawp[2]; size_t rawn[2]; fxg_run *runs[2];   /* FXSHIM_RAW=1: a plain CPU walk over canonical FASTQ */
 };
 
 static const char *g_err = "";
@@ -75,6 +79,7 @@ int fxg_acquire_buffer(fxg_ctx *c, void **pinned, size_t *cap)
     return FXG_ERR_STATE;
 }
 
+static const uint8_t *find_bytes(const uint8_t *h, size_t hn, const uint8_t *p, size_t pn);
 static int lent(fxg_ctx *c) { for (int i = 0; i < 2; ++i) if (c->state[i] == 1) return i; return -1; }
 
 int fxg_submit_raw(fxg_ctx *c, size_t nbytes, int is_last)
@@ -88,9 +93,10 @@ int fxg_submit_raw(fxg_ctx *c, size_t nbytes, int is_last)
 
 int fxg_submit_raw_from(fxg_ctx *c, const void *h, size_t n, int l)
 {
-    (void)h; (void)l;
+    (void)l;
     for (int i = 0; i < 2; ++i) if (c->state[i] == 0) {
         c->raw[i] = n ? 1 : 2; c->state[i] = 2; c->fifo[c->nfifo++] = i;
+        c->rawp[i] = (const uint8_t *)h; c->rawn[i] = n;
         return FXG_OK;
     }
     g_err = "both slots are in flight";
@@ -142,7 +148,35 @@ int fxg_collect(fxg_ctx *c, fxg_result *r)
     int s = c->fifo[0];
     c->fifo[0] = c->fifo[1]; c->nfifo--;
     memset(r, 0, sizeof *r);
-    if (c->raw[s]) {                         /* raw path: always "not canonical" (empty batches are fine) */
+    if (c->raw[s] == 1 && getenv("FXSHIM_RAW") && c->cfg.mode == FXG_MODE_LITERAL && c->cfg.target == FXG_TARGET_SEQ) {
+        /* host-ingest tests: the batch must be whole 4-line records; literal search on the sequence line, runs of
+         * consecutive selected records (NOT the product's algorithm, and no validation beyond the line count) */
+        const uint8_t *b = c->rawp[s]; size_t n = c->rawn[s], pos = 0, run_start = 0; int in_run = 0;
+        free(c->runs[s]); c->runs[s] = (fxg_run *)malloc(sizeof(fxg_run) * (n / 8 + 2));
+        r->canonical_ok = 1;
+        while (pos < n) {
+            size_t e[4], q = pos; int ok = 1;
+            for (int k = 0; k < 4; ++k) {
+                const uint8_t *nl = (const uint8_t *)memchr(b + q, '\n', n - q);
+                if (!nl) { ok = 0; break; }
+                e[k] = (size_t)(nl - b); q = e[k] + 1;
+            }
+            if (!ok || b[pos] != '@') { r->canonical_ok = 0; r->violation = FXG_V_TRUNCATED; break; }
+            int hit = 0;
+            for (uint32_t p = 0; p < c->n && p < 2 && !hit; ++p)
+                hit = find_bytes(b + e[0] + 1, e[1] - e[0] - 1, c->blob + c->off[p], c->off[p + 1] - c->off[p]) != NULL;
+            r->n_records++; r->n_matched += hit;
+            int sel = hit ^ (c->cfg.invert ? 1 : 0);
+            r->n_selected += sel;
+            if (sel && !in_run) { in_run = 1; run_start = pos; }
+            if (!sel && in_run) { in_run = 0; c->runs[s][r->n_runs].off = run_start; c->runs[s][r->n_runs++].len = pos - run_start; }
+            pos = q;
+        }
+        if (in_run) { c->runs[s][r->n_runs].off = run_start; c->runs[s][r->n_runs++].len = pos - run_start; }
+        if (c->cfg.count_only) r->n_runs = 0;
+        r->runs = c->runs[s];
+        r->consumed_bytes = r->canonical_ok ? n : 0;
+    } else if (c->raw[s]) {                  /* raw path: "not canonical" (empty batches are fine) */
         r->canonical_ok = c->raw[s] == 2;
         r->violation = c->raw[s] == 2 ? 0 : FXG_V_DENSE_LINES;
     } else {
@@ -157,7 +191,19 @@ int fxg_count(fxg_ctx *c, uint64_t *t) { (void)c; *t = 0; return FXG_OK; }
 
 size_t fxg_find_record_cut(const uint8_t *buf, size_t n)
 {
-    /* any line start that looks like a header; the shim's raw path rejects everything anyway */
-    for (size_t c = n; c > 1; --c) if (buf[c - 1] == '@' && buf[c - 2] == '\n') return c - 1;
+    /* last line start that opens a record: '@' there and '+' at the start of the line after next */
+    size_t pos = n;
+    for (int tries = 0; tries < 64 && pos > 0; ++tries) {
+        size_t c = pos - 1;
+        while (c > 0 && buf[c - 1] != '\n') --c;
+        if (buf[c] == '@') {
+            const uint8_t *e1 = (const uint8_t *)memchr(buf + c, '\n', n - c);
+            if (e1) {
+                const uint8_t *e2 = (const uint8_t *)memchr(e1 + 1, '\n', n - (size_t)(e1 + 1 - buf));
+                if (e2 && (size_t)(e2 + 1 - buf) < n && e2[1] == '+') return c;
+            }
+        }
+        pos = c;
+    }
     return 0;
 }

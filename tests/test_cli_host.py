@@ -85,3 +85,25 @@ def test_large_streaming_inputs(shim_env, tmp_path):
         r1 = subprocess.run([helpers.REF_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
         r2 = subprocess.run([helpers.PRODUCT_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env)
         assert r1.stdout == r2.stdout, (argv, len(r1.stdout), len(r2.stdout), r2.stderr[-300:])
+
+
+def test_raw_ingest_windows_and_carry(shim_env, tmp_path):
+    """Threaded window ingest of the raw path (strategies.cpp, RawIngest): windows smaller than the file, partial
+    records carried from window to window, several reader threads, two contexts dealt round-robin -- output must be
+    the reference's.  The shim walks the batches on the CPU (FXSHIM_RAW=1); the kernels are not under test here."""
+    if not os.path.exists(helpers.REF_CLI):
+        pytest.skip("oracle/_ref/fxtract not built")
+    rng = random.Random(5)
+    wd = str(tmp_path)
+    fq = helpers.make_fastq(rng, 40000, seqlen=(30, 300))
+    open(os.path.join(wd, "w.fq"), "wb").write(fq)
+    pat = helpers.pick_substring(rng, fq, 5, 7).decode()
+    for mib, readers, devs in (("1", "1", "0"), ("1", "5", "0,0,0"), ("2", "3", "0,0"), ("64", "4", "0")):
+        env = dict(shim_env, FXSHIM_RAW="1", FXTRACT_PATH="raw", FXTRACT_BATCH_MIB=mib, FXTRACT_READERS=readers,
+                   FXTRACT_DEVICES=devs, FXTRACT_STATS="1")
+        for argv in (["-S", pat, "w.fq"], ["-Sv", pat, "w.fq"], ["-Sc", pat, "w.fq"], ["-Sc", pat, "w.fq", "w.fq"]):
+            r1 = subprocess.run([helpers.REF_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+            r2 = subprocess.run([helpers.PRODUCT_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=120)
+            assert r2.returncode == 0, (argv, r2.stderr[-300:])
+            assert r1.stdout == r2.stdout, (mib, readers, devs, argv, len(r1.stdout), len(r2.stdout), r2.stderr[-300:])
+            assert b"raw 0 B" not in r2.stderr and b"0 re-routed" in r2.stderr, r2.stderr

@@ -191,7 +191,8 @@ def test_exact_fused_long_reads_and_redo(fx):
     assert got["ok"] == 1 and got["out"] == want
     # the k-mer matcher over the same input (long reads, occurrences across several tile edges)
     pats = sorted(set(helpers.rand_dna(rng, 24).encode() for _ in range(50)) |
-                  set(s[o:o + 24] for s in lines[1::4] if len(s) > 30000 for o in (0, 24576 - 10, 32768 - 7, len(s) - 24)))
+                  set(s[o:o + 24] for s in lines[1::4] if len(s) > 30000 for o in (0, 24576 - 10, 32768 - 7, len(s) - 24)
+                      if len(s[o:o + 24]) == 24))
     want = fxoracle.run(data, "", pattern_file=b"\n".join(pats) + b"\n")
     got = run_raw(fx, data, fx.MODE_MULTI, pats)
     assert got["ok"] == 1 and got["out"] == want and len(want) > 0
@@ -207,12 +208,12 @@ def test_short_records_are_never_dropped(fx, rec_bytes):
     nrec = 60000                                        # > 15 KB of input per the finding, many tiles
     recs = []
     for i in range(nrec):
-        # "@" name "\n" seq "\n+\n" qual "\n": 5 + |name| + 2 |seq| bytes
-        slen = rng.randint(3, max(3, (rec_bytes - 8) // 2))
-        nlen = rec_bytes - 5 - 2 * slen
+        # "@" name "\n" seq "\n+\n" qual "\n": 6 + |name| + 2 |seq| bytes
+        slen = rng.randint(3, max(3, (rec_bytes - 9) // 2))
+        nlen = rec_bytes - 6 - 2 * slen
         if nlen < 1:
-            slen = (rec_bytes - 6) // 2
-            nlen = rec_bytes - 5 - 2 * slen
+            slen = (rec_bytes - 7) // 2
+            nlen = rec_bytes - 6 - 2 * slen
         name = (b"%x" % i).rjust(nlen, b"n")[-nlen:]
         seq = helpers.rand_dna(rng, slen).encode()
         recs.append(b"@" + name + b"\n" + seq + b"\n+\n" + b"I" * slen + b"\n")
