@@ -46,14 +46,14 @@ struct fxg_ctx {
     uint8_t *d_cls = nullptr; int *d_next = nullptr; int *d_out = nullptr; int ac_ncls = 0, ac_nstates = 0;
     unsigned int *d_kfilter = nullptr, *d_kkey = nullptr, *d_kval = nullptr;      // packed k-mer index of the field engine (ACGT pattern sets)
     unsigned int k_mask = 0, k_kmask = 0; int k_k = 0, k_stride = 0; bool kmer_ok = false;
-    unsigned int *d_ktfilter = nullptr, *d_ktkey = nullptr, *d_ktval = nullptr;   // window index of the fused scan matcher (KmerTile)
+    unsigned int *d_ktfilter = nullptr; uint4 *d_ktht = nullptr, *d_ktrec = nullptr;  // window index of the fused scan matcher (KmerTile)
     fxg::KmerTile kt = {}; bool kt_ok = false;
     int scan_mode = 0;                  // kMode* the raw path runs with (fixed by fxg_set_patterns)
     int tile_bytes = 0, nl_stride = 0, hit_words = 0;     // geometry of that mode
     bool two_stage = false;             // FXG_TWO_STAGE=1: multi / exact keep the index pass + field matcher (A/B measurements)
     cudaStream_t copy_stream = nullptr; // H2D of batch k+1 overlaps the kernels of batch k
-    unsigned long long *d_slot_hash = nullptr; int *d_slot_pat = nullptr; unsigned int exact_mask = 0;
-    unsigned long long *d_key_words = nullptr; unsigned int *d_key_woff = nullptr;
+    uint4 *d_bkt = nullptr; unsigned int exact_mask = 0;                          // bucketed exact table
+    unsigned long long *d_key_words = nullptr;
     // scan resources (shared; everything is ordered on one stream)
     size_t cap_bytes = 0; size_t rec_cap = 0; size_t ntiles_cap = 0; size_t nblocks_cap = 0;
     fxg::TileInfo *d_info = nullptr; unsigned short *d_tile_nl = nullptr; unsigned int *d_tile_hit = nullptr;
@@ -269,60 +269,90 @@ static int build_kmer(fxg_ctx *ctx)
 }
 
 // ---------------------------------------------------------------- window index of the fused scan matcher (host build)
-// Usable when every pattern is a string over {A,C,G,T} of length >= 12 (fxg_common.cuh: KmerTile).  Probe stride S
-// (16, 8, 4 or 2 bytes) and window length k <= 16 with k + S - 1 <= shortest pattern: every pattern contributes
-// the windows at its offsets 0..S-1.  The largest S is taken whose k keeps the share of text windows that hit an
-// index entry by chance (entries / 4^k) under 1/64 -- those cost a table walk and a byte comparison each.
+// Usable when every pattern holds a run of >= 12 bases {A,C,G,T} (fxg_common.cuh: KmerTile); bytes outside such a
+// run (an N, an IUPAC code) are fine -- they are compared when a candidate is verified.  Probe stride S (16, 8, 4
+// or 2 bytes) and window length k <= 16 with k + S - 1 <= the shortest run: every pattern contributes the S windows
+// at the first S offsets of its run, so every occurrence holds a window at a probed text position.  The largest S
+// is taken whose k keeps the share of text windows that hit an index entry by chance (entries / 4^k) under 1/64 --
+// those cost a table look-up and a byte comparison each.
 static int build_kmer_tile(fxg_ctx *ctx)
 {
     ctx->kt_ok = false;
     const uint32_t n = ctx->npat;
-    uint32_t minlen = 0xffffffffu;
+    if (n == 0 || n >= (1u << 24)) return FXG_OK;
+    std::vector<uint32_t> run_start(n, 0);
+    uint32_t minrun = 0xffffffffu;
     for (uint32_t i = 0; i < n; ++i) {
-        const uint32_t len = ctx->off[i + 1] - ctx->off[i];
-        if (len < minlen) minlen = len;
-        for (uint32_t j = ctx->off[i]; j < ctx->off[i + 1]; ++j) if (!fxg_is_acgt(ctx->blob[j])) return FXG_OK;
+        // longest run of bases of pattern i
+        uint32_t best = 0, best_at = 0, cur = 0;
+        for (uint32_t j = ctx->off[i]; j < ctx->off[i + 1]; ++j) {
+            cur = fxg_is_acgt(ctx->blob[j]) ? cur + 1 : 0;
+            if (cur > best) { best = cur; best_at = j + 1 - cur - ctx->off[i]; }
+        }
+        run_start[i] = best_at;
+        if (best < minrun) minrun = best;
     }
-    if (n == 0 || minlen < 12 || n >= (1u << 26)) return FXG_OK;
+    if (minrun < 12) return FXG_OK;
     int S = 0, k = 0;
     for (int s = 16; s >= 2; s >>= 1) {
-        if ((int)minlen - s + 1 < 11) continue;
-        const int kk = std::min(16, (int)minlen - s + 1);
+        if ((int)minrun - s + 1 < 11) continue;
+        const int kk = std::min(16, (int)minrun - s + 1);
         const double space = kk >= 16 ? 4294967296.0 : (double)(1ull << (2 * kk));
         if ((double)n * s / space > 1.0 / 64) continue;
         S = s; k = kk;
         break;
     }
     if (!S) return FXG_OK;
+    for (uint32_t i = 0; i < n; ++i) if (run_start[i] + (uint32_t)S > 128u) return FXG_OK;     // window offsets are stored in 7 bits
     const unsigned int kmask = k == 16 ? 0xffffffffu : ((1u << (2 * k)) - 1u);
     const size_t entries = (size_t)n * (size_t)S;
-    size_t nslots = 16;
-    while (nslots < entries * 2) nslots <<= 1;
-    if (nslots > ((size_t)1 << 30)) return FXG_OK;
-    const int flw = entries <= 16384 ? 12 : 15;       // 16 KiB filter (2 CTAs / SM) or 128 KiB (1 CTA / SM)
-    std::vector<unsigned int> filter((size_t)1 << flw, 0u), hk(nslots, 0u), hv(nslots, 0u);
-    const unsigned int mask = (unsigned int)(nslots - 1);
+    size_t nbuckets = 16;                             // 4 entries per bucket, <= 1 on average
+    while (nbuckets < entries) nbuckets <<= 1;
+    if (nbuckets > ((size_t)1 << 28)) return FXG_OK;
+    const int flw = entries <= 16384 ? 12 : 15;       // 16 KiB filter (2 CTAs / SM) or 128 KiB (1 CTA / SM); 2 bits per entry
+    std::vector<unsigned int> filter((size_t)1 << flw, 0u), ht(nbuckets * 8, 0u);
+    std::vector<unsigned char> fill(nbuckets, 0);
+    const unsigned int mask = (unsigned int)(nbuckets - 1);
+    // pattern records {length, id, bytes}, 16-byte aligned, 48 bytes of slack at the end (the verifier fetches 3 x 16)
+    std::vector<unsigned int> rec;
+    std::vector<unsigned int> rec_at(n, 0);
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t len = ctx->off[i + 1] - ctx->off[i];
+        rec_at[i] = (unsigned int)(rec.size() / 4);
+        rec.push_back(len); rec.push_back(i);
+        const size_t words = (len + 3) / 4;
+        for (size_t w = 0; w < words; ++w) {
+            unsigned int v = 0;
+            for (uint32_t b = 0; b < 4 && w * 4 + b < len; ++b) v |= (unsigned int)ctx->blob[ctx->off[i] + w * 4 + b] << (8 * b);
+            rec.push_back(v);
+        }
+        while (rec.size() % 4) rec.push_back(0u);
+    }
+    for (int pad = 0; pad < 12; ++pad) rec.push_back(0u);
+    if (rec.size() / 4 >= ((size_t)1 << 25)) return FXG_OK;          // record offsets are stored in 25 bits
     for (uint32_t i = 0; i < n; ++i) {
         const uint8_t *p = ctx->blob.data() + ctx->off[i];
-        for (int o = 0; o < S; ++o) {
+        for (int j = 0; j < S; ++j) {
+            const unsigned int o = run_start[i] + (unsigned int)j;      // offset of the window inside the pattern
             unsigned int key = 0;
             for (int b = 0; b < k; ++b) key |= fxg_base_code(p[o + b]) << (2 * b);
             key &= kmask;
-            filter[kmer_tile_filter_word(key, flw)] |= 1u << kmer_tile_filter_bit(key);
-            unsigned int slot = kmer_tile_slot(key, mask);
-            while (hv[slot]) slot = (slot + 1) & mask;
-            hk[slot] = key; hv[slot] = ((i << 5) | (unsigned int)o) + 1u;
+            filter[kmer_tile_filter_word(key, flw)] |= kmer_tile_filter_mask(key);
+            unsigned int bkt = kmer_tile_bucket(key, mask);
+            while (fill[bkt] == 4) bkt = (bkt + 1) & mask;
+            const int e = fill[bkt]++;
+            ht[(size_t)bkt * 8 + e] = key; ht[(size_t)bkt * 8 + 4 + e] = ((rec_at[i] << 7) | o) + 1u;
         }
     }
     cudaError_t e;
     if ((e = dev_realloc(ctx->d_ktfilter, filter.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window filter");
-    if ((e = dev_realloc(ctx->d_ktkey, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window table");
-    if ((e = dev_realloc(ctx->d_ktval, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window table");
+    if ((e = dev_realloc(ctx->d_ktht, nbuckets * 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window table");
     if ((e = cudaMemcpy(ctx->d_ktfilter, filter.data(), filter.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload window filter");
-    if ((e = cudaMemcpy(ctx->d_ktkey, hk.data(), nslots * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload window table");
-    if ((e = cudaMemcpy(ctx->d_ktval, hv.data(), nslots * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload window table");
+    if ((e = cudaMemcpy(ctx->d_ktht, ht.data(), ht.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload window table");
+    if ((e = dev_realloc(ctx->d_ktrec, rec.size() / 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pattern records");
+    if ((e = cudaMemcpy(ctx->d_ktrec, rec.data(), rec.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload pattern records");
     KmerTile &K = ctx->kt;
-    K.filter = ctx->d_ktfilter; K.ht_key = ctx->d_ktkey; K.ht_val = ctx->d_ktval; K.blob = ctx->d_pat; K.off = ctx->d_patoff;
+    K.filter = ctx->d_ktfilter; K.ht = ctx->d_ktht; K.rec = ctx->d_ktrec;
     K.ht_mask = mask; K.kmask = kmask; K.k = k; K.stride = S; K.filter_log2_words = flw;
     ctx->kt_ok = true;
     return FXG_OK;
@@ -332,42 +362,40 @@ static int build_kmer_tile(fxg_ctx *ctx)
 static int build_exact(fxg_ctx *ctx)
 {
     const uint32_t n = ctx->npat;
-    size_t nslots = 16;
-    while (nslots < (size_t)n * 2) nslots <<= 1;
-    std::vector<unsigned long long> sh(nslots, 0); std::vector<int> sp(nslots, -1);
-    unsigned int mask = (unsigned int)(nslots - 1);
-    for (uint32_t i = 0; i < n; ++i) {
-        unsigned long long h = fxg_hash_bytes(ctx->blob.data() + ctx->off[i], ctx->off[i + 1] - ctx->off[i]);
-        unsigned int slot = (unsigned int)(h >> 20) & mask;
-        while (sh[slot] != 0) slot = (slot + 1) & mask;
-        sh[slot] = h; sp[slot] = (int)i;
-    }
-    cudaError_t e;
-    if ((e = dev_realloc(ctx->d_slot_hash, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
-    if ((e = dev_realloc(ctx->d_slot_pat, nslots)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
-    if ((e = cudaMemcpy(ctx->d_slot_hash, sh.data(), nslots * 8, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
-    e = cudaMemcpy(ctx->d_slot_pat, sp.data(), nslots * 4, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
-    ctx->exact_mask = mask;
-    // the keys once more as zero-padded little-endian words: the look-up kernel verifies 8 bytes per step
+    // key storage: meta word (pattern id << 32 | length) + the key as zero-padded little-endian 8-byte words
     std::vector<unsigned long long> kw; std::vector<unsigned int> kwoff(n ? n : 1, 0u);
     for (uint32_t i = 0; i < n; ++i) {
         const uint8_t *kp = ctx->blob.data() + ctx->off[i];
         const uint32_t len = ctx->off[i + 1] - ctx->off[i];
         kwoff[i] = (unsigned int)kw.size();
+        kw.push_back(((unsigned long long)i << 32) | len);
         for (uint32_t o = 0; o < len; o += 8) {
             unsigned long long w = 0;
             for (uint32_t b = 0; b < 8 && o + b < len; ++b) w |= (unsigned long long)kp[o + b] << (8 * b);
             kw.push_back(w);
         }
+        if (kw.size() > 0xfffffff0ull) return set_error(ctx, FXG_ERR_UNSUPPORTED, "key set too large for the exact table");
     }
-    if (kw.empty()) kw.push_back(0);
-    if (kw.size() > 0xffffffffull) return set_error(ctx, FXG_ERR_UNSUPPORTED, "key set too large for the exact table");
+    for (int pad = 0; pad < 8; ++pad) kw.push_back(0);
+    size_t nbuckets = 16;                             // 8 entries per bucket, <= 2 keys on average
+    while (nbuckets * 2 < (size_t)n) nbuckets <<= 1;
+    if (nbuckets > ((size_t)1 << 27)) return set_error(ctx, FXG_ERR_UNSUPPORTED, "key set too large for the exact table");
+    std::vector<unsigned int> bk(nbuckets * 16, 0u);  // per bucket: {fp, off} x 8
+    std::vector<unsigned char> fill(nbuckets, 0);
+    const unsigned int mask = (unsigned int)(nbuckets - 1);
+    for (uint32_t i = 0; i < n; ++i) {
+        const unsigned long long h = fxg_hash_bytes(ctx->blob.data() + ctx->off[i], ctx->off[i + 1] - ctx->off[i]);
+        unsigned int bkt = (unsigned int)h & mask;
+        while (fill[bkt] == 8) bkt = (bkt + 1) & mask;
+        const int e = fill[bkt]++;
+        bk[(size_t)bkt * 16 + 2 * e] = (unsigned int)(h >> 32) | 1u; bk[(size_t)bkt * 16 + 2 * e + 1] = kwoff[i];
+    }
+    cudaError_t e;
+    if ((e = dev_realloc(ctx->d_bkt, nbuckets * 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
+    if ((e = cudaMemcpy(ctx->d_bkt, bk.data(), bk.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
+    ctx->exact_mask = mask;
     if ((e = dev_realloc(ctx->d_key_words, kw.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key words");
-    if ((e = dev_realloc(ctx->d_key_woff, kwoff.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key words");
     if ((e = cudaMemcpy(ctx->d_key_words, kw.data(), kw.size() * 8, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload key words");
-    e = cudaMemcpy(ctx->d_key_woff, kwoff.data(), kwoff.size() * 4, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) return set_cuda_error(ctx, e, "upload key words");
     return FXG_OK;
 }
 
@@ -478,7 +506,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     P.header_whole = ctx->cfg.mode == FXG_MODE_EXACT && ctx->cfg.target == FXG_TARGET_NAME;
     if (mode_is_kmer(P.mode)) P.kmer = ctx->kt;
     if (P.mode == kModeExact) {
-        P.exact = ExactDevice{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask, ctx->d_key_words, ctx->d_key_woff};
+        P.exact = ExactDevice{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
         P.redo_unanchored = 1;
     }
     if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[1], st));
@@ -496,7 +524,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
             FXG_CUDA_OK(launch_fields_ac(src, rec_cap, A, O, st));
         } else {
-            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask, ctx->d_key_words, ctx->d_key_woff};
+            ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
             FXG_CUDA_OK(launch_fields_exact(src, rec_cap, E, O, st));
         }
         ctx->last_launches += 1;
@@ -623,7 +651,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h2d_done) cudaEventDestroy(s.h2d_done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_ktfilter, ctx->d_ktkey, ctx->d_ktval, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_key_words, ctx->d_key_woff,
+    void *dev[] = {ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
                    ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
@@ -819,7 +847,7 @@ extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *of
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
             FXG_CUDA_OK(launch_fields_ac(src, nrec, A, O, st));
         } else {
-            ExactDevice E{ctx->d_slot_hash, ctx->d_slot_pat, ctx->d_pat, ctx->d_patoff, ctx->exact_mask, ctx->d_key_words, ctx->d_key_woff};
+            ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
             FXG_CUDA_OK(launch_fields_exact(src, nrec, E, O, st));
         }
         ctx->last_launches = 1;

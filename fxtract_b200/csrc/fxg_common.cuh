@@ -99,18 +99,22 @@ __host__ __device__ constexpr bool mode_is_literal(int m) { return m == 1 || m =
 // alphabet ... warp-cooperative scan over coalesced 16-byte loads with overlap handling at chunk edges").
 // Position-centric: every 16-byte chunk of the staged tile is packed to 32 bits (2 bits per byte), a window of k <= 16
 // bases that starts at a byte offset == 0 (mod S) is the funnel shift of two neighbouring chunk words (the neighbour
-// comes from the next lane by shuffle), and is looked up in a one-bit hashed filter in shared memory.  Every pattern
+// comes from the next lane by shuffle), and is looked up in a hashed filter in shared memory (two bits of one word).  Every pattern
 // contributes its first S windows (offsets 0..S-1, k + S - 1 <= shortest pattern), so each occurrence contains one
 // probed window.  Filter hits are queued per warp and resolved after the newline table exists: open-addressing table
 // (L2) -> byte-wise verification against the pattern -> "local line i has a match" bit.  No false positives, no
 // false negatives; bytes that are not bases only make keys that no pattern has.
 struct KmerTile {
     const unsigned int *filter;            // [1 << filter_log2_words] device copy, staged into shared memory per CTA
-    const unsigned int *ht_key;            // [nslots] packed window
-    const unsigned int *ht_val;            // [nslots] 0 = empty, else ((pattern id << 5) | offset) + 1
-    const uint8_t *blob;                   // pattern bytes
-    const unsigned int *off;               // [n+1]
-    unsigned int ht_mask;                  // nslots - 1
+    // bucketed table: bucket b = 32 bytes (one L2 sector) = 4 keys (uint4 at ht[2b]) + 4 values (uint4 at ht[2b+1]);
+    // value 0 = empty, else ((record offset / 16 << 7) | window offset in the pattern) + 1; slots fill in order, a full bucket spills into the
+    // next one.  A look-up is ONE dependent memory round trip unless its bucket is full (~2 % at <= 1 entry per
+    // bucket): the drain of a tile waits for the slowest lane, so the chain length is what matters.
+    const uint4 *ht;                       // [2 * nbuckets]
+    // pattern records, 16-byte aligned: {length u32, pattern id u32, bytes ...}; a value of the table holds the
+    // record's offset in 16-byte units, so a window hit is verified after ONE more round trip
+    const uint4 *rec;
+    unsigned int ht_mask;                  // nbuckets - 1
     unsigned int kmask;                    // (1 << 2k) - 1
     int k, stride;                         // stride in {2, 4, 8, 16}
     int filter_log2_words;                 // 12 (16 KiB, 2 CTAs / SM) or 15 (128 KiB, 1 CTA / SM)
@@ -118,17 +122,24 @@ struct KmerTile {
 // window key of bases b[0..k): base i in bits 2i, 2i+1 (code = (byte >> 1) & 3); identical on host and device
 constexpr unsigned int kKmerHashMul = 0x9E3779B1u;
 __host__ __device__ inline unsigned int kmer_tile_filter_word(unsigned int key, int log2_words) { return (key * kKmerHashMul) >> (32 - log2_words); }
-__host__ __device__ inline unsigned int kmer_tile_filter_bit(unsigned int key) { return 31u - ((key * kKmerHashMul) & 31u); }
-__host__ __device__ inline unsigned int kmer_tile_slot(unsigned int key, unsigned int mask) { return ((key * kKmerHashMul) >> 7) & mask; }
+// two bits of one filter word per key: 31 - (h & 31) and 31 - ((h >> 5) & 31)
+__host__ __device__ inline unsigned int kmer_tile_filter_mask(unsigned int key)
+{
+    const unsigned int h = key * kKmerHashMul;
+    return (1u << (31u - (h & 31u))) | (1u << (31u - ((h >> 5) & 31u)));
+}
+__host__ __device__ inline unsigned int kmer_tile_bucket(unsigned int key, unsigned int mask) { return ((key * kKmerHashMul) >> 7) & mask; }
 
-struct ExactDevice {           // open-addressing table over whole-field keys
-    const unsigned long long *slot_hash;   // [nslots] 0 = empty
-    const int *slot_pat;                   // [nslots] pattern id
-    const uint8_t *blob;                   // pattern bytes
-    const unsigned int *off;               // [n+1]
-    unsigned int mask;                     // nslots - 1
-    const unsigned long long *kw;          // keys again as zero-padded little-endian 8-byte words (word-wise verification)
-    const unsigned int *kwoff;             // [n] first word of key i
+// Bucketed table over whole-field keys.  Bucket b = 8 entries {fingerprint, key offset} = 64 bytes (two L2 sectors,
+// fetched with four independent 16-byte loads); fingerprint 0 = empty, slots fill in order, a full bucket spills into
+// the next one (0.1 % of the buckets at <= 2 keys per bucket).  The key offset points into `kw`: one meta word
+// (pattern id << 32 | key length) followed by the key as zero-padded little-endian 8-byte words, so a fingerprint
+// match is verified after ONE more round trip.  The tile that issues a look-up waits for its slowest lane: what
+// counts is the length of the dependent chain -- one round trip for a miss, two for a hit -- not the average.
+struct ExactDevice {
+    const uint4 *bkt;                      // [4 * nbuckets] {fp0, off0, fp1, off1} x 4; fingerprint = (hash >> 32) | 1
+    const unsigned long long *kw;          // meta + key words per key (+ 8 words of slack at the end)
+    unsigned int mask;                     // nbuckets - 1; bucket = (unsigned)hash & mask
 };
 
 struct ScanParams {

@@ -2,8 +2,9 @@
 // global memory) and the fused scan kernel (fxg_scan_kernel.cuh: keys read from the staged tile in shared memory).
 //
 // Replaces manager.find(*data) of hash_search (main.cpp:315, fileManager.cpp:171-177: std::map<string,int>::find).
-// Open addressing over the 64-bit key hash of fxg_hash_bytes; a slot whose hash matches is verified word by word
-// against a zero-padded copy of the key, so no parity claim rests on the hash.
+// Bucketed table (ExactDevice, fxg_common.cuh) over the 64-bit key hash of fxg_hash_bytes: one 32-byte bucket per
+// look-up; a fingerprint match is verified word by word against a zero-padded copy of the key, so no parity claim
+// rests on the hash.
 #pragma once
 #include "fxg_common.cuh"
 
@@ -56,33 +57,39 @@ __device__ __forceinline__ bool exact_lookup(const ExactDevice &E, const LD &ld,
     }
     len = used;
     h = fxg_hash_finish(h, len);
-    unsigned int slot = (unsigned int)(h >> 20) & E.mask;
+    unsigned int bkt = (unsigned int)h & E.mask;
+    const unsigned int fp = (unsigned int)(h >> 32) | 1u;
     for (;;) {
-        const unsigned long long sv = __ldg(&E.slot_hash[slot]);
-        if (sv == 0) return false;
-        if (sv == h) {
-            const int cand = __ldg(&E.slot_pat[slot]);
-            const unsigned int a = __ldg(&E.off[cand]), b = __ldg(&E.off[cand + 1]);
-            if (b - a == len) {
-                bool eq = true;
-                if (len) {
-                    const unsigned long long *kw = E.kw + __ldg(&E.kwoff[cand]);
-                    long long wi = w0;
-                    unsigned int g0 = ld(wi);
-                    for (unsigned int o = 0; o < len; o += 8) {
-                        const unsigned int g1 = ld(wi + 1), g2 = ld(wi + 2);
-                        unsigned long long w = (unsigned long long)__funnelshift_r(g0, g1, sh) |
-                                               ((unsigned long long)__funnelshift_r(g1, g2, sh) << 32);
-                        if (len - o < 8) w &= (1ull << (8 * (len - o))) - 1ull;
-                        if (w != __ldg(&kw[o >> 3])) { eq = false; break; }
-                        g0 = g2;
-                        wi += 2;
-                    }
-                }
-                if (eq) { pid = cand; return true; }
+        const uint4 *B = E.bkt + 4 * (size_t)bkt;
+        const uint4 q0 = __ldg(B), q1 = __ldg(B + 1), q2 = __ldg(B + 2), q3 = __ldg(B + 3);
+        const unsigned int fps[8] = {q0.x, q0.z, q1.x, q1.z, q2.x, q2.z, q3.x, q3.z};
+        const unsigned int offs[8] = {q0.y, q0.w, q1.y, q1.w, q2.y, q2.w, q3.y, q3.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            if (fps[e] != fp) continue;
+            // meta word and the first four key words in one round trip (the array has slack behind the last key)
+            const unsigned long long *kw = E.kw + offs[e];
+            const unsigned long long meta = __ldg(kw);
+            const unsigned long long pre[4] = {__ldg(kw + 1), __ldg(kw + 2), __ldg(kw + 3), __ldg(kw + 4)};
+            if ((unsigned int)meta != len) continue;
+            bool eq = true;
+            long long wi = w0;
+            unsigned int g0 = ld(wi);
+            for (unsigned int o = 0; o < len; o += 8) {
+                const unsigned int g1 = ld(wi + 1), g2 = ld(wi + 2);
+                unsigned long long w = (unsigned long long)__funnelshift_r(g0, g1, sh) |
+                                       ((unsigned long long)__funnelshift_r(g1, g2, sh) << 32);
+                if (len - o < 8) w &= (1ull << (8 * (len - o))) - 1ull;
+                const unsigned int i = o >> 3;
+                const unsigned long long kv = i == 0 ? pre[0] : (i == 1 ? pre[1] : (i == 2 ? pre[2] : (i == 3 ? pre[3] : __ldg(kw + 1 + i))));
+                if (w != kv) { eq = false; break; }
+                g0 = g2;
+                wi += 2;
             }
+            if (eq) { pid = (int)(meta >> 32); return true; }
         }
-        slot = (slot + 1) & E.mask;
+        if (q3.z == 0u) return false;                      // the bucket has a free slot: nothing spilled past it
+        bkt = (bkt + 1) & E.mask;
     }
 }
 

@@ -340,28 +340,47 @@ __device__ __noinline__ void kmer_resolve(ScanSmem<G> &S, TileState &T, const un
                                           unsigned long long base, int n_tab, int win_rel, unsigned int key)
 {
     const KmerTile &K = P.kmer;
-    unsigned int slot = kmer_tile_slot(key, K.ht_mask);
+    unsigned int bkt = kmer_tile_bucket(key, K.ht_mask);
     for (;;) {
-        const unsigned int v = __ldg(&K.ht_val[slot]);
-        if (!v) return;
-        if (__ldg(&K.ht_key[slot]) == key) {
-            const unsigned int q = (v - 1u) >> 5, o = (v - 1u) & 31u;
-            const unsigned int a = __ldg(&K.off[q]), m = __ldg(&K.off[q + 1]) - a;
+        const uint4 kk = __ldg(K.ht + 2 * (size_t)bkt), vv = __ldg(K.ht + 2 * (size_t)bkt + 1);
+        const unsigned int keys[4] = {kk.x, kk.y, kk.z, kk.w}, vals[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const unsigned int v = vals[e];
+            if (!v || keys[e] != key) continue;
+            const unsigned int o = (v - 1u) & 127u;
+            const uint4 *rec = K.rec + ((v - 1u) >> 7);
+            // pattern record: {length, id, bytes}; the first 40 pattern bytes arrive in one round trip
+            const uint4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
+            const unsigned int m = r0.x;
             const long long p = (long long)base + win_rel - (long long)o;
-            if (p >= 0 && (unsigned long long)p + m <= P.nbytes) {
-                bool eq = true;
-                for (unsigned int i = 0; i < m; ++i)
-                    if (text_byte<G>(tb, P, base, p + i) != K.blob[a + i]) { eq = false; break; }
-                if (eq) {
-                    const long long rel = p - (long long)base;
-                    const unsigned int loc = rel > 0 ? lines_before(S, n_tab, (int)rel) : 0u;
-                    atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31));
-                    atomicOr(&T.viol, kTileHasHit);
-                    return;
+            if (p < 0 || (unsigned long long)p + m > P.nbytes) continue;
+            const unsigned int head[10] = {r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
+            bool eq = true;
+            for (unsigned int i = 0; i < m && eq; i += 4) {
+                unsigned int w;
+                if (i < 40) {
+                    w = head[0];
+#pragma unroll
+                    for (int q = 1; q < 10; ++q) if ((i >> 2) == (unsigned int)q) w = head[q];
+                } else {
+                    const uint4 rr = __ldg(rec + ((i + 8) >> 4));
+                    const unsigned int sel = ((i + 8) >> 2) & 3u;
+                    w = sel == 0 ? rr.x : (sel == 1 ? rr.y : (sel == 2 ? rr.z : rr.w));
                 }
+                for (unsigned int b = 0; b < 4 && i + b < m; ++b)
+                    if (text_byte<G>(tb, P, base, p + i + b) != ((w >> (8 * b)) & 0xffu)) { eq = false; break; }
+            }
+            if (eq) {
+                const long long rel = p - (long long)base;
+                const unsigned int loc = rel > 0 ? lines_before(S, n_tab, (int)rel) : 0u;
+                atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31));
+                atomicOr(&T.viol, kTileHasHit);
+                return;
             }
         }
-        slot = (slot + 1) & K.ht_mask;
+        if (vv.w == 0u) return;                            // the bucket has a free slot: nothing spilled past it
+        bkt = (bkt + 1) & K.ht_mask;
     }
 }
 
@@ -585,7 +604,8 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                     unsigned int acc = 0;
                     if (SB == 16) {
                         const unsigned int h = (pack16(x) & kmask) * kKmerHashMul;
-                        acc = __funnelshift_l(0u, filt[h >> fshift], h) >> 31;
+                        const unsigned int fw = filt[h >> fshift];
+                        acc = (__funnelshift_l(0u, fw, h) & __funnelshift_l(0u, fw, h >> 5)) >> 31;
                     } else {
                         const unsigned int pk = pkn;
                         xn = tile[c + 32];                            // lane's chunk of the next step (see above)
@@ -597,8 +617,10 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                         for (int s = 0; s < 16; s += SB) {
                             const unsigned int key = (s ? __funnelshift_r(pk, pq, 2 * s) : pk) & kmask;
                             const unsigned int h = key * kKmerHashMul;
-                            // filter bit 31 - (h & 31) of word h >> fshift, moved to the top and shifted into acc
-                            acc = __funnelshift_l(__funnelshift_l(0u, filt[h >> fshift], h), acc, 1);
+                            // filter bits 31 - (h & 31) and 31 - ((h >> 5) & 31) of word h >> fshift, moved to the top,
+                            // combined and shifted into acc
+                            const unsigned int fw = filt[h >> fshift];
+                            acc = __funnelshift_l(__funnelshift_l(0u, fw, h) & __funnelshift_l(0u, fw, h >> 5), acc, 1);
                         }
                     }
                     const unsigned int vb = __ballot_sync(0xffffffffu, acc != 0u);

@@ -16,7 +16,7 @@ if [ "${TESTS-all}" != "" ]; then
 fi
 : > gpurun_out/workloads.txt
 for w in ${WORKLOADS:-c2 c3 c4 c5v c5c}; do
-  timeout 600 python bench.py --workload $w --records ${RECORDS:-20000000} --steps ${STEPS:-5} --warmup 3 --no-e2e --no-cpu-baseline ${BENCH_EXTRA} \
+  timeout 600 python bench.py --workload $w --records ${RECORDS:-20000000} --steps ${STEPS:-5} --warmup 3 --also '' --no-e2e --no-cpu-baseline --no-cli ${BENCH_EXTRA} \
      > gpurun_out/wl_$w.json 2> gpurun_out/wl_$w.err; echo "$w rc=$?" >> gpurun_out/workloads.txt
   python - "$w" <<'PY' >> gpurun_out/workloads.txt
 import json, sys

@@ -110,6 +110,39 @@ def test_kmer_fused_revcomp_and_quality_lookalikes(fx):
     assert got_q["ok"] == 1 and got_q["out"] == want_q
 
 
+def test_kmer_fused_patterns_with_non_base_bytes(fx):
+    """The reference's own speed-test sets hold a pattern with an N (fxtract_test/speed_test/random_10000_*): such a
+    pattern is indexed by the windows of its longest run of bases and compared in full when a window hits, so the set
+    stays on the fused matcher; the N only matches an N in the text."""
+    rng = random.Random(31)
+    pats = set(helpers.rand_dna(rng, rng.randint(20, 40)).encode() for _ in range(400))
+    odd = []
+    for _ in range(40):
+        p = bytearray(helpers.rand_dna(rng, rng.randint(28, 60)).encode())
+        pos = rng.choice([0, len(p) - 1, rng.randint(0, len(p) - 1)])
+        p[pos] = rng.choice(b"NRYn")
+        odd.append(bytes(p))
+    allp = sorted(pats | set(odd))
+    recs = []
+    for i in range(5000):
+        n = rng.randint(70, 200)
+        seq = bytearray(helpers.rand_dna(rng, n).encode())
+        if i % 3 == 0:
+            p = rng.choice(odd if i % 2 else allp)
+            o = rng.randint(0, n - len(p))
+            seq[o:o + len(p)] = p
+            if i % 12 == 3:                                   # the odd byte replaced by a base: must NOT match
+                for k, ch in enumerate(p):
+                    if ch not in b"ACGT":
+                        seq[o + k] = ord("A")
+        recs.append(b"@o%d\n" % i + bytes(seq) + b"\n+\n" + b"I" * n + b"\n")
+    data = b"".join(recs)
+    want = fxoracle.run(data, "", pattern_file=b"\n".join(allp) + b"\n")
+    got = run_raw(fx, data, fx.MODE_MULTI, allp)
+    assert got["ok"] == 1 and got["out"] == want, (len(got["out"]), len(want))
+    assert 1000 < want.count(b"\n") // 4 < 1700
+
+
 def test_kmer_fused_equals_two_stage(fx, monkeypatch):
     """FXG_TWO_STAGE=1 keeps the round-1 pipeline (index pass + field matcher); both must select the same records."""
     rng = random.Random(5)
