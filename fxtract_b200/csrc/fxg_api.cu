@@ -43,7 +43,7 @@ struct fxg_ctx {
     fxg::LiteralTable h_lit;
     fxg::LiteralTable *d_lit = nullptr;
     uint8_t *d_pat = nullptr; uint32_t *d_patoff = nullptr;
-    uint8_t *d_cls = nullptr; int *d_next = nullptr; int *d_out = nullptr; int ac_ncls = 0, ac_nstates = 0;
+    uint8_t *d_cls = nullptr; int *d_next = nullptr; int *d_out = nullptr; int ac_ncls = 0, ac_nstates = 0, ac_wide = 0;
     unsigned int *d_kfilter = nullptr, *d_kkey = nullptr, *d_kval = nullptr;      // packed k-mer index of the field engine (ACGT pattern sets)
     unsigned int k_mask = 0, k_kmask = 0; int k_k = 0, k_stride = 0; bool kmer_ok = false;
     unsigned int *d_ktfilter = nullptr; uint4 *d_ktht = nullptr, *d_ktrec = nullptr;  // window index of the fused scan matcher (KmerTile)
@@ -53,6 +53,8 @@ struct fxg_ctx {
     bool two_stage = false;             // FXG_TWO_STAGE=1: multi / exact keep the index pass + field matcher (A/B measurements)
     cudaStream_t copy_stream = nullptr; // H2D of batch k+1 overlaps the kernels of batch k
     uint4 *d_bkt = nullptr; unsigned int exact_mask = 0;                          // bucketed exact table
+    unsigned long long *d_keyhash = nullptr;                                      // exact mode: key hash per target line (scan -> resolve)
+    uint2 *d_cand = nullptr; unsigned int *d_tile_ncand = nullptr;                // k-mer mode: filter hits per tile (scan -> resolve)
     unsigned long long *d_key_words = nullptr;
     // scan resources (shared; everything is ordered on one stream)
     size_t cap_bytes = 0; size_t rec_cap = 0; size_t ntiles_cap = 0; size_t nblocks_cap = 0;
@@ -208,13 +210,25 @@ static int build_ac(fxg_ctx *ctx)
             else { fail[t] = next[(size_t)f * ncls + c]; queue.push_back(t); }
         }
     }
+    // transition entries: next state | high bit "the next state reports a pattern"; 16 bits while the states fit
+    const bool wide = ns >= 32768;
+    std::vector<unsigned short> n16; std::vector<unsigned int> n32;
+    if (wide) {
+        n32.resize(next.size() + 4, 0u);
+        for (size_t i = 0; i < next.size(); ++i) n32[i] = (unsigned int)next[i] | (out[next[i]] >= 0 ? 0x80000000u : 0u);
+    } else {
+        n16.resize(next.size() + 8, 0);
+        for (size_t i = 0; i < next.size(); ++i) n16[i] = (unsigned short)((unsigned int)next[i] | (out[next[i]] >= 0 ? 0x8000u : 0u));
+    }
     cudaError_t e;
     if ((e = dev_realloc(ctx->d_cls, 256)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc cls");
-    if ((e = dev_realloc(ctx->d_next, next.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc dfa");
+    if ((e = dev_realloc(ctx->d_next, wide ? n32.size() : (n16.size() + 1) / 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc dfa");
     if ((e = dev_realloc(ctx->d_out, out.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc dfa out");
     if ((e = cudaMemcpy(ctx->d_cls, cls.data(), 256, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa classes");
-    if ((e = cudaMemcpy(ctx->d_next, next.data(), next.size() * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa");
+    if ((e = cudaMemcpy(ctx->d_next, wide ? (const void *)n32.data() : (const void *)n16.data(), wide ? n32.size() * 4 : n16.size() * 2,
+                        cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa");
     if ((e = cudaMemcpy(ctx->d_out, out.data(), out.size() * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload dfa");
+    ctx->ac_wide = wide ? 1 : 0;
     ctx->ac_ncls = ncls; ctx->ac_nstates = (int)ns;
     return FXG_OK;
 }
@@ -420,6 +434,12 @@ static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
     if (ctx->scan_mode != kModeIndex &&
         (e = dev_realloc(ctx->d_tile_hit, ntiles * (size_t)ctx->hit_words)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line hits");
     if ((e = dev_realloc(ctx->d_hitbits, words + 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc hit bitset");
+    if (ctx->scan_mode == kModeExact &&
+        (e = dev_realloc(ctx->d_keyhash, ntiles * (size_t)(ctx->nl_stride / 4))) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key hashes");
+    if (mode_is_kmer(ctx->scan_mode)) {
+        if ((e = dev_realloc(ctx->d_cand, ntiles * (size_t)kKmerCandCap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window candidates");
+        if ((e = dev_realloc(ctx->d_tile_ncand, ntiles)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window candidate counts");
+    }
     if (!ctx->d_ctr && (e = dev_realloc(ctx->d_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counters");
     if (!ctx->d_counts && (e = dev_realloc(ctx->d_counts, 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counts");
     if (!ctx->cfg.count_only) {
@@ -504,9 +524,10 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     const bool field_stage = P.mode == kModeIndex && !literal;
     if (field_stage) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
     P.header_whole = ctx->cfg.mode == FXG_MODE_EXACT && ctx->cfg.target == FXG_TARGET_NAME;
-    if (mode_is_kmer(P.mode)) P.kmer = ctx->kt;
+    if (mode_is_kmer(P.mode)) { P.kmer = ctx->kt; P.cand = ctx->d_cand; P.tile_ncand = ctx->d_tile_ncand; P.cand_cap = kKmerCandCap; }
     if (P.mode == kModeExact) {
         P.exact = ExactDevice{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
+        P.keyhash = ctx->d_keyhash;
         P.redo_unanchored = 1;
     }
     if (ctx->profiling) FXG_CUDA_OK(cudaEventRecord(s.ev[1], st));
@@ -521,7 +542,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
             KmerDevice K{ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_pat, ctx->d_patoff, ctx->k_mask, ctx->k_kmask, ctx->k_k, ctx->k_stride};
             FXG_CUDA_OK(launch_fields_kmer(src, rec_cap, K, O, st));
         } else if (ctx->cfg.mode == FXG_MODE_MULTI) {
-            AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
+            AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates, ctx->ac_wide};
             FXG_CUDA_OK(launch_fields_ac(src, rec_cap, A, O, st));
         } else {
             ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
@@ -651,7 +672,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h2d_done) cudaEventDestroy(s.h2d_done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
+    void *dev[] = {ctx->d_keyhash, ctx->d_cand, ctx->d_tile_ncand, ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
                    ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
@@ -844,7 +865,7 @@ extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *of
             KmerDevice K{ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_pat, ctx->d_patoff, ctx->k_mask, ctx->k_kmask, ctx->k_k, ctx->k_stride};
             FXG_CUDA_OK(launch_fields_kmer(src, nrec, K, O, st));
         } else if (ctx->cfg.mode == FXG_MODE_MULTI) {
-            AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates};
+            AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates, ctx->ac_wide};
             FXG_CUDA_OK(launch_fields_ac(src, nrec, A, O, st));
         } else {
             ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};

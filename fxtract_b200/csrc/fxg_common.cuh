@@ -37,6 +37,7 @@ template <int TILE_BYTES, int THREADS, int MIN_CTAS> struct Geom {
 typedef Geom<24576, 384, 3> G24;
 typedef Geom<32768, 512, 2> G32;
 constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
+constexpr int kKmerCandCap = 1024;             // k-mer mode: filter hits listed per tile for kmer_resolve_kernel
 
 // ---------------------------------------------------------------- per-tile results
 // The scan kernel has no cross-tile dependency: every tile publishes its '\n' count, its
@@ -170,7 +171,11 @@ struct ScanParams {
     unsigned int *redo_count;         // [1]
     int redo_unanchored;              // exact mode: tiles without a phase anchor go to the REDO launch too
     KmerTile kmer;                    // mode_is_kmer(mode)
+    uint2 *cand;                      // [ntiles * cand_cap] k-mer mode: {window key, tile-relative offset} per filter hit
+    unsigned int *tile_ncand;         // [ntiles] entries of the tile's candidate list
+    int cand_cap;                     // list capacity per tile (what does not fit is resolved inside the scan kernel)
     ExactDevice exact;                // mode == kModeExact
+    unsigned long long *keyhash;      // [ntiles * nl_stride / 4] exact mode: key hash of the target line with local index 4j + first
     // field table for the second-stage matchers (multi without k-mer index): target field of record k
     unsigned long long *fld_off;      // [rec_cap] or nullptr
     unsigned int *fld_len;            // [rec_cap]
@@ -179,12 +184,17 @@ struct ScanParams {
 };
 
 // ---------------------------------------------------------------- field engine
-struct AcDevice {              // byte-class compressed Aho-Corasick DFA
-    const uint8_t *cls;        // [256]
-    const int *next;           // [nstates * ncls]
-    const int *out;            // [nstates] longest pattern ending here or -1
+// Byte-class compressed Aho-Corasick DFA.  One transition entry = next state | (high bit: the next state reports a
+// pattern), 16 bits wide when the automaton has < 32768 states, else 32; the whole table is staged in shared
+// memory when it fits (north_star: "transition table held in shared memory"), else it is walked in L2.  Per text
+// byte the walk is ONE dependent look-up (the class of the next bytes does not depend on the state).
+struct AcDevice {
+    const uint8_t *cls;        // [256] byte -> class
+    const void *next;          // [nstates * ncls] u16 or u32 entries
+    const int *out;            // [nstates] longest pattern ending here or -1 (read when an entry's high bit is set)
     int ncls;
     int nstates;
+    int wide;                  // 1: 32-bit entries
 };
 // Packed 2-bit k-mer index for pattern sets over {A,C,G,T} (north_star: "packed 2-bit k-mer hash for the ACGT
 // alphabet").  Every pattern contributes its first `stride` k-mers (offsets 0..stride-1, stride = min pattern
@@ -285,6 +295,7 @@ cudaError_t launch_fields_ac(const FieldSrc &src, unsigned long long n, const Ac
 cudaError_t launch_fields_kmer(const FieldSrc &src, unsigned long long n, const KmerDevice &K, const FieldOut &O, cudaStream_t st);
 cudaError_t launch_fields_exact(const FieldSrc &src, unsigned long long n, const ExactDevice &E, const FieldOut &O, cudaStream_t st);
 cudaError_t launch_synth(const fxg_synth_spec &s, uint8_t *d_out, cudaStream_t st);
+cudaError_t scan_launch_config(const void *func, int threads, size_t smem, int dev, int *grid_cap);
 
 #define FXG_CUDA_OK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return fxg::set_cuda_error(ctx, e__, #expr); } while (0)
 

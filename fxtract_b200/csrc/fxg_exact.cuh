@@ -23,16 +23,16 @@ struct TileWords {
 
 // Key = bytes [start, start + len) of the loader's byte space; with stop_at_space it ends at the first ' ' before that
 // (the read name of a header line).  8 bytes per step: two funnel shifts by the key's byte misalignment.
+// Returns fxg_hash_bytes of the key; `keylen` = its length.
 template <class LD>
-__device__ __forceinline__ bool exact_lookup(const ExactDevice &E, const LD &ld, long long start, unsigned int len,
-                                             bool stop_at_space, int &pid)
+__device__ __forceinline__ unsigned long long exact_hash(const LD &ld, long long start, unsigned int len, bool stop_at_space,
+                                                         unsigned int &keylen)
 {
-    const long long w0 = start >> 2;
     const int sh = (int)(start & 3) * 8;
     unsigned long long h = kHashSeed;
     unsigned int used = 0;
     if (len) {
-        long long wi = w0;
+        long long wi = start >> 2;
         unsigned int g0 = ld(wi);
         for (;;) {
             const unsigned int g1 = ld(wi + 1), g2 = ld(wi + 2);
@@ -55,8 +55,31 @@ __device__ __forceinline__ bool exact_lookup(const ExactDevice &E, const LD &ld,
             wi += 2;
         }
     }
-    len = used;
-    h = fxg_hash_finish(h, len);
+    keylen = used;
+    return fxg_hash_finish(h, used);
+}
+
+// true iff the bucket chain of hash h holds its fingerprint (one memory round trip unless a bucket is full)
+__device__ __forceinline__ bool exact_fingerprint_present(const ExactDevice &E, unsigned long long h)
+{
+    unsigned int bkt = (unsigned int)h & E.mask;
+    const unsigned int fp = (unsigned int)(h >> 32) | 1u;
+    for (;;) {
+        const uint4 *B = E.bkt + 4 * (size_t)bkt;
+        const uint4 q0 = __ldg(B), q1 = __ldg(B + 1), q2 = __ldg(B + 2), q3 = __ldg(B + 3);
+        if (q0.x == fp || q0.z == fp || q1.x == fp || q1.z == fp || q2.x == fp || q2.z == fp || q3.x == fp || q3.z == fp) return true;
+        if (q3.z == 0u) return false;
+        bkt = (bkt + 1) & E.mask;
+    }
+}
+
+// table probe + verification of the key [start, start + len) whose hash is h
+template <class LD>
+__device__ __forceinline__ bool exact_probe(const ExactDevice &E, unsigned long long h, const LD &ld, long long start, unsigned int len,
+                                            int &pid)
+{
+    const long long w0 = start >> 2;
+    const int sh = (int)(start & 3) * 8;
     unsigned int bkt = (unsigned int)h & E.mask;
     const unsigned int fp = (unsigned int)(h >> 32) | 1u;
     for (;;) {
@@ -91,6 +114,15 @@ __device__ __forceinline__ bool exact_lookup(const ExactDevice &E, const LD &ld,
         if (q3.z == 0u) return false;                      // the bucket has a free slot: nothing spilled past it
         bkt = (bkt + 1) & E.mask;
     }
+}
+
+template <class LD>
+__device__ __forceinline__ bool exact_lookup(const ExactDevice &E, const LD &ld, long long start, unsigned int len,
+                                             bool stop_at_space, int &pid)
+{
+    unsigned int keylen;
+    const unsigned long long h = exact_hash(ld, start, len, stop_at_space, keylen);
+    return exact_probe(E, h, ld, start, keylen, pid);
 }
 
 // key in global memory: bytes [p, p + len) of a buffer whose last readable byte is at or after p + len - 1

@@ -79,11 +79,27 @@ __global__ void __launch_bounds__(256) fields_literal_kernel(FieldSrc src, unsig
 }
 
 // ---------------------------------------------------------------- multi: thread per field, DFA walk
-__global__ void __launch_bounds__(256) fields_ac_kernel(FieldSrc src, unsigned long long n, AcDevice A, FieldOut O)
+// ENTRY = unsigned short / unsigned int (transition entry width), SMEM = the table is staged in shared memory.
+// The field is read 8 bytes per load; per byte: class look-up (shared memory, independent of the state) and one
+// dependent transition look-up; the walk stops at the first entry whose high bit says "reports a pattern" = smallest
+// end offset, longest pattern (oracle/fxo_ac.h).
+template <typename ENTRY, bool SMEM>
+__global__ void __launch_bounds__(512) fields_ac_kernel(FieldSrc src, unsigned long long n, AcDevice A, FieldOut O)
 {
-    __shared__ uint8_t cls[256];
-    cls[threadIdx.x & 255] = A.cls[threadIdx.x & 255];
+    extern __shared__ __align__(16) unsigned char ac_smem[];
+    uint8_t *cls = ac_smem;                                                    // [256]
+    const ENTRY *next = reinterpret_cast<const ENTRY *>(A.next);
+    if (threadIdx.x < 256) cls[threadIdx.x] = A.cls[threadIdx.x];
+    if (SMEM) {
+        ENTRY *tab = reinterpret_cast<ENTRY *>(ac_smem + 256);
+        const size_t words = ((size_t)A.nstates * A.ncls * sizeof(ENTRY) + 3) / 4;
+        const unsigned int *g = reinterpret_cast<const unsigned int *>(A.next);      // allocation is padded to whole words
+        for (size_t w = threadIdx.x; w < words; w += blockDim.x) reinterpret_cast<unsigned int *>(tab)[w] = __ldg(g + w);
+        next = tab;
+    }
     __syncthreads();
+    constexpr ENTRY kFlag = (ENTRY)1 << (sizeof(ENTRY) * 8 - 1);
+    const unsigned int ncls = (unsigned int)A.ncls;
     n = src.count(n);
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     const unsigned long long nround = (n + 31) & ~31ull;      // keep whole warps in the loop for the ballot
@@ -93,13 +109,29 @@ __global__ void __launch_bounds__(256) fields_ac_kernel(FieldSrc src, unsigned l
         if (k < n) {
             const uint8_t *p; unsigned int len;
             src.get(k, p, len);
-            int s = 0;
-            pid = A.out[0];                   // empty pattern ends at offset 0
-            unsigned int i = 0;
-            while (pid < 0 && i < len) {
-                s = __ldg(&A.next[(size_t)s * A.ncls + cls[p[i]]]);
-                pid = __ldg(&A.out[s]);
-                ++i;
+            pid = __ldg(&A.out[0]);                  // the empty pattern ends at offset 0
+            if (pid < 0 && len) {
+                const uint8_t *end = p + len;
+                const uint8_t *ga = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)7);
+                unsigned int skip = (unsigned int)((uintptr_t)p & 7);        // bytes of the first word in front of the field
+                unsigned int s = 0;
+                bool found = false;
+                while (ga < end && !found) {
+                    unsigned long long w = __ldg(reinterpret_cast<const unsigned long long *>(ga)) >> (8 * skip);
+                    const unsigned int avail = 8 - skip;
+                    const unsigned int left = (unsigned int)(end - (ga + skip));
+                    const unsigned int cnt = left < avail ? left : avail;
+                    for (unsigned int b = 0; b < cnt; ++b) {
+                        const unsigned int c = cls[(unsigned int)w & 0xffu];
+                        w >>= 8;
+                        const ENTRY t = SMEM ? next[s * ncls + c] : __ldg(&next[(size_t)s * ncls + c]);
+                        s = (unsigned int)(t & (ENTRY)~kFlag);
+                        if (t & kFlag) { found = true; break; }
+                    }
+                    ga += 8;
+                    skip = 0;
+                }
+                if (found) pid = __ldg(&A.out[s]);
             }
             hit = pid >= 0;
         }
@@ -288,11 +320,29 @@ cudaError_t launch_fields_literal(const FieldSrc &src, unsigned long long n, con
     fields_literal_kernel<<<grid_for(n, 8), 256, 0, st>>>(src, n, L, O);
     return cudaGetLastError();
 }
+template <typename ENTRY, bool SMEM>
+static cudaError_t launch_fields_ac_t(const FieldSrc &src, unsigned long long n, const AcDevice &A, const FieldOut &O, cudaStream_t st, size_t smem)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int cap = 0;
+    cudaError_t e = scan_launch_config((const void *)fields_ac_kernel<ENTRY, SMEM>, 512, smem, dev, &cap);
+    if (e != cudaSuccess) return e;
+    unsigned long long b = (n + 511) / 512;
+    if (SMEM && b > (unsigned long long)cap) b = (unsigned long long)cap;       // persistent CTAs: the table is staged once per CTA
+    if (!SMEM && b > 148ull * 16) b = 148ull * 16;
+    if (b == 0) b = 1;
+    fields_ac_kernel<ENTRY, SMEM><<<(unsigned int)b, 512, smem, st>>>(src, n, A, O);
+    return cudaGetLastError();
+}
 cudaError_t launch_fields_ac(const FieldSrc &src, unsigned long long n, const AcDevice &A, const FieldOut &O, cudaStream_t st)
 {
     if (n == 0) return cudaSuccess;
-    fields_ac_kernel<<<grid_for(n, 256), 256, 0, st>>>(src, n, A, O);
-    return cudaGetLastError();
+    const size_t table = (size_t)A.nstates * A.ncls * (A.wide ? 4 : 2);
+    const bool smem = table + 256 + 16 <= 200u * 1024u;
+    const size_t bytes = 256 + (smem ? ((table + 15) & ~(size_t)15) : 0);
+    if (A.wide) return smem ? launch_fields_ac_t<unsigned int, true>(src, n, A, O, st, bytes) : launch_fields_ac_t<unsigned int, false>(src, n, A, O, st, bytes);
+    return smem ? launch_fields_ac_t<unsigned short, true>(src, n, A, O, st, bytes) : launch_fields_ac_t<unsigned short, false>(src, n, A, O, st, bytes);
 }
 template <int S> static cudaError_t launch_fields_kmer_s(const FieldSrc &src, unsigned long long n, const KmerDevice &K,
                                                          const FieldOut &O, cudaStream_t st)

@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
     if (t + 1 == P.ntiles && ((lb + ti.total) >> 2) > P.rec_cap) viol |= FXG_V_DENSE_LINES;   // more records than the per-record buffers hold
     if (viol) { atomicOr(&P.ctr->violation, viol); atomicMin(&P.ctr->first_bad, base); }
 
-    // exact mode: the scan kernel looks up the lines that lie wholly inside a tile; the line that ends at this
+    // exact mode: exact_resolve_kernel looks up the lines that lie wholly inside a tile; the line that ends at this
     // tile's first '\n' (it starts in an earlier tile, or exactly at the tile's first byte) is done here
     if (P.mode == kModeExact && n_tab > 0 && r == target_role(P.target)) {
         const long long ls = V.prev_nl(t, 1) + 1;
@@ -245,6 +245,105 @@ __global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
     }
 }
 
+// ---------------------------------------------------------------- second half of the fused matchers
+// The scan kernel does everything that reads the staged tile (hashing a key, packing and filtering windows) and
+// leaves one small entry per look-up; the look-ups themselves -- dependent global loads into tables that do not fit
+// shared memory -- run here, one thread per entry over the whole batch, where tens of thousands of them are in
+// flight at once instead of stalling a tile of the lock-step scan.
+//
+// exact mode: one WARP per tile, one lane per line of the target's role; key hash from keyhash[], bucket probe,
+// and for a fingerprint match the key compared word by word against the batch text (replaces manager.find(*data),
+// main.cpp:315).  Line 0 of a tile (it may start in an earlier tile) is done by tile_finalize_kernel.
+__global__ void __launch_bounds__(256) exact_resolve_kernel(const ScanParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (t >= P.ntiles) return;
+    const TileView V(P);
+    const unsigned long long lb = V.lbase(t);
+    const int n_tab = V.lines(t);
+    const int first = (target_role(P.target) - (int)(lb & 3ull)) & 3;
+    const unsigned long long *kh = P.keyhash + t * (unsigned long long)(P.nl_stride / 4);
+    unsigned int fresh = 0;
+    for (int i = first + 4 * lane; i < n_tab; i += 128) {
+        if (i < 1) continue;
+        const unsigned long long h = __ldg(kh + (i >> 2));
+        if (!exact_fingerprint_present(P.exact, h)) continue;
+        if (!exact_line_global(P, V.nl(t, i - 1) + 1, V.nl(t, i))) continue;
+        const unsigned long long rec = (lb + (unsigned long long)i) >> 2;
+        if (rec >= P.rec_cap) continue;
+        const unsigned int bit = 1u << (rec & 31);
+        if (!(atomicOr(&P.hitbits[rec >> 5], bit) & bit)) ++fresh;
+    }
+    fresh = __reduce_add_sync(0xffffffffu, fresh);
+    if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
+}
+
+// k-mer mode: one WARP per tile, one lane per candidate {window key, tile-relative offset of the window}: table
+// bucket, every pattern record that holds the window at one of its first S offsets compared with the batch text,
+// the occurrence's line found in the tile's '\n' table, kept if that line has the target's role.
+__global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (t >= P.ntiles) return;
+    const unsigned int nc = P.tile_ncand[t];
+    if (!nc) return;
+    const KmerTile &K = P.kmer;
+    const TileView V(P);
+    const unsigned long long lb = V.lbase(t);
+    const int n_tab = V.lines(t);
+    const int trole = target_role(P.target);
+    const unsigned long long base = t * (unsigned long long)P.tile_bytes;
+    const unsigned short *nl = P.tile_nl + t * (unsigned long long)P.nl_stride;
+    const uint2 *list = P.cand + t * (unsigned long long)P.cand_cap;
+    unsigned int fresh = 0;
+    for (unsigned int c = lane; c < nc; c += 32) {
+        const uint2 cd = __ldg(list + c);
+        const unsigned int key = cd.x;
+        const int win_rel = (int)cd.y;
+        bool found = false;
+        unsigned int bkt = kmer_tile_bucket(key, K.ht_mask);
+        for (;;) {
+            const uint4 kk = __ldg(K.ht + 2 * (size_t)bkt), vv = __ldg(K.ht + 2 * (size_t)bkt + 1);
+            const unsigned int keys[4] = {kk.x, kk.y, kk.z, kk.w}, vals[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const unsigned int v = vals[e];
+                if (found || !v || keys[e] != key) continue;
+                const unsigned int o = (v - 1u) & 127u;
+                const uint4 *rec = K.rec + ((v - 1u) >> 7);
+                const unsigned int m = __ldg(reinterpret_cast<const unsigned int *>(rec));
+                const long long p = (long long)base + win_rel - (long long)o;
+                if (p < 0 || (unsigned long long)p + m > P.nbytes) continue;
+                const unsigned char *pb = reinterpret_cast<const unsigned char *>(rec) + 8;
+                bool eq = true;
+                for (unsigned int i = 0; i < m; ++i)
+                    if (P.buf[p + i] != __ldg(pb + i)) { eq = false; break; }
+                found = eq;
+            }
+            if (found || vv.w == 0u) break;                  // the bucket has a free slot: nothing spilled past it
+            bkt = (bkt + 1) & K.ht_mask;
+        }
+        if (!found) continue;
+        // local line of the occurrence = number of '\n' before the window (a pattern holds no '\n', so all of it
+        // lies on the line of its window)
+        int lo = 0, hi = n_tab;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if ((int)nl[mid] < win_rel) lo = mid + 1; else hi = mid;
+        }
+        const unsigned long long line = lb + (unsigned long long)lo;
+        if ((int)(line & 3ull) != trole) continue;
+        const unsigned long long r = line >> 2;
+        if (r >= P.rec_cap) continue;
+        const unsigned int bit = 1u << (r & 31);
+        if (!(atomicOr(&P.hitbits[r >> 5], bit) & bit)) ++fresh;
+    }
+    fresh = __reduce_add_sync(0xffffffffu, fresh);
+    if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
+}
+
 // ---------------------------------------------------------------- launch configuration cache
 // cudaFuncSetAttribute + occupancy query once per (kernel, device, shared-memory size); guarded, because contexts
 // driven from different host threads share it.
@@ -302,6 +401,13 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
     if (e != cudaSuccess) return e;
     tile_finalize_kernel<<<(unsigned int)((P.ntiles + 255) / 256), 256, 0, stream>>>(P);
     if (launches) *launches += 6;
+    if (kmer) {
+        kmer_resolve_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
+        if (launches) *launches += 1;
+    } else if (P.mode == kModeExact) {
+        exact_resolve_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
+        if (launches) *launches += 1;
+    }
     if (P.fld_off) {
         tile_emit_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
         if (launches) *launches += 1;

@@ -385,8 +385,11 @@ __device__ __noinline__ void kmer_resolve(ScanSmem<G> &S, TileState &T, const un
 }
 
 // ---------------------------------------------------------------- exact mode: key of one whole line of the tile
-// Line = tile bytes [a, e).  Returns true when the target field of that line is a key of the table.
-__device__ __forceinline__ bool exact_line_tile(const ScanParams &P, const unsigned char *tb, int a, int e)
+// Line = tile bytes [a, e).  The scan kernel only HASHES the target field of its lines (shared-memory reads, no
+// dependent global load inside the lock-step tile loop) and leaves the 64-bit hashes in a per-tile list; the table
+// look-ups are done afterwards by exact_resolve_kernel with one thread per record, where their latency is hidden by
+// parallelism instead of stalling a tile.
+__device__ __forceinline__ unsigned long long exact_line_hash_tile(const ScanParams &P, const unsigned char *tb, int a, int e)
 {
     int ks = a, ke = e;
     bool stop = false;
@@ -396,11 +399,11 @@ __device__ __forceinline__ bool exact_line_tile(const ScanParams &P, const unsig
         for (int q = a + 1; q < e; ++q) if (tb[q] == ' ') { sp = q + 1; break; }
         ks = sp;
     }
-    if (ks > ke) return false;
+    if (ks > ke) ks = ke;                                                    // empty key (no match unless "" is a key)
     TileWords ld;
     ld.w = reinterpret_cast<const unsigned int *>(tb);
-    int pid;
-    return exact_lookup(P.exact, ld, (long long)ks, (unsigned int)(ke - ks), stop, pid);
+    unsigned int keylen;
+    return exact_hash(ld, (long long)ks, (unsigned int)(ke - ks), stop, keylen);
 }
 // the same over global memory: line = batch bytes [a, e)
 __device__ __forceinline__ bool exact_line_global(const ScanParams &P, long long a, long long e)
@@ -413,7 +416,7 @@ __device__ __forceinline__ bool exact_line_global(const ScanParams &P, long long
         for (long long q = a + 1; q < e; ++q) if (P.buf[q] == ' ') { sp = q + 1; break; }
         ks = sp;
     }
-    if (ks > ke) return false;
+    if (ks > ke) ks = ke;
     int pid;
     return exact_lookup_global(P.exact, P.buf + ks, (unsigned int)(ke - ks), stop, pid);
 }
@@ -449,7 +452,7 @@ __device__ __forceinline__ unsigned int class_bad(const ScanSmem<G> &S, const ui
 // buffer while the current one is processed.
 // MODE = kMode* (fxg_common.cuh).  REDO = second launch over the (normally empty) list of tiles whose locally
 // guessed line phase turned out wrong (exact mode: also the tiles without anchor): those are re-evaluated with the
-// phase-free per-line path, exact look-ups under the true phase.
+// phase-free per-line path, exact-mode hashes under the true phase.
 template <class G, int MODE, bool REDO>
 __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(const ScanParams P)
 {
@@ -462,7 +465,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     constexpr bool EXACT = MODE == kModeExact;
     constexpr int SB = KMER ? (1 << (MODE - kModeKmer)) : 16;          // probe stride (bytes == bases)
     constexpr int NPROBE = 16 / SB;
-    constexpr bool HITS = MODE != kModeIndex && (!REDO || EXACT);     // this launch produces line-hit words
+    constexpr bool HITS = MODE != kModeIndex && !EXACT && !REDO;      // this launch produces line-hit words
     typedef ScanSmem<G> Smem;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &S = *reinterpret_cast<Smem *>(smem_raw);
@@ -720,7 +723,6 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
             const int role = warp & 3;                        // 0 header, 1 sequence, 2 plus, 3 quality
             const int first = (role - r) & 3;                 // smallest local line index with that role
             unsigned int viol = 0;
-            bool any_hit = false;
             for (int i = first + 4 * ((warp >> 2) * 32 + lane); i <= n_tab; i += 4 * (kWarps / 4) * 32) {
                 const int a = i >= 1 ? (int)S.nlpos[i - 1] + 1 : 0;
                 const int e = i < n_tab ? (int)S.nlpos[i] : kTileBytes;
@@ -741,15 +743,12 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                         else if (i >= 3 && e - a != (int)S.nlpos[i - 2] - (int)S.nlpos[i - 3] - 1) viol |= FXG_V_QUAL_LEN;
                     }
                 }
-                // exact mode: the warps of the target's role look their (whole) lines up; the line that straddles
-                // the tile's left edge is left to tile_finalize_kernel
-                if (EXACT && role == trole && whole && exact_line_tile(P, tb, a, e)) {
-                    atomicOr(&S.linehit[i >> 5], 1u << (i & 31));
-                    any_hit = true;
-                }
+                // exact mode: the warps of the target's role hash their (whole) lines; the line that straddles the
+                // tile's left edge is left to tile_finalize_kernel
+                if (EXACT && role == trole && whole)
+                    P.keyhash[t * (unsigned long long)(kMaxTileLines / 4) + (unsigned int)(i >> 2)] = exact_line_hash_tile(P, tb, a, e);
             }
             viol = __reduce_or_sync(0xffffffffu, viol);
-            if (EXACT && __any_sync(0xffffffffu, any_hit)) viol |= kTileHasHit;
             if (lane == 0 && viol) atomicOr(&T.viol, viol);
         } else {
             // generic path (no "+" line in the tile, or REDO): one thread per line, flags OR-ed per
@@ -771,18 +770,14 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                 if (f) atomicOr(&T.cls[n_tab & 3], f);
             }
             if (EXACT && REDO) {
-                // the true phase is known by now (prefix kernels ran before this launch): look the whole lines of
-                // the target's role up; line 0 is left to tile_finalize_kernel like in the first launch
+                // the true phase is known by now (prefix kernels ran before this launch): hash the whole lines of
+                // the target's role; line 0 is left to tile_finalize_kernel like in the first launch
                 const int r = (int)((P.lbase[t] + P.bsum[t / kPrefixSpan]) & 3ull);
-                bool any_hit = false;
                 for (int i = 1 + tid; i < n_tab; i += kThreads) {
                     if (((i + r) & 3) != trole) continue;
-                    if (exact_line_tile(P, tb, (int)S.nlpos[i - 1] + 1, (int)S.nlpos[i])) {
-                        atomicOr(&S.linehit[i >> 5], 1u << (i & 31));
-                        any_hit = true;
-                    }
+                    P.keyhash[t * (unsigned long long)(kMaxTileLines / 4) + (unsigned int)(i >> 2)] =
+                        exact_line_hash_tile(P, tb, (int)S.nlpos[i - 1] + 1, (int)S.nlpos[i]);
                 }
-                if (any_hit) atomicOr(&T.viol, kTileHasHit);
             }
         }
 
@@ -816,8 +811,25 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
             }
         }
         if (KMER && !REDO) {
-            // every warp resolves the filter hits of its own segment (queue written by this warp in step 1)
+            // every warp moves the filter hits of its own segment (queue written by this warp in step 1) into the
+            // tile's candidate list in global memory as {window key, tile-relative offset}; kmer_resolve_kernel
+            // looks them up afterwards, one thread per candidate.  Only what does not fit the list is resolved here.
             __syncwarp();
+            unsigned int mine = 0;
+            for (unsigned int q = lane; q < kqn; q += 32) mine += __popc((unsigned int)my_kq[q] & 0xffu);
+            unsigned int inc = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            const unsigned int wtotal = __shfl_sync(0xffffffffu, inc, 31);
+            unsigned int wbase = 0;
+            if (lane == 0 && wtotal) wbase = atomicAdd(&T.n_cand, wtotal);
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            unsigned int slot = wbase + inc - mine;
+            const unsigned int cap = (unsigned int)P.cand_cap;
+            uint2 *list = P.cand + t * (unsigned long long)cap;
             for (unsigned int q = lane; q < kqn; q += 32) {
                 const unsigned int e = my_kq[q];
                 const int ce = warp * kWarpChunks + (int)(e >> 8);    // chunk the windows start in
@@ -829,7 +841,9 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                     bits &= ~(1u << bi);
                     const int s = (NPROBE - 1 - bi) * SB;             // first probe of a chunk ends up in the highest bit
                     const unsigned int key = (s ? __funnelshift_r(p0, p1, 2 * s) : p0) & kmask;
-                    kmer_resolve(S, T, tb, P, base, n_tab, ce * 16 + s, key);
+                    if (slot < cap) list[slot] = make_uint2(key, (unsigned int)(ce * 16 + s));
+                    else kmer_resolve(S, T, tb, P, base, n_tab, ce * 16 + s, key);
+                    ++slot;
                 }
             }
         }
@@ -852,8 +866,9 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                 }
             }
             if (tid == 0) {
-                // a REDO launch that re-checks structure only keeps the hit words of the first launch, and their flag
-                const unsigned int kept = (REDO && !EXACT) ? (P.info[t].viol & kTileHasHit) : 0u;
+                if (KMER && !REDO) P.tile_ncand[t] = T.n_cand < (unsigned int)P.cand_cap ? T.n_cand : (unsigned int)P.cand_cap;
+                // the REDO launch re-checks structure only: the hit words of the first launch stand, and so does their flag
+                const unsigned int kept = REDO ? (P.info[t].viol & kTileHasHit) : 0u;
                 const TileInfo ti = {total, kept | T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),
                                      {(unsigned short)T.cls[0], (unsigned short)T.cls[1], (unsigned short)T.cls[2], (unsigned short)T.cls[3]}};
                 P.info[t] = ti;
