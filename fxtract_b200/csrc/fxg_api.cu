@@ -53,6 +53,7 @@ struct fxg_ctx {
     bool two_stage = false;             // FXG_TWO_STAGE=1: multi / exact keep the index pass + field matcher (A/B measurements)
     cudaStream_t copy_stream = nullptr; // H2D of batch k+1 overlaps the kernels of batch k
     uint4 *d_bkt = nullptr; unsigned int exact_mask = 0;                          // bucketed exact table
+    unsigned int *d_exact_pre = nullptr; unsigned int exact_pre_mask = 0;         // its Bloom pre-filter
     unsigned long long *d_keyhash = nullptr;                                      // exact mode: key hash per target line (scan -> resolve)
     uint2 *d_cand = nullptr; unsigned int *d_tile_ncand = nullptr;                // k-mer mode: filter hits per tile (scan -> resolve)
     unsigned long long *d_key_words = nullptr;
@@ -283,51 +284,39 @@ static int build_kmer(fxg_ctx *ctx)
 }
 
 // ---------------------------------------------------------------- window index of the fused scan matcher (host build)
-// Usable when every pattern holds a run of >= 12 bases {A,C,G,T} (fxg_common.cuh: KmerTile); bytes outside such a
-// run (an N, an IUPAC code) are fine -- they are compared when a candidate is verified.  Probe stride S (16, 8, 4
-// or 2 bytes) and window length k <= 16 with k + S - 1 <= the shortest run: every pattern contributes the S windows
-// at the first S offsets of its run, so every occurrence holds a window at a probed text position.  The largest S
-// is taken whose k keeps the share of text windows that hit an index entry by chance (entries / 4^k) under 1/64 --
-// those cost a table look-up and a byte comparison each.
+// Usable when no pattern holds a '\n' and the shortest one is long enough for a probe stride S of 16, 8 or 4 bytes
+// with a window of k <= 16 bytes, k + S - 1 <= shortest pattern (fxg_common.cuh: KmerTile): every pattern contributes
+// the S windows at its first S offsets, so every occurrence holds a window at a probed text position.  The largest
+// S is taken whose k keeps the share of text windows that equal an index entry by chance (entries / 4^k for a
+// four-letter text) under 1/64 -- those cost a table look-up and a byte comparison each.  Any byte values: the
+// windows are hashed as raw bytes.
 static int build_kmer_tile(fxg_ctx *ctx)
 {
     ctx->kt_ok = false;
     const uint32_t n = ctx->npat;
     if (n == 0 || n >= (1u << 24)) return FXG_OK;
-    std::vector<uint32_t> run_start(n, 0);
-    uint32_t minrun = 0xffffffffu;
-    for (uint32_t i = 0; i < n; ++i) {
-        // longest run of bases of pattern i
-        uint32_t best = 0, best_at = 0, cur = 0;
-        for (uint32_t j = ctx->off[i]; j < ctx->off[i + 1]; ++j) {
-            cur = fxg_is_acgt(ctx->blob[j]) ? cur + 1 : 0;
-            if (cur > best) { best = cur; best_at = j + 1 - cur - ctx->off[i]; }
-        }
-        run_start[i] = best_at;
-        if (best < minrun) minrun = best;
-    }
-    if (minrun < 12) return FXG_OK;
+    uint32_t minlen = 0xffffffffu;
+    for (uint32_t i = 0; i < n; ++i) minlen = std::min(minlen, ctx->off[i + 1] - ctx->off[i]);
+    if (!ctx->blob.empty() && memchr(ctx->blob.data(), '\n', ctx->blob.size())) return FXG_OK;
     int S = 0, k = 0;
-    for (int s = 16; s >= 2; s >>= 1) {
-        if ((int)minrun - s + 1 < 11) continue;
-        const int kk = std::min(16, (int)minrun - s + 1);
+    for (int s = 16; s >= 4; s >>= 1) {
+        if ((int)minlen - s + 1 < 11) continue;
+        const int kk = std::min(16, (int)minlen - s + 1);
         const double space = kk >= 16 ? 4294967296.0 : (double)(1ull << (2 * kk));
         if ((double)n * s / space > 1.0 / 64) continue;
         S = s; k = kk;
         break;
     }
     if (!S) return FXG_OK;
-    for (uint32_t i = 0; i < n; ++i) if (run_start[i] + (uint32_t)S > 128u) return FXG_OK;     // window offsets are stored in 7 bits
-    const unsigned int kmask = k == 16 ? 0xffffffffu : ((1u << (2 * k)) - 1u);
     const size_t entries = (size_t)n * (size_t)S;
+    if (entries > 400000) return FXG_OK;              // the 128 KiB filter would pass more than ~ 1 window in 6
     size_t nbuckets = 16;                             // 4 entries per bucket, <= 1 on average
     while (nbuckets < entries) nbuckets <<= 1;
-    if (nbuckets > ((size_t)1 << 28)) return FXG_OK;
-    const int flw = entries <= 16384 ? 12 : 15;       // 16 KiB filter (2 CTAs / SM) or 128 KiB (1 CTA / SM); 2 bits per entry
+    const int flw = entries <= 32768 ? 13 : 15;       // 32 KiB filter (2 CTAs / SM) or 128 KiB (1 CTA / SM); 4 bits per entry
     std::vector<unsigned int> filter((size_t)1 << flw, 0u), ht(nbuckets * 8, 0u);
     std::vector<unsigned char> fill(nbuckets, 0);
     const unsigned int mask = (unsigned int)(nbuckets - 1);
-    // pattern records {length, id, bytes}, 16-byte aligned, 48 bytes of slack at the end (the verifier fetches 3 x 16)
+    // pattern records {length, id, bytes}, 16-byte aligned
     std::vector<unsigned int> rec;
     std::vector<unsigned int> rec_at(n, 0);
     for (uint32_t i = 0; i < n; ++i) {
@@ -346,16 +335,15 @@ static int build_kmer_tile(fxg_ctx *ctx)
     if (rec.size() / 4 >= ((size_t)1 << 25)) return FXG_OK;          // record offsets are stored in 25 bits
     for (uint32_t i = 0; i < n; ++i) {
         const uint8_t *p = ctx->blob.data() + ctx->off[i];
-        for (int j = 0; j < S; ++j) {
-            const unsigned int o = run_start[i] + (unsigned int)j;      // offset of the window inside the pattern
-            unsigned int key = 0;
-            for (int b = 0; b < k; ++b) key |= fxg_base_code(p[o + b]) << (2 * b);
-            key &= kmask;
-            filter[kmer_tile_filter_word(key, flw)] |= kmer_tile_filter_mask(key);
-            unsigned int bkt = kmer_tile_bucket(key, mask);
+        for (int o = 0; o < S; ++o) {                                 // offset of the window inside the pattern
+            unsigned int w[4] = {0u, 0u, 0u, 0u};
+            for (int b = 0; b < k; ++b) w[b >> 2] |= (unsigned int)p[o + b] << (8 * (b & 3));
+            const unsigned int h = window_hash(w[0], w[1], w[2], w[3]);
+            filter[kmer_tile_filter_word(h, flw)] |= kmer_tile_filter_mask(h);
+            unsigned int bkt = kmer_tile_bucket(h, mask);
             while (fill[bkt] == 4) bkt = (bkt + 1) & mask;
             const int e = fill[bkt]++;
-            ht[(size_t)bkt * 8 + e] = key; ht[(size_t)bkt * 8 + 4 + e] = ((rec_at[i] << 7) | o) + 1u;
+            ht[(size_t)bkt * 8 + e] = h; ht[(size_t)bkt * 8 + 4 + e] = ((rec_at[i] << 7) | (unsigned int)o) + 1u;
         }
     }
     cudaError_t e;
@@ -367,7 +355,9 @@ static int build_kmer_tile(fxg_ctx *ctx)
     if ((e = cudaMemcpy(ctx->d_ktrec, rec.data(), rec.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload pattern records");
     KmerTile &K = ctx->kt;
     K.filter = ctx->d_ktfilter; K.ht = ctx->d_ktht; K.rec = ctx->d_ktrec;
-    K.ht_mask = mask; K.kmask = kmask; K.k = k; K.stride = S; K.filter_log2_words = flw;
+    K.ht_mask = mask; K.k = k; K.stride = S; K.filter_log2_words = flw;
+    K.mask2 = k >= 12 ? 0xffffffffu : ((1u << (8 * (k - 8))) - 1u);
+    K.mask3 = k >= 16 ? 0xffffffffu : (k > 12 ? ((1u << (8 * (k - 12))) - 1u) : 0u);
     ctx->kt_ok = true;
     return FXG_OK;
 }
@@ -397,8 +387,13 @@ static int build_exact(fxg_ctx *ctx)
     std::vector<unsigned int> bk(nbuckets * 16, 0u);  // per bucket: {fp, off} x 8
     std::vector<unsigned char> fill(nbuckets, 0);
     const unsigned int mask = (unsigned int)(nbuckets - 1);
+    size_t pre_words = 64;                            // >= 16 bits per key
+    while (pre_words * 2 < (size_t)n) pre_words <<= 1;
+    std::vector<unsigned int> pre(pre_words, 0u);
+    const unsigned int pre_mask = (unsigned int)(pre_words - 1);
     for (uint32_t i = 0; i < n; ++i) {
         const unsigned long long h = fxg_hash_bytes(ctx->blob.data() + ctx->off[i], ctx->off[i + 1] - ctx->off[i]);
+        pre[exact_pre_word(h, pre_mask)] |= exact_pre_mask(h);
         unsigned int bkt = (unsigned int)h & mask;
         while (fill[bkt] == 8) bkt = (bkt + 1) & mask;
         const int e = fill[bkt]++;
@@ -408,6 +403,9 @@ static int build_exact(fxg_ctx *ctx)
     if ((e = dev_realloc(ctx->d_bkt, nbuckets * 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc table");
     if ((e = cudaMemcpy(ctx->d_bkt, bk.data(), bk.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload table");
     ctx->exact_mask = mask;
+    if ((e = dev_realloc(ctx->d_exact_pre, pre.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key pre-filter");
+    if ((e = cudaMemcpy(ctx->d_exact_pre, pre.data(), pre.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload key pre-filter");
+    ctx->exact_pre_mask = pre_mask;
     if ((e = dev_realloc(ctx->d_key_words, kw.size())) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key words");
     if ((e = cudaMemcpy(ctx->d_key_words, kw.data(), kw.size() * 8, cudaMemcpyHostToDevice)) != cudaSuccess) return set_cuda_error(ctx, e, "upload key words");
     return FXG_OK;
@@ -431,7 +429,7 @@ static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
     if ((e = dev_realloc(ctx->d_lbase, ntiles + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile prefix");
     if ((e = dev_realloc(ctx->d_bsum, ntiles / 4096 + 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc span prefix");
     if ((e = dev_realloc(ctx->d_redo, ntiles + 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc redo list");
-    if (ctx->scan_mode != kModeIndex &&
+    if (mode_is_literal(ctx->scan_mode) &&
         (e = dev_realloc(ctx->d_tile_hit, ntiles * (size_t)ctx->hit_words)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc tile line hits");
     if ((e = dev_realloc(ctx->d_hitbits, words + 4)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc hit bitset");
     if (ctx->scan_mode == kModeExact &&
@@ -515,18 +513,19 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     P.info = ctx->d_info; P.tile_nl = ctx->d_tile_nl;
     P.tile_hit = ctx->d_tile_hit; P.lbase = ctx->d_lbase; P.bsum = ctx->d_bsum; P.ctr = ctx->d_ctr; P.hitbits = ctx->d_hitbits;
     P.rec_cap = rec_cap; P.one = 1;
+    { const char *h = getenv("FXG_L2_HINT"); P.l2_evict_first = !(h && !strcmp(h, "0")); }
     P.redo_list = ctx->d_redo; P.redo_count = ctx->d_redo + ctx->ntiles_cap;
     P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     P.mode = ctx->scan_mode;
-    P.match_enabled = P.mode != kModeIndex;
+    P.match_enabled = mode_is_literal(P.mode);
     P.lit_unit = ctx->h_lit.unit;
     const bool field_stage = P.mode == kModeIndex && !literal;
     if (field_stage) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
     P.header_whole = ctx->cfg.mode == FXG_MODE_EXACT && ctx->cfg.target == FXG_TARGET_NAME;
     if (mode_is_kmer(P.mode)) { P.kmer = ctx->kt; P.cand = ctx->d_cand; P.tile_ncand = ctx->d_tile_ncand; P.cand_cap = kKmerCandCap; }
     if (P.mode == kModeExact) {
-        P.exact = ExactDevice{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
+        P.exact = ExactDevice{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask, ctx->d_exact_pre, ctx->exact_pre_mask};
         P.keyhash = ctx->d_keyhash;
         P.redo_unanchored = 1;
     }
@@ -545,7 +544,7 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates, ctx->ac_wide};
             FXG_CUDA_OK(launch_fields_ac(src, rec_cap, A, O, st));
         } else {
-            ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
+            ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask, ctx->d_exact_pre, ctx->exact_pre_mask};
             FXG_CUDA_OK(launch_fields_exact(src, rec_cap, E, O, st));
         }
         ctx->last_launches += 1;
@@ -672,7 +671,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h2d_done) cudaEventDestroy(s.h2d_done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_keyhash, ctx->d_cand, ctx->d_tile_ncand, ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
+    void *dev[] = {ctx->d_exact_pre, ctx->d_keyhash, ctx->d_cand, ctx->d_tile_ncand, ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
                    ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
@@ -868,7 +867,7 @@ extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *of
             AcDevice A{ctx->d_cls, ctx->d_next, ctx->d_out, ctx->ac_ncls, ctx->ac_nstates, ctx->ac_wide};
             FXG_CUDA_OK(launch_fields_ac(src, nrec, A, O, st));
         } else {
-            ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask};
+            ExactDevice E{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask, ctx->d_exact_pre, ctx->exact_pre_mask};
             FXG_CUDA_OK(launch_fields_exact(src, nrec, E, O, st));
         }
         ctx->last_launches = 1;

@@ -14,8 +14,8 @@ int set_cuda_error(fxg_ctx *ctx, cudaError_t e, const char *what);
 // ---------------------------------------------------------------- geometry
 // The scan kernel is compiled for two tile geometries (template parameter of scan_tiles_kernel):
 //   G24  24 KiB tiles, 12 warps, 3 CTAs / SM   literal, exact and index-only passes
-//   G32  32 KiB tiles, 16 warps, 2 CTAs / SM   fused k-mer matcher (room for its filter in shared memory;
-//                                              1 CTA / SM when the pattern set needs the 128 KiB filter)
+//   G32  32 KiB tiles, 16 warps, 2 CTAs / SM   fused window matcher with a 32 KiB filter in shared memory
+//   G32W 32 KiB tiles, 32 warps, 1 CTA / SM    ... with the 128 KiB filter (large pattern sets)
 // Every warp owns a contiguous 2 KiB segment of its tile in both.  Kernels downstream of the scan (prefix,
 // finalize, compaction) read the geometry of the batch from ScanParams at run time.
 template <int TILE_BYTES, int THREADS, int MIN_CTAS> struct Geom {
@@ -36,8 +36,9 @@ template <int TILE_BYTES, int THREADS, int MIN_CTAS> struct Geom {
 };
 typedef Geom<24576, 384, 3> G24;
 typedef Geom<32768, 512, 2> G32;
+typedef Geom<32768, 1024, 1> G32W;
 constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
-constexpr int kKmerCandCap = 1024;             // k-mer mode: filter hits listed per tile for kmer_resolve_kernel
+constexpr int kKmerCandCap = 512;              // window matcher: filter hits listed per tile for kmer_resolve_kernel
 
 // ---------------------------------------------------------------- per-tile results
 // The scan kernel has no cross-tile dependency: every tile publishes its '\n' count, its
@@ -91,45 +92,49 @@ constexpr int kModeIndex = 0;        // record index + canonical predicate only 
 constexpr int kModeLitSmall = 1;     // literal, patterns shorter than 15 bytes: aligned units of 4 / 2 / 1 bytes
 constexpr int kModeLit8 = 8;         // literal, aligned 8-byte-unit fingerprints (two multipliers)
 constexpr int kModeLit9 = 9;         // ... first multiplier 1
-constexpr int kModeKmer = 16;        // + log2(probe stride): 17 (S=2), 18 (S=4), 19 (S=8), 20 (S=16): fused packed k-mer matcher
+constexpr int kModeKmer = 16;        // + log2(probe stride): 18 (S=4), 19 (S=8), 20 (S=16): fused window matcher (multi-pattern)
 constexpr int kModeExact = 30;       // fused whole-field hash look-up (FileManager::find)
-__host__ __device__ constexpr bool mode_is_kmer(int m) { return m >= 17 && m <= 20; }
+__host__ __device__ constexpr bool mode_is_kmer(int m) { return m >= 18 && m <= 20; }
 __host__ __device__ constexpr bool mode_is_literal(int m) { return m == 1 || m == 8 || m == 9; }
 
-// Fused multi-pattern matcher for pattern sets over {A,C,G,T} (north_star: "packed 2-bit k-mer hash for the ACGT
-// alphabet ... warp-cooperative scan over coalesced 16-byte loads with overlap handling at chunk edges").
-// Position-centric: every 16-byte chunk of the staged tile is packed to 32 bits (2 bits per byte), a window of k <= 16
-// bases that starts at a byte offset == 0 (mod S) is the funnel shift of two neighbouring chunk words (the neighbour
-// comes from the next lane by shuffle), and is looked up in a hashed filter in shared memory (two bits of one word).  Every pattern
-// contributes its first S windows (offsets 0..S-1, k + S - 1 <= shortest pattern), so each occurrence contains one
-// probed window.  Filter hits are queued per warp and resolved after the newline table exists: open-addressing table
-// (L2) -> byte-wise verification against the pattern -> "local line i has a match" bit.  No false positives, no
-// false negatives; bytes that are not bases only make keys that no pattern has.
+// Fused multi-pattern matcher (replaces ssearch_scan, main.cpp:406,426, on the raw path; north_star: "warp-cooperative
+// scan over coalesced 16-byte loads with overlap handling at chunk edges").  Position-centric: every lane looks at
+// the windows of k <= 16 BYTES that start at byte 0, S, 2S, ... of its 16-byte chunk of the staged tile (S = 16, 8 or
+// 4; a window that runs past the chunk takes its tail from the head of the next chunk, the last chunk of a tile from
+// the 16 bytes staged behind it).  Every pattern contributes the S windows at its first S offsets and k + S - 1 <=
+// the shortest pattern, so every occurrence holds a window at a probed text position.  A window is hashed as four
+// little-endian words, one multiply-add each (window_hash); the hash selects one word of a blocked Bloom filter in
+// shared memory and four bits in it.  Filter hits go to a per-tile list in global memory as {hash, tile-relative
+// offset}; kmer_resolve_kernel looks them up afterwards (bucketed table in L2 -> pattern record -> byte-wise
+// comparison with the text), one thread per candidate.  No false positives, no false negatives, any alphabet.
 struct KmerTile {
     const unsigned int *filter;            // [1 << filter_log2_words] device copy, staged into shared memory per CTA
-    // bucketed table: bucket b = 32 bytes (one L2 sector) = 4 keys (uint4 at ht[2b]) + 4 values (uint4 at ht[2b+1]);
-    // value 0 = empty, else ((record offset / 16 << 7) | window offset in the pattern) + 1; slots fill in order, a full bucket spills into the
-    // next one.  A look-up is ONE dependent memory round trip unless its bucket is full (~2 % at <= 1 entry per
-    // bucket): the drain of a tile waits for the slowest lane, so the chain length is what matters.
+    // bucketed table: bucket b = 32 bytes (one L2 sector) = 4 window hashes (uint4 at ht[2b]) + 4 values (uint4 at
+    // ht[2b+1]); value 0 = empty, else ((record offset / 16 << 7) | window offset in the pattern) + 1; slots fill in
+    // order, a full bucket spills into the next one.
     const uint4 *ht;                       // [2 * nbuckets]
-    // pattern records, 16-byte aligned: {length u32, pattern id u32, bytes ...}; a value of the table holds the
-    // record's offset in 16-byte units, so a window hit is verified after ONE more round trip
+    // pattern records, 16-byte aligned: {length u32, pattern id u32, bytes ...}
     const uint4 *rec;
     unsigned int ht_mask;                  // nbuckets - 1
-    unsigned int kmask;                    // (1 << 2k) - 1
-    int k, stride;                         // stride in {2, 4, 8, 16}
-    int filter_log2_words;                 // 12 (16 KiB, 2 CTAs / SM) or 15 (128 KiB, 1 CTA / SM)
+    unsigned int mask2, mask3;             // bytes of window words 2 and 3 that belong to the window (k = 9 .. 16)
+    int k, stride;                         // stride in {4, 8, 16}
+    int filter_log2_words;                 // 13 (32 KiB, 2 CTAs / SM) or 15 (128 KiB, 1 CTA of 32 warps / SM)
 };
-// window key of bases b[0..k): base i in bits 2i, 2i+1 (code = (byte >> 1) & 3); identical on host and device
-constexpr unsigned int kKmerHashMul = 0x9E3779B1u;
-__host__ __device__ inline unsigned int kmer_tile_filter_word(unsigned int key, int log2_words) { return (key * kKmerHashMul) >> (32 - log2_words); }
-// two bits of one filter word per key: 31 - (h & 31) and 31 - ((h >> 5) & 31)
-__host__ __device__ inline unsigned int kmer_tile_filter_mask(unsigned int key)
+// hash of a window given as four little-endian words (bytes past the window masked off); identical on host and device
+constexpr unsigned int kWinMul0 = 0x9E3779B1u, kWinMul1 = 0x85EBCA77u, kWinMul2 = 0xC2B2AE3Du, kWinMul3 = 0x27D4EB2Fu;
+__host__ __device__ inline unsigned int window_hash(unsigned int w0, unsigned int w1, unsigned int w2, unsigned int w3)
 {
-    const unsigned int h = key * kKmerHashMul;
-    return (1u << (31u - (h & 31u))) | (1u << (31u - ((h >> 5) & 31u)));
+    return w0 * kWinMul0 + w1 * kWinMul1 + w2 * kWinMul2 + w3 * kWinMul3;
 }
-__host__ __device__ inline unsigned int kmer_tile_bucket(unsigned int key, unsigned int mask) { return ((key * kKmerHashMul) >> 7) & mask; }
+__host__ __device__ inline unsigned int kmer_tile_filter_word(unsigned int h, int log2_words) { return h >> (32 - log2_words); }
+// four bits of one filter word per window: {r, r + 16} and {s, s + 8} (mod 32), r = h & 31, s = (h >> 5) & 31
+__host__ __device__ inline unsigned int kmer_tile_filter_mask(unsigned int h)
+{
+    const unsigned int r = h & 31u, s = (h >> 5) & 31u;
+    return ((0x00010001u << r) | (0x00010001u >> ((32u - r) & 31u))) | ((0x00000101u << s) | (0x00000101u >> ((32u - s) & 31u)));
+}
+__host__ __device__ inline unsigned int kmer_tile_bucket(unsigned int h, unsigned int mask) { return ((h * 0x9E3779B1u) >> 9) & mask; }
+constexpr unsigned int kCandOverflow = 0x80000000u;   // tile_ncand: the tile had more filter hits than its list holds
 
 // Bucketed table over whole-field keys.  Bucket b = 8 entries {fingerprint, key offset} = 64 bytes (two L2 sectors,
 // fetched with four independent 16-byte loads); fingerprint 0 = empty, slots fill in order, a full bucket spills into
@@ -141,7 +146,18 @@ struct ExactDevice {
     const uint4 *bkt;                      // [4 * nbuckets] {fp0, off0, fp1, off1} x 4; fingerprint = (hash >> 32) | 1
     const unsigned long long *kw;          // meta + key words per key (+ 8 words of slack at the end)
     unsigned int mask;                     // nbuckets - 1; bucket = (unsigned)hash & mask
+    // Pre-filter in front of the table: word-blocked Bloom filter, >= 16 bits per key, four bits of one 32-bit word
+    // per key (exact_pre_word / exact_pre_mask).  1 M keys = 2 MiB: resident in L2 while the batch streams past it
+    // (the scan's bulk copies are evict-first), so the ~99 % of the records that are not in the list cost one 4-byte
+    // L2 hit instead of a 64-byte bucket read from HBM.
+    const unsigned int *pre;               // [pre_mask + 1] or nullptr
+    unsigned int pre_mask;
 };
+__host__ __device__ inline unsigned int exact_pre_word(unsigned long long h, unsigned int pre_mask) { return (unsigned int)(h >> 20) & pre_mask; }
+__host__ __device__ inline unsigned int exact_pre_mask(unsigned long long h)
+{
+    return (1u << ((h >> 44) & 31u)) | (1u << ((h >> 49) & 31u)) | (1u << ((h >> 54) & 31u)) | (1u << ((h >> 59) & 31u));
+}
 
 struct ScanParams {
     const uint8_t *buf;
@@ -163,17 +179,19 @@ struct ScanParams {
     const uint8_t *pat_bytes;         // device copy of pattern bytes
     int target;
     int mode;                         // kMode*: selects the scan kernel variant
-    int match_enabled;                // 1: the scan kernel leaves line hits in tile_hit (literal / k-mer / exact);
+    int match_enabled;                // 1: the scan kernel leaves line hits in tile_hit (literal modes);
                                       // 0: index/validate only (a second-stage field matcher uses the field table)
     int lit_unit;                     // host copy of lit->unit
     unsigned int one;                 // == 1 (lets the kernel issue adds as IMAD; see fma_add)
+    int l2_evict_first;               // 1: the bulk copies of the batch carry an L2 evict-first hint (FXG_L2_HINT=0 turns it off)
     unsigned int *redo_list;          // [ntiles] tiles whose locally guessed line phase was wrong (normally none)
     unsigned int *redo_count;         // [1]
     int redo_unanchored;              // exact mode: tiles without a phase anchor go to the REDO launch too
     KmerTile kmer;                    // mode_is_kmer(mode)
-    uint2 *cand;                      // [ntiles * cand_cap] k-mer mode: {window key, tile-relative offset} per filter hit
-    unsigned int *tile_ncand;         // [ntiles] entries of the tile's candidate list
-    int cand_cap;                     // list capacity per tile (what does not fit is resolved inside the scan kernel)
+    uint2 *cand;                      // [ntiles * cand_cap] window matcher: {window hash, tile-relative offset} per filter hit
+    unsigned int *tile_ncand;         // [ntiles] entries of the tile's candidate list (| kCandOverflow: the list was too
+                                      // short -- kmer_resolve_kernel then walks every probe position of the tile itself)
+    int cand_cap;                     // list capacity per tile
     ExactDevice exact;                // mode == kModeExact
     unsigned long long *keyhash;      // [ntiles * nl_stride / 4] exact mode: key hash of the target line with local index 4j + first
     // field table for the second-stage matchers (multi without k-mer index): target field of record k

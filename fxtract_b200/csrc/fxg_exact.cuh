@@ -62,6 +62,10 @@ __device__ __forceinline__ unsigned long long exact_hash(const LD &ld, long long
 // true iff the bucket chain of hash h holds its fingerprint (one memory round trip unless a bucket is full)
 __device__ __forceinline__ bool exact_fingerprint_present(const ExactDevice &E, unsigned long long h)
 {
+    if (E.pre) {
+        const unsigned int m = exact_pre_mask(h);
+        if ((__ldg(E.pre + exact_pre_word(h, E.pre_mask)) & m) != m) return false;
+    }
     unsigned int bkt = (unsigned int)h & E.mask;
     const unsigned int fp = (unsigned int)(h >> 32) | 1u;
     for (;;) {
@@ -78,6 +82,10 @@ template <class LD>
 __device__ __forceinline__ bool exact_probe(const ExactDevice &E, unsigned long long h, const LD &ld, long long start, unsigned int len,
                                             int &pid)
 {
+    if (E.pre) {
+        const unsigned int m = exact_pre_mask(h);
+        if ((__ldg(E.pre + exact_pre_word(h, E.pre_mask)) & m) != m) return false;
+    }
     const long long w0 = start >> 2;
     const int sh = (int)(start & 3) * 8;
     unsigned int bkt = (unsigned int)h & E.mask;

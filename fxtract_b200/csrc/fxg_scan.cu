@@ -279,16 +279,44 @@ __global__ void __launch_bounds__(256) exact_resolve_kernel(const ScanParams P)
     if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
 }
 
-// k-mer mode: one WARP per tile, one lane per candidate {window key, tile-relative offset of the window}: table
-// bucket, every pattern record that holds the window at one of its first S offsets compared with the batch text,
-// the occurrence's line found in the tile's '\n' table, kept if that line has the target's role.
+// window matcher: one WARP per tile, one lane per candidate {window hash, tile-relative offset of the window}:
+// table bucket, every pattern record that holds a window with this hash at one of its first S offsets compared with
+// the batch text, the occurrence's line found in the tile's '\n' table, kept if that line has the target's role.
+// A tile whose list overflowed (kCandOverflow: pattern-dense text) has every probe position walked here instead.
+__device__ __forceinline__ bool window_lookup(const ScanParams &P, unsigned int h, long long win)
+{
+    const KmerTile &K = P.kmer;
+    unsigned int bkt = kmer_tile_bucket(h, K.ht_mask);
+    for (;;) {
+        const uint4 kk = __ldg(K.ht + 2 * (size_t)bkt), vv = __ldg(K.ht + 2 * (size_t)bkt + 1);
+        const unsigned int keys[4] = {kk.x, kk.y, kk.z, kk.w}, vals[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const unsigned int v = vals[e];
+            if (!v || keys[e] != h) continue;
+            const unsigned int o = (v - 1u) & 127u;
+            const uint4 *rec = K.rec + ((v - 1u) >> 7);
+            const unsigned int m = __ldg(reinterpret_cast<const unsigned int *>(rec));
+            const long long p = win - (long long)o;
+            if (p < 0 || (unsigned long long)p + m > P.nbytes) continue;
+            const unsigned char *pb = reinterpret_cast<const unsigned char *>(rec) + 8;
+            bool eq = true;
+            for (unsigned int i = 0; i < m; ++i)
+                if (P.buf[p + i] != __ldg(pb + i)) { eq = false; break; }
+            if (eq) return true;
+        }
+        if (vv.w == 0u) return false;                        // the bucket has a free slot: nothing spilled past it
+        bkt = (bkt + 1) & K.ht_mask;
+    }
+}
+
 __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
 {
     const int lane = threadIdx.x & 31;
     const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (t >= P.ntiles) return;
-    const unsigned int nc = P.tile_ncand[t];
-    if (!nc) return;
+    const unsigned int nc_raw = P.tile_ncand[t];
+    if (!nc_raw) return;
     const KmerTile &K = P.kmer;
     const TileView V(P);
     const unsigned long long lb = V.lbase(t);
@@ -297,35 +325,26 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
     const unsigned long long base = t * (unsigned long long)P.tile_bytes;
     const unsigned short *nl = P.tile_nl + t * (unsigned long long)P.nl_stride;
     const uint2 *list = P.cand + t * (unsigned long long)P.cand_cap;
+    const bool overflow = (nc_raw & kCandOverflow) != 0u;
+    const unsigned long long left = P.nbytes - base;
+    const unsigned int tile_len = left < (unsigned long long)P.tile_bytes ? (unsigned int)left : (unsigned int)P.tile_bytes;
+    const unsigned int nc = overflow ? (tile_len + (unsigned int)K.stride - 1u) / (unsigned int)K.stride : nc_raw;
     unsigned int fresh = 0;
     for (unsigned int c = lane; c < nc; c += 32) {
-        const uint2 cd = __ldg(list + c);
-        const unsigned int key = cd.x;
-        const int win_rel = (int)cd.y;
-        bool found = false;
-        unsigned int bkt = kmer_tile_bucket(key, K.ht_mask);
-        for (;;) {
-            const uint4 kk = __ldg(K.ht + 2 * (size_t)bkt), vv = __ldg(K.ht + 2 * (size_t)bkt + 1);
-            const unsigned int keys[4] = {kk.x, kk.y, kk.z, kk.w}, vals[4] = {vv.x, vv.y, vv.z, vv.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const unsigned int v = vals[e];
-                if (found || !v || keys[e] != key) continue;
-                const unsigned int o = (v - 1u) & 127u;
-                const uint4 *rec = K.rec + ((v - 1u) >> 7);
-                const unsigned int m = __ldg(reinterpret_cast<const unsigned int *>(rec));
-                const long long p = (long long)base + win_rel - (long long)o;
-                if (p < 0 || (unsigned long long)p + m > P.nbytes) continue;
-                const unsigned char *pb = reinterpret_cast<const unsigned char *>(rec) + 8;
-                bool eq = true;
-                for (unsigned int i = 0; i < m; ++i)
-                    if (P.buf[p + i] != __ldg(pb + i)) { eq = false; break; }
-                found = eq;
-            }
-            if (found || vv.w == 0u) break;                  // the bucket has a free slot: nothing spilled past it
-            bkt = (bkt + 1) & K.ht_mask;
+        unsigned int h;
+        int win_rel;
+        if (!overflow) {
+            const uint2 cd = __ldg(list + c);
+            h = cd.x; win_rel = (int)cd.y;
+        } else {
+            win_rel = (int)(c * (unsigned int)K.stride);
+            const unsigned long long g = base + (unsigned long long)win_rel;
+            if (g + (unsigned long long)K.k > P.nbytes) continue;      // a window inside an occurrence lies inside the batch
+            unsigned int w[4] = {0u, 0u, 0u, 0u};
+            for (int i = 0; i < K.k; ++i) w[i >> 2] |= (unsigned int)P.buf[g + i] << (8 * (i & 3));
+            h = window_hash(w[0], w[1], w[2], w[3]);
         }
-        if (!found) continue;
+        if (!window_lookup(P, h, (long long)base + win_rel)) continue;
         // local line of the occurrence = number of '\n' before the window (a pattern holds no '\n', so all of it
         // lies on the line of its window)
         int lo = 0, hi = n_tab;
@@ -383,9 +402,9 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
     const bool kmer = mode_is_kmer(P.mode);
     if (kmer) e = launch_scan_kmer(P, stream, dev);
     else if (P.mode == kModeExact) e = launch_scan_tiles<G24, kModeExact, false>(P, 0, stream, dev, 0);
-    else if (P.mode == kModeLit9) e = launch_scan_tiles<G24, kModeLit9, false>(P, 0, stream, dev, 0);
-    else if (P.mode == kModeLit8) e = launch_scan_tiles<G24, kModeLit8, false>(P, 0, stream, dev, 0);
-    else if (P.mode == kModeLitSmall) e = launch_scan_tiles<G24, kModeLitSmall, false>(P, 0, stream, dev, 0);
+    else if (P.mode == kModeLit9) e = launch_scan_tiles<G24, kModeLit9, false>(P, sizeof(LitSmem), stream, dev, 0);
+    else if (P.mode == kModeLit8) e = launch_scan_tiles<G24, kModeLit8, false>(P, sizeof(LitSmem), stream, dev, 0);
+    else if (P.mode == kModeLitSmall) e = launch_scan_tiles<G24, kModeLitSmall, false>(P, sizeof(LitSmem), stream, dev, 0);
     else e = launch_scan_tiles<G24, kModeIndex, false>(P, 0, stream, dev, 0);
     if (e != cudaSuccess) return e;
     if (after_scan) cudaEventRecord(after_scan, stream);

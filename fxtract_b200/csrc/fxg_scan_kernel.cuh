@@ -53,21 +53,20 @@ template <class G> struct __align__(128) ScanSmem {
     unsigned int sbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x41 (not a sequence letter)
     unsigned int qbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x21 (not a quality char)
     unsigned int linehit[G::kHitWords];               // bit i: local line i has a (phase-conditional) match
-    union {
-        struct {
-            unsigned long long keys[64];
-            unsigned int fp[64];
-            unsigned short masks[64];
-            int cand_off[kCandCap];                   // tile-relative offset of a candidate unit
-            unsigned short cand_mask[kCandCap];       // (pattern,shift) bits to verify
-        } lit;
-        // k-mer mode: per warp, (chunk index within the warp's segment << 8) | filter-hit bits of that chunk
-        unsigned short kq[G::kWarps][G::kWarpChunks];
-    } m;
     unsigned long long mbar[2];                       // bulk-copy completion barriers
     // per-tile scalars, double buffered by tile parity: the copy of the previous tile is reset by
     // thread 0 while the current one is in use (no extra barrier between "last read" and "first write")
     TileState st[2];
+};
+
+// literal modes: fingerprint table and candidate queue, placed behind ScanSmem in the dynamic allocation (the window
+// matcher has its filter there instead)
+struct __align__(16) LitSmem {
+    unsigned long long keys[64];
+    unsigned int fp[64];
+    unsigned short masks[64];
+    int cand_off[kCandCap];                           // tile-relative offset of a candidate unit
+    unsigned short cand_mask[kCandCap];               // (pattern,shift) bits to verify
 };
 
 __device__ __forceinline__ void reset_state(TileState &T)
@@ -89,10 +88,19 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned long long *mbar, unsigne
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(bytes) : "memory");
 }
 // 1-D bulk async copy global -> shared (TMA engine), completion counted in bytes on the mbarrier
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned int bytes, unsigned long long *mbar)
+// The batch streams through L2 exactly once, so its lines are marked evict-first: the look-up tables of the matchers
+// (window index, key table, DFA) and the per-tile tables the epilogue kernels read back stay resident in the 126 MB L2.
+__device__ __forceinline__ unsigned long long l2_stream_policy(int evict_first)
 {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(mbar)) : "memory");
+    unsigned long long pol;
+    if (evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned int bytes, unsigned long long *mbar, unsigned long long pol)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(mbar)), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long *mbar, unsigned int parity)
 {
@@ -145,16 +153,6 @@ __device__ __forceinline__ unsigned int lin_mask(const uint4 &x, unsigned int ad
     unsigned int n2 = ((~(x.z + add) & kHi) * 0x00204081u) >> 28;
     unsigned int n3 = ((~(x.w + add) & kHi) * 0x00204081u) >> 28;
     return n0 | (n1 << 4) | (n2 << 8) | (n3 << 12);
-}
-
-// 2-bit codes of the 16 bytes of a chunk, byte i in bits 2i, 2i+1 (code = (byte >> 1) & 3: A 0, C 1, T 2, G 3).
-// Per word: mask bits 1..2 of every byte, one multiply gathers the four codes in the top byte (the partial
-// products land on disjoint bits, so nothing carries), three byte permutes assemble the chunk word.
-__device__ __forceinline__ unsigned int pack16(const uint4 &x)
-{
-    const unsigned int m0 = (x.x & 0x06060606u) * 0x00820820u, m1 = (x.y & 0x06060606u) * 0x00820820u;
-    const unsigned int m2 = (x.z & 0x06060606u) * 0x00820820u, m3 = (x.w & 0x06060606u) * 0x00820820u;
-    return __byte_perm(__byte_perm(m0, m1, 0x0073), __byte_perm(m2, m3, 0x0073), 0x5410);
 }
 
 __device__ __forceinline__ void note_violation(TileState &T, unsigned int bit) { atomicOr(&T.viol, bit); }
@@ -311,15 +309,14 @@ __device__ __noinline__ void verify_candidate(ScanSmem<G> &S, TileState &T, cons
     }
 }
 
-template <class G> __device__ __forceinline__ void push_candidate(ScanSmem<G> &S, TileState &T, int unit_rel, unsigned int bits)
+__device__ __forceinline__ void push_candidate(LitSmem &LS, TileState &T, int unit_rel, unsigned int bits)
 {
     unsigned int slot = atomicAdd(&T.n_cand, 1u);
-    if (slot < kCandCap) { S.m.lit.cand_off[slot] = unit_rel; S.m.lit.cand_mask[slot] = (unsigned short)bits; }
+    if (slot < kCandCap) { LS.cand_off[slot] = unit_rel; LS.cand_mask[slot] = (unsigned short)bits; }
 }
 
 // generic (short-pattern) literal filter: units of 4, 2 or 1 bytes compared against every key
-template <class G>
-__device__ __noinline__ void filter_small_units(ScanSmem<G> &S, TileState &T, unsigned int x0, unsigned int x1, unsigned int x2,
+static __device__ __noinline__ void filter_small_units(LitSmem &LS, TileState &T, unsigned int x0, unsigned int x1, unsigned int x2,
                                                 unsigned int x3, int off, int U, int nkeys)
 {
     for (int u = 0; u < 16; u += U) {
@@ -327,60 +324,7 @@ __device__ __noinline__ void filter_small_units(ScanSmem<G> &S, TileState &T, un
         unsigned int word = wi == 0 ? x0 : (wi == 1 ? x1 : (wi == 2 ? x2 : x3));
         unsigned int val = U == 4 ? word : (U == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu) : ((word >> ((u & 3) * 8)) & 0xffu));
         for (int k = 0; k < nkeys; ++k)
-            if ((unsigned int)S.m.lit.keys[k] == val) push_candidate(S, T, off + u, S.m.lit.masks[k]);
-    }
-}
-
-// ---------------------------------------------------------------- k-mer mode: one filter hit -> table -> bytes
-// `win_rel` = tile-relative offset of the first byte of the window, `key` its packed bases.  Every
-// pattern that holds this window at one of its first S offsets is compared byte by byte with the text; the first
-// one that matches marks the local line of the occurrence (all of them lie on the same line).
-template <class G>
-__device__ __noinline__ void kmer_resolve(ScanSmem<G> &S, TileState &T, const unsigned char *tb, const ScanParams &P,
-                                          unsigned long long base, int n_tab, int win_rel, unsigned int key)
-{
-    const KmerTile &K = P.kmer;
-    unsigned int bkt = kmer_tile_bucket(key, K.ht_mask);
-    for (;;) {
-        const uint4 kk = __ldg(K.ht + 2 * (size_t)bkt), vv = __ldg(K.ht + 2 * (size_t)bkt + 1);
-        const unsigned int keys[4] = {kk.x, kk.y, kk.z, kk.w}, vals[4] = {vv.x, vv.y, vv.z, vv.w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const unsigned int v = vals[e];
-            if (!v || keys[e] != key) continue;
-            const unsigned int o = (v - 1u) & 127u;
-            const uint4 *rec = K.rec + ((v - 1u) >> 7);
-            // pattern record: {length, id, bytes}; the first 40 pattern bytes arrive in one round trip
-            const uint4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
-            const unsigned int m = r0.x;
-            const long long p = (long long)base + win_rel - (long long)o;
-            if (p < 0 || (unsigned long long)p + m > P.nbytes) continue;
-            const unsigned int head[10] = {r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
-            bool eq = true;
-            for (unsigned int i = 0; i < m && eq; i += 4) {
-                unsigned int w;
-                if (i < 40) {
-                    w = head[0];
-#pragma unroll
-                    for (int q = 1; q < 10; ++q) if ((i >> 2) == (unsigned int)q) w = head[q];
-                } else {
-                    const uint4 rr = __ldg(rec + ((i + 8) >> 4));
-                    const unsigned int sel = ((i + 8) >> 2) & 3u;
-                    w = sel == 0 ? rr.x : (sel == 1 ? rr.y : (sel == 2 ? rr.z : rr.w));
-                }
-                for (unsigned int b = 0; b < 4 && i + b < m; ++b)
-                    if (text_byte<G>(tb, P, base, p + i + b) != ((w >> (8 * b)) & 0xffu)) { eq = false; break; }
-            }
-            if (eq) {
-                const long long rel = p - (long long)base;
-                const unsigned int loc = rel > 0 ? lines_before(S, n_tab, (int)rel) : 0u;
-                atomicOr(&S.linehit[loc >> 5], 1u << (loc & 31));
-                atomicOr(&T.viol, kTileHasHit);
-                return;
-            }
-        }
-        if (vv.w == 0u) return;                            // the bucket has a free slot: nothing spilled past it
-        bkt = (bkt + 1) & K.ht_mask;
+            if ((unsigned int)LS.keys[k] == val) push_candidate(LS, T, off + u, LS.masks[k]);
     }
 }
 
@@ -463,13 +407,14 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     constexpr bool LIT = mode_is_literal(MODE);
     constexpr bool KMER = mode_is_kmer(MODE);
     constexpr bool EXACT = MODE == kModeExact;
-    constexpr int SB = KMER ? (1 << (MODE - kModeKmer)) : 16;          // probe stride (bytes == bases)
+    constexpr int SB = KMER ? (1 << (MODE - kModeKmer)) : 16;          // probe stride in bytes
     constexpr int NPROBE = 16 / SB;
-    constexpr bool HITS = MODE != kModeIndex && !EXACT && !REDO;      // this launch produces line-hit words
+    constexpr bool HITS = LIT && !REDO;                                // this launch produces line-hit words
     typedef ScanSmem<G> Smem;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &S = *reinterpret_cast<Smem *>(smem_raw);
-    unsigned int *filt = reinterpret_cast<unsigned int *>(smem_raw + sizeof(Smem));   // k-mer filter (dynamic tail)
+    unsigned int *filt = reinterpret_cast<unsigned int *>(smem_raw + sizeof(Smem));   // window filter (dynamic tail), or
+    LitSmem &LS = *reinterpret_cast<LitSmem *>(smem_raw + sizeof(Smem));              // the literal tables
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LiteralTable *lit = P.lit;
     const unsigned long long n_work = REDO ? (unsigned long long)*P.redo_count : P.ntiles;
@@ -484,11 +429,12 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         const unsigned int bulk__ = (unsigned int)(rem__ < (unsigned long long)kFetch ? rem__ : (unsigned long long)kFetch) & ~15u; \
         if (bulk__) {                                                                                                   \
             mbar_expect_tx(&S.mbar[bf], bulk__);                                                                        \
-            bulk_g2s(&S.tile[bf][0], P.buf + b__, bulk__, &S.mbar[bf]);                                                 \
+            bulk_g2s(&S.tile[bf][0], P.buf + b__, bulk__, &S.mbar[bf], l2pol);                                                 \
         }                                                                                                               \
     } while (0)
 
     // ---- once per CTA: tables, barriers, first tile in flight
+    const unsigned long long l2pol = l2_stream_policy(P.l2_evict_first);
     if (tid == 0) {
         mbar_init(&S.mbar[0], 1);
         mbar_init(&S.mbar[1], 1);
@@ -498,19 +444,19 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         reset_state(S.st[1]);
     }
     if (tid >= 128 && tid < 145) S.below[tid - 128] = kBelowTab[tid - 128];
-    if (MODE != kModeIndex) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
+    if (LIT) for (int w = tid; w < kHitWords; w += kThreads) S.linehit[w] = 0;
     int lit_unit = 0, lit_nkeys = 0;
     unsigned int lit_mul1 = 0, lit_mul2 = 0, lit_shift = 26;
     if (LIT) {
         lit_unit = lit->unit; lit_nkeys = lit->n_keys; lit_mul1 = lit->mul1; lit_mul2 = lit->mul2; lit_shift = (unsigned int)lit->shift;
         if (tid >= 64 && tid < 128) {
             const int k = tid - 64;
-            S.m.lit.keys[k] = lit->keys[k]; S.m.lit.fp[k] = lit->fp[k]; S.m.lit.masks[k] = lit->masks[k];
+            LS.keys[k] = lit->keys[k]; LS.fp[k] = lit->fp[k]; LS.masks[k] = lit->masks[k];
         }
     }
-    unsigned int kmask = 0, fshift = 0;
+    unsigned int wmask2 = 0, wmask3 = 0, fshift = 0;
     if (KMER && !REDO) {
-        kmask = P.kmer.kmask; fshift = 32u - (unsigned int)P.kmer.filter_log2_words;
+        wmask2 = P.kmer.mask2; wmask3 = P.kmer.mask3; fshift = 32u - (unsigned int)P.kmer.filter_log2_words;
         const int nw = 1 << P.kmer.filter_log2_words;
         const uint4 *src = reinterpret_cast<const uint4 *>(P.kmer.filter);
         uint4 *dst = reinterpret_cast<uint4 *>(filt);
@@ -520,7 +466,6 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     const unsigned int lt_mask = (1u << lane) - 1u;
     unsigned short *my_list = S.wl[warp];
     unsigned short *my_mask = S.wm[warp];
-    unsigned short *my_kq = S.m.kq[warp];
     const int trole = target_role(P.target);
     __syncthreads();
 
@@ -563,20 +508,13 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         // ---- 1. main pass: 16 bytes per lane per step, SWAR only.  Per chunk: byte range, "has a
         //         byte < 0x41" / "< 0x21" ballot rows, list of the chunks with a byte < 0x21 (the only
         //         ones that can hold a '\n'), matcher filter.
-        unsigned int wcount = 0, kqn = 0;
+        unsigned int wcount = 0;
         {
             unsigned int hi_acc = 0;
-            // k-mer mode: the lane's chunk and its packed word are fetched one step ahead, because the windows that
-            // start in lane 31's chunk end in lane 0's chunk of the NEXT step (last step: the chunk behind the warp's
-            // segment -- the next warp's first chunk, or the 16 bytes staged behind the tile)
-            uint4 xn = make_uint4(0u, 0u, 0u, 0u);
-            unsigned int pkn = 0;
-            if (KMER && !REDO && SB < 16) { xn = tile[warp * kWarpChunks + lane]; pkn = pack16(xn); }
 #pragma unroll
             for (int j = 0; j < kChunksPerThread; ++j) {
                 const int c = warp * kWarpChunks + j * 32 + lane;
-                uint4 x;
-                if (KMER && !REDO && SB < 16) x = xn; else x = tile[c];
+                const uint4 x = tile[c];
                 hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);     // bytes >= 0x7f anywhere
                 hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
                 hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
@@ -594,42 +532,44 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                 if (LIT8 && !REDO) {
                     const unsigned int r0 = MODE == kModeLit9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
                     const unsigned int r1 = MODE == kModeLit9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
-                    const bool c0 = S.m.lit.fp[r0 >> lit_shift] == r0, c1 = S.m.lit.fp[r1 >> lit_shift] == r1;
+                    const bool c0 = LS.fp[r0 >> lit_shift] == r0, c1 = LS.fp[r1 >> lit_shift] == r1;
                     if (__any_sync(0xffffffffu, c0 || c1)) {          // rare: keep the hot loop branch-free
-                        if (c0) push_candidate(S, T, c << 4, S.m.lit.masks[r0 >> lit_shift]);
-                        if (c1) push_candidate(S, T, (c << 4) + 8, S.m.lit.masks[r1 >> lit_shift]);
+                        if (c0) push_candidate(LS, T, c << 4, LS.masks[r0 >> lit_shift]);
+                        if (c1) push_candidate(LS, T, (c << 4) + 8, LS.masks[r1 >> lit_shift]);
                     }
                 } else if (MODE == kModeLitSmall && !REDO) {
-                    if ((c << 4) < tile_len) filter_small_units(S, T, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
+                    if ((c << 4) < tile_len) filter_small_units(LS, T, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
                 } else if (KMER && !REDO) {
-                    // windows of k bases that start at byte 0, SB, 2 SB, ... of the lane's chunk; they end in it or in
-                    // the next chunk, whose packed word comes from the next lane
-                    unsigned int acc = 0;
-                    if (SB == 16) {
-                        const unsigned int h = (pack16(x) & kmask) * kKmerHashMul;
-                        const unsigned int fw = filt[h >> fshift];
-                        acc = (__funnelshift_l(0u, fw, h) & __funnelshift_l(0u, fw, h >> 5)) >> 31;
-                    } else {
-                        const unsigned int pk = pkn;
-                        xn = tile[c + 32];                            // lane's chunk of the next step (see above)
-                        pkn = pack16(xn);
-                        unsigned int pq = __shfl_down_sync(0xffffffffu, pk, 1);
-                        const unsigned int first_next = __shfl_sync(0xffffffffu, pkn, 0);
-                        if (lane == 31) pq = first_next;
-#pragma unroll
-                        for (int s = 0; s < 16; s += SB) {
-                            const unsigned int key = (s ? __funnelshift_r(pk, pq, 2 * s) : pk) & kmask;
-                            const unsigned int h = key * kKmerHashMul;
-                            // filter bits 31 - (h & 31) and 31 - ((h >> 5) & 31) of word h >> fshift, moved to the top,
-                            // combined and shifted into acc
-                            const unsigned int fw = filt[h >> fshift];
-                            acc = __funnelshift_l(__funnelshift_l(0u, fw, h) & __funnelshift_l(0u, fw, h >> 5), acc, 1);
-                        }
+                    // windows of k bytes that start at byte 0, SB, 2 SB, ... of the lane's chunk; what lies past the
+                    // chunk comes from the head of the next one (same shared-memory row; behind the tile's last chunk
+                    // lie the 16 bytes staged after the tile)
+                    unsigned int wd[7] = {x.x, x.y, x.z, x.w, 0u, 0u, 0u};
+                    if (SB == 8) {
+                        const uint2 n = *reinterpret_cast<const uint2 *>(&tile[c + 1]);
+                        wd[4] = n.x; wd[5] = n.y;
+                    } else if (SB == 4) {
+                        const uint4 n = tile[c + 1];
+                        wd[4] = n.x; wd[5] = n.y; wd[6] = n.z;
                     }
-                    const unsigned int vb = __ballot_sync(0xffffffffu, acc != 0u);
-                    if (vb) {
-                        if (acc) my_kq[kqn + __popc(vb & lt_mask)] = (unsigned short)(((j * 32 + lane) << 8) | acc);
-                        kqn += __popc(vb);
+                    unsigned int hs[NPROBE], hits = 0;
+#pragma unroll
+                    for (int q = 0; q < NPROBE; ++q) {
+                        const int o = q * (SB / 4);                   // first word of the window
+                        const unsigned int h = window_hash(wd[o], wd[o + 1], wd[o + 2] & wmask2, wd[o + 3] & wmask3);
+                        hs[q] = h;
+                        const unsigned int fw = filt[h >> fshift];
+                        const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h) | __funnelshift_l(0x00000101u, 0x00000101u, h >> 5);
+                        if ((m & ~fw) == 0u) hits |= 1u << q;
+                    }
+                    if (__any_sync(0xffffffffu, hits != 0u)) {        // filter hits are rare: listed for kmer_resolve_kernel
+#pragma unroll
+                        for (int q = 0; q < NPROBE; ++q) {
+                            if (hits & (1u << q)) {
+                                const unsigned int slot = atomicAdd(&T.n_cand, 1u);
+                                if (slot < (unsigned int)P.cand_cap)
+                                    P.cand[t * (unsigned long long)P.cand_cap + slot] = make_uint2(hs[q], (unsigned int)((c << 4) + q * SB));
+                            }
+                        }
                     }
                 }
             }
@@ -743,13 +683,21 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                         else if (i >= 3 && e - a != (int)S.nlpos[i - 2] - (int)S.nlpos[i - 3] - 1) viol |= FXG_V_QUAL_LEN;
                     }
                 }
-                // exact mode: the warps of the target's role hash their (whole) lines; the line that straddles the
-                // tile's left edge is left to tile_finalize_kernel
-                if (EXACT && role == trole && whole)
-                    P.keyhash[t * (unsigned long long)(kMaxTileLines / 4) + (unsigned int)(i >> 2)] = exact_line_hash_tile(P, tb, a, e);
             }
             viol = __reduce_or_sync(0xffffffffu, viol);
             if (lane == 0 && viol) atomicOr(&T.viol, viol);
+            // exact mode: the (whole) lines of the target's role are hashed by the warps of the role two lines away
+            // -- for a header target those are the "+"-line warps, which have next to nothing to check, so the
+            // longest chain of this step stays one class check or one key hash, not both.  The line that straddles
+            // the tile's left edge is left to tile_finalize_kernel.
+            if (EXACT && role == ((trole + 2) & 3)) {
+                const int hfirst = (trole - r) & 3;
+                for (int i = hfirst + 4 * ((warp >> 2) * 32 + lane); i < n_tab; i += 4 * (kWarps / 4) * 32) {
+                    if (i < 1) continue;
+                    P.keyhash[t * (unsigned long long)(kMaxTileLines / 4) + (unsigned int)(i >> 2)] =
+                        exact_line_hash_tile(P, tb, (int)S.nlpos[i - 1] + 1, (int)S.nlpos[i]);
+                }
+            }
         } else {
             // generic path (no "+" line in the tile, or REDO): one thread per line, flags OR-ed per
             // (local line index mod 4); tile_finalize_kernel maps them to roles once the phase is known.
@@ -786,7 +734,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
             const unsigned int nc_all = T.n_cand;
             if (nc_all <= (unsigned int)kCandCap) {
                 for (unsigned int q = tid; q < nc_all; q += kThreads)
-                    verify_candidate(S, T, tb, P, base, n_tab, S.m.lit.cand_off[q], S.m.lit.cand_mask[q]);
+                    verify_candidate(S, T, tb, P, base, n_tab, LS.cand_off[q], LS.cand_mask[q]);
             } else {
                 // queue overflow (pattern hits nearly everywhere): rescan the tile and verify in place
                 for (int c = tid; c < kChunks && (c << 4) < tile_len; c += kThreads) {
@@ -794,8 +742,8 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                     if (LIT8) {
                         const unsigned int r0 = MODE == kModeLit9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
                         const unsigned int r1 = MODE == kModeLit9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
-                        if (S.m.lit.fp[r0 >> lit_shift] == r0) verify_candidate(S, T, tb, P, base, n_tab, c << 4, S.m.lit.masks[r0 >> lit_shift]);
-                        if (S.m.lit.fp[r1 >> lit_shift] == r1) verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + 8, S.m.lit.masks[r1 >> lit_shift]);
+                        if (LS.fp[r0 >> lit_shift] == r0) verify_candidate(S, T, tb, P, base, n_tab, c << 4, LS.masks[r0 >> lit_shift]);
+                        if (LS.fp[r1 >> lit_shift] == r1) verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + 8, LS.masks[r1 >> lit_shift]);
                     } else {
                         const unsigned int wv[4] = {x.x, x.y, x.z, x.w};
                         for (int u = 0; u < 16; u += lit_unit) {
@@ -803,47 +751,10 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                             unsigned int val = lit_unit == 4 ? word : (lit_unit == 2 ? ((word >> ((u & 2) * 8)) & 0xffffu)
                                                                                      : ((word >> ((u & 3) * 8)) & 0xffu));
                             for (int q = 0; q < lit_nkeys; ++q)
-                                if ((unsigned int)S.m.lit.keys[q] == val)
-                                    verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + u, S.m.lit.masks[q]);
+                                if ((unsigned int)LS.keys[q] == val)
+                                    verify_candidate(S, T, tb, P, base, n_tab, (c << 4) + u, LS.masks[q]);
                         }
                     }
-                }
-            }
-        }
-        if (KMER && !REDO) {
-            // every warp moves the filter hits of its own segment (queue written by this warp in step 1) into the
-            // tile's candidate list in global memory as {window key, tile-relative offset}; kmer_resolve_kernel
-            // looks them up afterwards, one thread per candidate.  Only what does not fit the list is resolved here.
-            __syncwarp();
-            unsigned int mine = 0;
-            for (unsigned int q = lane; q < kqn; q += 32) mine += __popc((unsigned int)my_kq[q] & 0xffu);
-            unsigned int inc = mine;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const unsigned int o = __shfl_up_sync(0xffffffffu, inc, d);
-                if (lane >= d) inc += o;
-            }
-            const unsigned int wtotal = __shfl_sync(0xffffffffu, inc, 31);
-            unsigned int wbase = 0;
-            if (lane == 0 && wtotal) wbase = atomicAdd(&T.n_cand, wtotal);
-            wbase = __shfl_sync(0xffffffffu, wbase, 0);
-            unsigned int slot = wbase + inc - mine;
-            const unsigned int cap = (unsigned int)P.cand_cap;
-            uint2 *list = P.cand + t * (unsigned long long)cap;
-            for (unsigned int q = lane; q < kqn; q += 32) {
-                const unsigned int e = my_kq[q];
-                const int ce = warp * kWarpChunks + (int)(e >> 8);    // chunk the windows start in
-                unsigned int bits = e & 0xffu;
-                const unsigned int p0 = pack16(tile[ce]);
-                const unsigned int p1 = SB < 16 ? pack16(tile[ce + 1]) : 0u;
-                while (bits) {
-                    const int bi = 31 - __clz(bits);
-                    bits &= ~(1u << bi);
-                    const int s = (NPROBE - 1 - bi) * SB;             // first probe of a chunk ends up in the highest bit
-                    const unsigned int key = (s ? __funnelshift_r(p0, p1, 2 * s) : p0) & kmask;
-                    if (slot < cap) list[slot] = make_uint2(key, (unsigned int)(ce * 16 + s));
-                    else kmer_resolve(S, T, tb, P, base, n_tab, ce * 16 + s, key);
-                    ++slot;
                 }
             }
         }
@@ -866,7 +777,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                 }
             }
             if (tid == 0) {
-                if (KMER && !REDO) P.tile_ncand[t] = T.n_cand < (unsigned int)P.cand_cap ? T.n_cand : (unsigned int)P.cand_cap;
+                if (KMER && !REDO) P.tile_ncand[t] = T.n_cand <= (unsigned int)P.cand_cap ? T.n_cand : ((unsigned int)P.cand_cap | kCandOverflow);
                 // the REDO launch re-checks structure only: the hit words of the first launch stand, and so does their flag
                 const unsigned int kept = REDO ? (P.info[t].viol & kTileHasHit) : 0u;
                 const TileInfo ti = {total, kept | T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),

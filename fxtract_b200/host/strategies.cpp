@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <chrono>
 #include <condition_variable>
+#include <cerrno>
 #include <cstdlib>
 #include <mutex>
 #include <set>
@@ -23,6 +24,7 @@
 #include <memory>
 #include <regex.h>
 #include <sys/stat.h>
+#include <sys/uio.h>
 #include <unistd.h>
 
 #ifndef REG_BASIC
@@ -37,7 +39,42 @@ enum Strategy { S_LITERAL, S_MULTI, S_EXACT };
 
 struct Stats {
     uint64_t raw_bytes = 0, raw_batches = 0, field_bytes = 0, field_batches = 0, records = 0, rerouted = 0;
+    double t_ingest = 0, t_gpu = 0, t_write = 0;      // raw path: main thread blocked on the readers / on the devices / writing
 };
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// Selected byte runs of a raw batch go out with writev straight from the pinned copy of the batch (stdio would
+// copy every byte once more into its buffer: with -v nearly the whole input is output).
+void write_runs(const uint8_t *host, const fxg_run *runs, uint64_t n)
+{
+    if (!n) return;
+    fflush(stdout);                                     // keep the order with anything printed through stdio
+    constexpr int kIov = 512;
+    struct iovec iov[kIov];
+    uint64_t k = 0;
+    while (k < n) {
+        int cnt = 0;
+        size_t want = 0;
+        for (; cnt < kIov && k < n; ++k) {
+            if (!runs[k].len) continue;
+            iov[cnt].iov_base = const_cast<uint8_t *>(host + runs[k].off);
+            iov[cnt].iov_len = (size_t)runs[k].len;
+            want += iov[cnt].iov_len;
+            ++cnt;
+        }
+        int first = 0;
+        while (want) {
+            ssize_t got = writev(STDOUT_FILENO, iov + first, cnt - first);
+            if (got < 0) { if (errno == EINTR) continue; perror("fxtract: write"); exit(1); }
+            want -= (size_t)got;
+            while (got > 0 && first < cnt) {              // short write: advance through the vector
+                if ((size_t)got >= iov[first].iov_len) { got -= (ssize_t)iov[first].iov_len; ++first; }
+                else { iov[first].iov_base = (uint8_t *)iov[first].iov_base + got; iov[first].iov_len -= (size_t)got; got = 0; }
+            }
+        }
+    }
+}
 
 // main.cpp:291-304 prepare_data; the multi-pattern twin (main.cpp:389-405, :410-425) differs for -Q
 void target_slice(const CliOptions &o, Strategy st, const PairBatch &b, const RecView &r, bool second,
@@ -293,15 +330,19 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
     int64_t reroute_at = -1;
     auto finish_oldest = [&]() {
         fxg_result r;
+        const double t0 = now_s();
         pool.collect(&r);
+        const double t1 = now_s();
+        stats.t_gpu += t1 - t0;
         RawPending p = pending.front();
         pending.pop_front();
         if (reroute_at < 0) {
             if (!r.canonical_ok) { reroute_at = (int64_t)p.file_off; stats.rerouted++; }
             else {
                 if (o.c) job.matched_records += (long)r.n_selected;
-                else for (uint64_t k = 0; k < r.n_runs; ++k) fwrite(p.host + r.runs[k].off, 1, r.runs[k].len, stdout);
+                else write_runs(p.host, r.runs, r.n_runs);
                 stats.records += r.n_records;
+                stats.t_write += now_s() - t1;
             }
         }                                                              // results after a rejected batch are discarded
         ingest.release_window(p.window);
@@ -312,7 +353,9 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
     for (uint64_t k = 0; k < ingest.windows() && reroute_at < 0; ++k) {
         if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute_at >= 0) break; }
         size_t wlen;
+        const double tw = now_s();
         uint8_t *w = ingest.wait_window(k, &wlen);
+        stats.t_ingest += now_s() - tw;
         if (carry_n > pad) {                            // a record longer than the pad: not the fast path's business
             while (!pending.empty()) finish_oldest();
             if (reroute_at < 0) reroute_at = (int64_t)consumed;
@@ -465,6 +508,9 @@ int run_input(Job &job, const char *file1, const char *file2)
     if (!done) run_fields(job, st, src, paired, pool, stats);
     if (job.stats) {
         const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (stats.raw_batches)
+            fprintf(stderr, "[fxtract] raw path main thread: %.3f s waiting for the readers, %.3f s for the devices, %.3f s writing\n",
+                    stats.t_ingest, stats.t_gpu, stats.t_write);
         fprintf(stderr, "[fxtract] %s: raw %llu B in %llu batches, fields %llu B in %llu batches, %llu records, %llu re-routed, "
                         "%.3f s%s\n", file1, (unsigned long long)stats.raw_bytes, (unsigned long long)stats.raw_batches,
                 (unsigned long long)stats.field_bytes, (unsigned long long)stats.field_batches,

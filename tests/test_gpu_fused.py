@@ -50,11 +50,12 @@ def fastq_with_plants(rng, nrec, pats, every=5, seqlen=(40, 200), letters=b"ACGT
     return b"".join(recs)
 
 
-# pattern length -> probe stride of the window index: 12,13 -> 2; 14..17 -> 4; 18..25 -> 8; >= 26 -> 16
+# shortest pattern -> probe stride of the window index: 12, 13 -> none (index pass + field matcher); 14..17 -> 4;
+# 18..25 -> 8; >= 26 -> 16
 @pytest.mark.parametrize("minlen,npat", [(12, 30), (13, 400), (14, 5), (17, 700), (18, 60), (20, 1000), (25, 3),
                                          (26, 200), (31, 900), (40, 50), (20, 3000), (16, 6000)])
 def test_kmer_fused_strides_and_filters(fx, minlen, npat):
-    """Every probe stride, both filter sizes (more than 16384 index entries take the 128 KiB filter), patterns of
+    """Every probe stride, both filter sizes (more than 32768 index entries take the 128 KiB filter), patterns of
     mixed length, hits at read edges and across tile edges; flags -f / -vf / -cf against the oracle."""
     rng = random.Random(minlen * 1000 + npat)
     pats = sorted(set(helpers.rand_dna(rng, rng.randint(minlen, minlen + rng.choice([0, 2, 9]))).encode() for _ in range(npat)) |
@@ -72,6 +73,39 @@ def test_kmer_fused_strides_and_filters(fx, minlen, npat):
     assert got_v["out"] == want_v
     cnt = run_raw(fx, data, fx.MODE_MULTI, pats, count_only=True)
     assert cnt["n_selected"] == want.count(b"\n") // 4
+
+
+def test_kmer_fused_candidate_list_overflow(fx):
+    """Pattern-dense text: nearly every probed window passes the filter, far more than a tile's candidate list holds
+    (kCandOverflow) -- the resolve kernel then walks every probe position of such a tile itself."""
+    rng = random.Random(99)
+    pats = sorted({b"A" * 20, b"ACGT" * 5, b"TTTTTTTTTTTTTTTTTTTTTTG"})
+    recs = []
+    for i in range(5000):
+        kind = i % 7
+        n = rng.randint(60, 160)
+        if kind < 3:
+            seq = b"A" * n
+        elif kind == 3:
+            seq = (b"ACGT" * 50)[rng.randint(0, 3):][:n]
+        elif kind == 4:
+            seq = b"A" * 19 + b"C" + b"A" * 19 + b"G" * (n - 39)          # 19 is not enough
+        elif kind == 5:
+            seq = b"T" * (n - 1) + b"G"
+        else:
+            seq = helpers.rand_dna(rng, n).encode()
+        qual = b"A" * n if i % 2 else bytes(rng.randint(33, 73) for _ in range(n))
+        recs.append(b"@o%d\n" % i + seq + b"\n+\n" + qual + b"\n")
+    data = b"".join(recs)
+    pf = b"\n".join(pats) + b"\n"
+    for flags, kw in (("", {}), ("v", {"invert": True})):
+        want = fxoracle.run(data, flags, pattern_file=pf)
+        got = run_raw(fx, data, fx.MODE_MULTI, pats, **kw)
+        assert got["ok"] == 1, got["violation"]
+        assert got["out"] == want, (flags, len(got["out"]), len(want))
+    want_q = fxoracle.run(data, "Q", pattern_file=pf)
+    got_q = run_raw(fx, data, fx.MODE_MULTI, pats, target=3)
+    assert got_q["out"] == want_q and want_q.count(b"\n") // 4 > 1000
 
 
 def test_kmer_fused_revcomp_and_quality_lookalikes(fx):
