@@ -20,6 +20,7 @@ struct Slot {
     unsigned long long *h_counts = nullptr;   // [2]: n_runs, n_selected (K6)
     fxg_run *h_runs = nullptr; size_t h_runs_cap = 0;
     fxg_run *d_runs = nullptr; size_t d_runs_cap = 0;
+    int *d_run_pid = nullptr, *h_run_pid = nullptr; size_t h_run_pid_cap = 0;     // routing: pattern id per run
     uint8_t *h_flags = nullptr; int *h_pid = nullptr; uint32_t *h_off = nullptr; size_t fields_cap = 0;
     cudaEvent_t done = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};   // profiling: pipeline begin, scan begin, scan end, pipeline end
@@ -55,6 +56,7 @@ struct fxg_ctx {
     uint4 *d_bkt = nullptr; unsigned int exact_mask = 0;                          // bucketed exact table
     unsigned int *d_exact_pre = nullptr; unsigned int exact_pre_mask = 0;         // its Bloom pre-filter
     unsigned long long *d_keyhash = nullptr;                                      // exact mode: key hash per target line (scan -> resolve)
+    unsigned long long *d_rec_first = nullptr;                                    // routing: first reported hit per record
     uint2 *d_cand = nullptr; unsigned int *d_tile_ncand = nullptr;                // k-mer mode: filter hits per tile (scan -> resolve)
     unsigned long long *d_key_words = nullptr;
     // scan resources (shared; everything is ordered on one stream)
@@ -312,7 +314,8 @@ static int build_kmer_tile(fxg_ctx *ctx)
     if (entries > 400000) return FXG_OK;              // the 128 KiB filter would pass more than ~ 1 window in 6
     size_t nbuckets = 16;                             // 4 entries per bucket, <= 1 on average
     while (nbuckets < entries) nbuckets <<= 1;
-    const int flw = entries <= 32768 ? 13 : 15;       // 32 KiB filter (2 CTAs / SM) or 128 KiB (1 CTA / SM); 4 bits per entry
+    int flw = entries <= 32768 ? 13 : 15;             // 32 KiB filter (2 CTAs / SM) or 128 KiB (1 CTA / SM); 4 bits per entry
+    if (const char *f = getenv("FXG_FORCE_FLW")) { if (atoi(f) == 15 || (atoi(f) == 13 && flw == 13)) flw = atoi(f); }   // experiments
     std::vector<unsigned int> filter((size_t)1 << flw, 0u), ht(nbuckets * 8, 0u);
     std::vector<unsigned char> fill(nbuckets, 0);
     const unsigned int mask = (unsigned int)(nbuckets - 1);
@@ -435,9 +438,10 @@ static int ensure_scan_capacity(fxg_ctx *ctx, size_t nbytes)
     if (ctx->scan_mode == kModeExact &&
         (e = dev_realloc(ctx->d_keyhash, ntiles * (size_t)(ctx->nl_stride / 4))) != cudaSuccess) return set_cuda_error(ctx, e, "alloc key hashes");
     if (mode_is_kmer(ctx->scan_mode)) {
-        if ((e = dev_realloc(ctx->d_cand, ntiles * (size_t)kKmerCandCap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window candidates");
+        if ((e = dev_realloc(ctx->d_cand, ntiles * (size_t)(ctx->tile_bytes / kKmerCandDiv))) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window candidates");
         if ((e = dev_realloc(ctx->d_tile_ncand, ntiles)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc window candidate counts");
     }
+    if (ctx->cfg.route_runs && (e = dev_realloc(ctx->d_rec_first, rec_cap)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc first-hit table");
     if (!ctx->d_ctr && (e = dev_realloc(ctx->d_ctr, 1)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counters");
     if (!ctx->d_counts && (e = dev_realloc(ctx->d_counts, 2)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc counts");
     if (!ctx->cfg.count_only) {
@@ -463,13 +467,25 @@ static int ensure_slot_result(fxg_ctx *ctx, Slot &s)
 // Selected runs come back in two parts: the first kRunPrefix of them ride with the counters (one small copy,
 // enqueued before the count is known); a batch with more runs fetches exactly n_runs once its count has arrived.
 constexpr size_t kRunPrefix = 1024;
+static bool routed(const fxg_ctx *ctx)
+{
+    return ctx->cfg.route_runs && !ctx->cfg.invert && !ctx->cfg.count_only &&
+           (ctx->scan_mode == kModeExact || mode_is_kmer(ctx->scan_mode));
+}
+
 static int ensure_slot_runs(fxg_ctx *ctx, Slot &s)
 {
-    size_t want = std::min<size_t>(ctx->rec_cap / 2 + 2, (size_t)1 << 26);
+    // plain: a run needs a selected record and an unselected one behind it; routed: every selected record is a run
+    size_t want = std::min<size_t>(routed(ctx) ? ctx->rec_cap + 2 : ctx->rec_cap / 2 + 2, (size_t)1 << 26);
     cudaError_t e;
     if (s.d_runs_cap < want) {
         if ((e = dev_realloc(s.d_runs, want)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc runs");
+        if (routed(ctx) && (e = dev_realloc(s.d_run_pid, want)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc run pattern ids");
         s.d_runs_cap = want;
+    }
+    if (routed(ctx) && s.h_run_pid_cap < kRunPrefix) {
+        if ((e = host_realloc(s.h_run_pid, kRunPrefix)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned run pattern ids");
+        s.h_run_pid_cap = kRunPrefix;
     }
     if (s.h_runs_cap < kRunPrefix) {
         if ((e = host_realloc(s.h_runs, kRunPrefix)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned runs");
@@ -483,6 +499,8 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
 {
     int rc;
     if (!ctx->have_patterns) return set_error(ctx, FXG_ERR_STATE, "fxg_set_patterns has not been called");
+    if (ctx->cfg.route_runs && !ctx->cfg.invert && !ctx->cfg.count_only && !fxg_can_route(ctx))
+        return set_error(ctx, FXG_ERR_UNSUPPORTED, "route_runs: this pattern set is not served by a fused matcher (see fxg_can_route)");
     if ((rc = ensure_scan_capacity(ctx, nbytes)) != FXG_OK) return rc;
     if ((rc = ensure_slot_result(ctx, s)) != FXG_OK) return rc;
     const bool emit = !ctx->cfg.count_only;
@@ -523,7 +541,12 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     const bool field_stage = P.mode == kModeIndex && !literal;
     if (field_stage) { P.fld_off = ctx->d_fld_off; P.fld_len = ctx->d_fld_len; }
     P.header_whole = ctx->cfg.mode == FXG_MODE_EXACT && ctx->cfg.target == FXG_TARGET_NAME;
-    if (mode_is_kmer(P.mode)) { P.kmer = ctx->kt; P.cand = ctx->d_cand; P.tile_ncand = ctx->d_tile_ncand; P.cand_cap = kKmerCandCap; }
+    if (mode_is_kmer(P.mode)) { P.kmer = ctx->kt; P.cand = ctx->d_cand; P.tile_ncand = ctx->d_tile_ncand; P.cand_cap = ctx->tile_bytes / kKmerCandDiv; }
+    const bool route = routed(ctx);
+    if (route) {
+        FXG_CUDA_OK(cudaMemsetAsync(ctx->d_rec_first, 0xff, rec_cap * sizeof(unsigned long long), st));
+        P.rec_first = ctx->d_rec_first;
+    }
     if (P.mode == kModeExact) {
         P.exact = ExactDevice{ctx->d_bkt, ctx->d_key_words, ctx->exact_mask, ctx->d_exact_pre, ctx->exact_pre_mask};
         P.keyhash = ctx->d_keyhash;
@@ -553,11 +576,12 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
         int inv = ctx->cfg.invert ? 1 : 0;
         if (literal && ctx->h_lit.all_match) inv ^= 1;     // every record matches: hit bits stay 0
         FXG_CUDA_OK(launch_compact(ctx->d_hitbits, P, ctx->d_ctr, rec_cap, ctx->d_block_sums, ctx->d_counts,
-                                   s.d_runs, s.d_runs_cap, inv, st, &ctx->last_launches));
+                                   s.d_runs, s.d_runs_cap, inv, route ? s.d_run_pid : nullptr, st, &ctx->last_launches));
         if (ctx->profiling) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
         FXG_CUDA_OK(cudaMemcpyAsync(s.h_counts, ctx->d_counts, 16, cudaMemcpyDeviceToHost, st));
         s.runs_copied = std::min<size_t>(kRunPrefix, s.d_runs_cap);
         FXG_CUDA_OK(cudaMemcpyAsync(s.h_runs, s.d_runs, s.runs_copied * sizeof(fxg_run), cudaMemcpyDeviceToHost, st));
+        if (route) FXG_CUDA_OK(cudaMemcpyAsync(s.h_run_pid, s.d_run_pid, s.runs_copied * sizeof(int), cudaMemcpyDeviceToHost, st));
     }
     if (ctx->profiling && !s.timed) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
     FXG_CUDA_OK(cudaMemcpyAsync(s.h_ctr, ctx->d_ctr, sizeof(ScanCounters), cudaMemcpyDeviceToHost, st));
@@ -604,9 +628,22 @@ static int finish_raw(fxg_ctx *ctx, Slot &s, fxg_result *res)
             }
             FXG_CUDA_OK(cudaMemcpy(s.h_runs + from, s.d_runs + from, ((size_t)nr - from) * sizeof(fxg_run), cudaMemcpyDeviceToHost));
             d2h += ((size_t)nr - from) * sizeof(fxg_run);
+            if (routed(ctx)) {
+                size_t pfrom = s.runs_copied;
+                if (s.h_run_pid_cap < nr) {
+                    cudaError_t e;
+                    size_t want = std::max<size_t>((size_t)nr, s.h_run_pid_cap * 2);
+                    if ((e = host_realloc(s.h_run_pid, want)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc pinned run pattern ids");
+                    s.h_run_pid_cap = want;
+                    pfrom = 0;
+                }
+                FXG_CUDA_OK(cudaMemcpy(s.h_run_pid + pfrom, s.d_run_pid + pfrom, ((size_t)nr - pfrom) * sizeof(int), cudaMemcpyDeviceToHost));
+                d2h += ((size_t)nr - pfrom) * sizeof(int);
+            }
             s.runs_copied = (size_t)nr;
         }
         res->n_runs = nr; res->runs = s.h_runs;
+        if (routed(ctx)) { res->run_pattern_id = s.h_run_pid; d2h += std::min<size_t>(kRunPrefix, (size_t)nr) * sizeof(int); }
     }
     ctx->last_d2h_bytes = d2h;
     return FXG_OK;
@@ -662,6 +699,8 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h_ctr) cudaFreeHost(s.h_ctr);
         if (s.h_counts) cudaFreeHost(s.h_counts);
         if (s.h_runs) cudaFreeHost(s.h_runs);
+        if (s.h_run_pid) cudaFreeHost(s.h_run_pid);
+        if (s.d_run_pid) cudaFree(s.d_run_pid);
         if (s.h_flags) cudaFreeHost(s.h_flags);
         if (s.h_pid) cudaFreeHost(s.h_pid);
         if (s.h_off) cudaFreeHost(s.h_off);
@@ -671,7 +710,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h2d_done) cudaEventDestroy(s.h2d_done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_exact_pre, ctx->d_keyhash, ctx->d_cand, ctx->d_tile_ncand, ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
+    void *dev[] = {ctx->d_rec_first, ctx->d_exact_pre, ctx->d_keyhash, ctx->d_cand, ctx->d_tile_ncand, ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
                    ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
@@ -726,10 +765,14 @@ extern "C" int fxg_set_patterns(fxg_ctx *ctx, const uint8_t *blob, const uint32_
             mode = kModeKmer + lg;
         }
     } else if (!ctx->two_stage) mode = kModeExact;
-    if (mode != ctx->scan_mode || !ctx->tile_bytes) {         // geometry may change: tile tables are re-made on the next batch
-        ctx->scan_mode = mode;
-        scan_geometry(mode, &ctx->tile_bytes, &ctx->nl_stride, &ctx->hit_words);
-        ctx->cap_bytes = 0;
+    {
+        int tb = 0, ns = 0, hw = 0;
+        scan_geometry(mode, ctx->kt_ok ? ctx->kt.filter_log2_words : 0, &tb, &ns, &hw);
+        if (mode != ctx->scan_mode || tb != ctx->tile_bytes) {   // geometry may change: tile tables are re-made on the next batch
+            ctx->scan_mode = mode;
+            ctx->tile_bytes = tb; ctx->nl_stride = ns; ctx->hit_words = hw;
+            ctx->cap_bytes = 0;
+        }
     }
     ctx->have_patterns = true;
     return FXG_OK;
@@ -958,6 +1001,11 @@ extern "C" int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res)
     return rc;
 }
 
+extern "C" int fxg_can_route(const fxg_ctx *ctx)
+{
+    return ctx && ctx->have_patterns && (ctx->scan_mode == kModeExact || mode_is_kmer(ctx->scan_mode)) &&
+           ctx->npat < (1u << 24) ? 1 : 0;
+}
 extern "C" int fxg_last_launch_count(const fxg_ctx *ctx) { return ctx ? ctx->last_launches : 0; }
 extern "C" uint64_t fxg_last_d2h_bytes(const fxg_ctx *ctx) { return ctx ? ctx->last_d2h_bytes : 0; }
 

@@ -15,12 +15,19 @@ int set_cuda_error(fxg_ctx *ctx, cudaError_t e, const char *what);
 // The scan kernel is compiled for two tile geometries (template parameter of scan_tiles_kernel):
 //   G24  24 KiB tiles, 12 warps, 3 CTAs / SM   literal, exact and index-only passes
 //   G32  32 KiB tiles, 16 warps, 2 CTAs / SM   fused window matcher with a 32 KiB filter in shared memory
-//   G32W 32 KiB tiles, 32 warps, 1 CTA / SM    ... with the 128 KiB filter (large pattern sets)
+//   G16D 16 KiB tiles, 2 x 16 warps, 1 CTA / SM ... with the 128 KiB filter (large pattern sets): the filter leaves room
+//                                              for one CTA only, and a single CTA idles the SM at each of its block
+//                                              barriers -- so its 32 warps form two groups that work on different
+//                                              tiles and synchronise separately (named barriers), like two CTAs would
+//   G16  16 KiB tiles, 16 warps                the REDO launch of G16D batches
 // Every warp owns a contiguous 2 KiB segment of its tile in both.  Kernels downstream of the scan (prefix,
 // finalize, compaction) read the geometry of the batch from ScanParams at run time.
-template <int TILE_BYTES, int THREADS, int MIN_CTAS> struct Geom {
-    static constexpr int kTileBytes = TILE_BYTES;           // bytes of input one CTA scans per step
-    static constexpr int kThreads = THREADS;
+template <int TILE_BYTES, int THREADS, int MIN_CTAS, int GROUPS = 1> struct Geom {
+    static constexpr int kTileBytes = TILE_BYTES;           // bytes of input one group of warps scans per step
+    static constexpr int kThreads = THREADS;                 // threads of one group
+    static constexpr int kGroups = GROUPS;                   // independent groups per CTA: own tiles, own named barrier,
+                                                             // own shared-memory block; they share the matcher's filter
+    static constexpr int kCtaThreads = THREADS * GROUPS;
     static constexpr int kMinCtas = MIN_CTAS;                // resident CTAs per SM the kernel is compiled for
     static constexpr int kChunks = TILE_BYTES / 16;          // 16-byte chunks per tile
     static constexpr int kWarps = THREADS / 32;
@@ -36,9 +43,10 @@ template <int TILE_BYTES, int THREADS, int MIN_CTAS> struct Geom {
 };
 typedef Geom<24576, 384, 3> G24;
 typedef Geom<32768, 512, 2> G32;
-typedef Geom<32768, 1024, 1> G32W;
+typedef Geom<16384, 512, 1, 2> G16D;
+typedef Geom<16384, 512, 2> G16;
 constexpr int kCandCap = 512;                  // literal candidates queued per tile pass
-constexpr int kKmerCandCap = 512;              // window matcher: filter hits listed per tile for kmer_resolve_kernel
+constexpr int kKmerCandDiv = 64;               // window matcher: a tile lists up to tile bytes / 64 filter hits for kmer_resolve_kernel
 
 // ---------------------------------------------------------------- per-tile results
 // The scan kernel has no cross-tile dependency: every tile publishes its '\n' count, its
@@ -194,6 +202,10 @@ struct ScanParams {
     int cand_cap;                     // list capacity per tile
     ExactDevice exact;                // mode == kModeExact
     unsigned long long *keyhash;      // [ntiles * nl_stride / 4] exact mode: key hash of the target line with local index 4j + first
+    // per-pattern output routing (cfg.route_runs): first reported hit of every record, min-reduced; all ones = none.
+    // EXACT: the pattern id.  MULTI: (end offset of the occurrence in its line << 40) | ((0xffff - pattern length)
+    // << 24) | pattern id -- smallest end offset first, then the longest pattern (oracle/fxo_ac.h).
+    unsigned long long *rec_first;    // [rec_cap] or nullptr
     // field table for the second-stage matchers (multi without k-mer index): target field of record k
     unsigned long long *fld_off;      // [rec_cap] or nullptr
     unsigned int *fld_len;            // [rec_cap]
@@ -300,13 +312,13 @@ struct LiteralFieldParams {
 
 
 // launchers (fxg_scan.cu / fxg_fields.cu / fxg_synth.cu)
-void scan_geometry(int mode, int *tile_bytes, int *nl_stride, int *hit_words);
+void scan_geometry(int mode, int filter_log2_words, int *tile_bytes, int *nl_stride, int *hit_words);
 cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launches, cudaEvent_t after_scan);
 cudaError_t launch_scan_kmer(const ScanParams &P, cudaStream_t stream, int dev);
 cudaError_t launch_scan_kmer_redo(const ScanParams &P, cudaStream_t stream, int dev);
 cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
-                           fxg_run *runs, unsigned long long run_cap, int invert, cudaStream_t stream, int *launches);
+                           fxg_run *runs, unsigned long long run_cap, int invert, int *run_pid, cudaStream_t stream, int *launches);
 cudaError_t launch_fields_literal(const FieldSrc &src, unsigned long long n, const LiteralFieldParams &L,
                                   const FieldOut &O, cudaStream_t st);
 cudaError_t launch_fields_ac(const FieldSrc &src, unsigned long long n, const AcDevice &A, const FieldOut &O, cudaStream_t st);

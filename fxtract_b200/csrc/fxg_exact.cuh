@@ -124,6 +124,59 @@ __device__ __forceinline__ bool exact_probe(const ExactDevice &E, unsigned long 
     }
 }
 
+// Look-up of a key whose hash h is already known (exact_resolve_kernel: the scan kernel hashed it from the staged
+// tile).  The key is text[ks, ke) -- or, with `name`, text[ks, first ' ' in [ks, ke)) -- of the batch in global
+// memory.  Pre-filter, bucket, and for a fingerprint match the candidate key (its length comes from the table) is
+// compared with the text in place, 8 bytes per step; nothing is hashed again.
+__device__ __forceinline__ bool exact_verify_hashed(const ExactDevice &E, unsigned long long h, const uint8_t *buf, long long ks,
+                                                    long long ke, bool name, int &pid)
+{
+    if (E.pre) {
+        const unsigned int m = exact_pre_mask(h);
+        if ((__ldg(E.pre + exact_pre_word(h, E.pre_mask)) & m) != m) return false;
+    }
+    unsigned int bkt = (unsigned int)h & E.mask;
+    const unsigned int fp = (unsigned int)(h >> 32) | 1u;
+    for (;;) {
+        const uint4 *B = E.bkt + 4 * (size_t)bkt;
+        const uint4 q0 = __ldg(B), q1 = __ldg(B + 1), q2 = __ldg(B + 2), q3 = __ldg(B + 3);
+        const unsigned int fps[8] = {q0.x, q0.z, q1.x, q1.z, q2.x, q2.z, q3.x, q3.z};
+        const unsigned int offs[8] = {q0.y, q0.w, q1.y, q1.w, q2.y, q2.w, q3.y, q3.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            if (fps[e] != fp) continue;
+            const unsigned long long *kw = E.kw + offs[e];
+            const unsigned long long meta = __ldg(kw);
+            const unsigned int len = (unsigned int)meta;
+            if (name) {
+                if (ks + (long long)len > ke) continue;
+                if (ks + (long long)len < ke && buf[ks + len] != ' ') continue;      // the name goes on
+            } else if ((long long)len != ke - ks) continue;
+            const uintptr_t a = (uintptr_t)(buf + ks);
+            const unsigned int *w32 = reinterpret_cast<const unsigned int *>(a & ~(uintptr_t)3);
+            const int sh = (int)(a & 3) * 8;
+            const unsigned int limit = (unsigned int)(((a & 3) + len + 3) >> 2);      // words that hold key bytes
+            bool eq = true;
+            unsigned int wi = 0;
+            unsigned int g0 = limit ? __ldg(w32) : 0u;
+            for (unsigned int o = 0; o < len; o += 8, wi += 2) {
+                const unsigned int g1 = wi + 1 < limit ? __ldg(w32 + wi + 1) : 0u, g2 = wi + 2 < limit ? __ldg(w32 + wi + 2) : 0u;
+                unsigned long long w = (unsigned long long)__funnelshift_r(g0, g1, sh) | ((unsigned long long)__funnelshift_r(g1, g2, sh) << 32);
+                if (len - o < 8) w &= (1ull << (8 * (len - o))) - 1ull;
+                if (w != __ldg(kw + 1 + (o >> 3))) { eq = false; break; }
+                if (name) {                                                           // a key with a ' ' is no read name
+                    const unsigned long long x = w ^ 0x2020202020202020ull;
+                    if ((x - 0x0101010101010101ull) & ~x & 0x8080808080808080ull) { eq = false; break; }
+                }
+                g0 = g2;
+            }
+            if (eq) { pid = (int)(meta >> 32); return true; }
+        }
+        if (q3.z == 0u) return false;                      // the bucket has a free slot: nothing spilled past it
+        bkt = (bkt + 1) & E.mask;
+    }
+}
+
 template <class LD>
 __device__ __forceinline__ bool exact_lookup(const ExactDevice &E, const LD &ld, long long start, unsigned int len,
                                              bool stop_at_space, int &pid)

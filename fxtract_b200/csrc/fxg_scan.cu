@@ -167,9 +167,11 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
     // tile's first '\n' (it starts in an earlier tile, or exactly at the tile's first byte) is done here
     if (P.mode == kModeExact && n_tab > 0 && r == target_role(P.target)) {
         const long long ls = V.prev_nl(t, 1) + 1;
-        if (exact_line_global(P, ls, V.nl(t, 0))) {
+        int pid = -1;
+        if (exact_line_global(P, ls, V.nl(t, 0), pid)) {
             const unsigned long long rec = lb >> 2;
             if (rec < P.rec_cap) {
+                if (P.rec_first) P.rec_first[rec] = (unsigned long long)(unsigned int)pid;
                 const unsigned int bit = 1u << (rec & 31);
                 const unsigned int old = atomicOr(&P.hitbits[rec >> 5], bit);
                 if (!(old & bit)) atomicAdd(&P.ctr->n_hits, 1ull);
@@ -268,10 +270,21 @@ __global__ void __launch_bounds__(256) exact_resolve_kernel(const ScanParams P)
     for (int i = first + 4 * lane; i < n_tab; i += 128) {
         if (i < 1) continue;
         const unsigned long long h = __ldg(kh + (i >> 2));
-        if (!exact_fingerprint_present(P.exact, h)) continue;
-        if (!exact_line_global(P, V.nl(t, i - 1) + 1, V.nl(t, i))) continue;
+        int pid = -1;
+        if (P.target == FXG_TARGET_COMMENT) {              // the key starts behind the first ' ': found by the slow path
+            if (!exact_fingerprint_present(P.exact, h)) continue;
+            if (!exact_line_global(P, V.nl(t, i - 1) + 1, V.nl(t, i), pid)) continue;
+        } else {
+            if (P.exact.pre) {                             // pre-filter first: the line's bounds are only read for the few that pass
+                const unsigned int m = exact_pre_mask(h);
+                if ((__ldg(P.exact.pre + exact_pre_word(h, P.exact.pre_mask)) & m) != m) continue;
+            }
+            const bool name = P.target == FXG_TARGET_NAME;
+            if (!exact_verify_hashed(P.exact, h, P.buf, V.nl(t, i - 1) + 1 + (name ? 1 : 0), V.nl(t, i), name, pid)) continue;
+        }
         const unsigned long long rec = (lb + (unsigned long long)i) >> 2;
         if (rec >= P.rec_cap) continue;
+        if (P.rec_first) P.rec_first[rec] = (unsigned long long)(unsigned int)pid;
         const unsigned int bit = 1u << (rec & 31);
         if (!(atomicOr(&P.hitbits[rec >> 5], bit) & bit)) ++fresh;
     }
@@ -283,8 +296,11 @@ __global__ void __launch_bounds__(256) exact_resolve_kernel(const ScanParams P)
 // table bucket, every pattern record that holds a window with this hash at one of its first S offsets compared with
 // the batch text, the occurrence's line found in the tile's '\n' table, kept if that line has the target's role.
 // A tile whose list overflowed (kCandOverflow: pattern-dense text) has every probe position walked here instead.
-__device__ __forceinline__ bool window_lookup(const ScanParams &P, unsigned int h, long long win)
+// `best` (routing): every occurrence through this window is examined and the smallest (end offset, 0xffff - length,
+// pattern id) triple is kept; without it the first verified occurrence ends the walk.
+__device__ __forceinline__ bool window_lookup(const ScanParams &P, unsigned int h, long long win, long long *best_end, unsigned long long *best_low)
 {
+    bool any = false;
     const KmerTile &K = P.kmer;
     unsigned int bkt = kmer_tile_bucket(h, K.ht_mask);
     for (;;) {
@@ -303,9 +319,15 @@ __device__ __forceinline__ bool window_lookup(const ScanParams &P, unsigned int 
             bool eq = true;
             for (unsigned int i = 0; i < m; ++i)
                 if (P.buf[p + i] != __ldg(pb + i)) { eq = false; break; }
-            if (eq) return true;
+            if (!eq) continue;
+            if (!best_end) return true;
+            any = true;
+            const unsigned long long low = ((unsigned long long)(0xffffu - (m < 0xffffu ? m : 0xffffu)) << 24) |
+                                           (unsigned long long)(__ldg(reinterpret_cast<const unsigned int *>(rec) + 1) & 0xffffffu);
+            const long long end = p + (long long)m;
+            if (end < *best_end || (end == *best_end && low < *best_low)) { *best_end = end; *best_low = low; }
         }
-        if (vv.w == 0u) return false;                        // the bucket has a free slot: nothing spilled past it
+        if (vv.w == 0u) return any;                          // the bucket has a free slot: nothing spilled past it
         bkt = (bkt + 1) & K.ht_mask;
     }
 }
@@ -330,34 +352,65 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
     const unsigned int tile_len = left < (unsigned long long)P.tile_bytes ? (unsigned int)left : (unsigned int)P.tile_bytes;
     const unsigned int nc = overflow ? (tile_len + (unsigned int)K.stride - 1u) / (unsigned int)K.stride : nc_raw;
     unsigned int fresh = 0;
-    for (unsigned int c = lane; c < nc; c += 32) {
-        unsigned int h;
-        int win_rel;
-        if (!overflow) {
-            const uint2 cd = __ldg(list + c);
-            h = cd.x; win_rel = (int)cd.y;
-        } else {
-            win_rel = (int)(c * (unsigned int)K.stride);
-            const unsigned long long g = base + (unsigned long long)win_rel;
-            if (g + (unsigned long long)K.k > P.nbytes) continue;      // a window inside an occurrence lies inside the batch
-            unsigned int w[4] = {0u, 0u, 0u, 0u};
-            for (int i = 0; i < K.k; ++i) w[i >> 2] |= (unsigned int)P.buf[g + i] << (8 * (i & 3));
-            h = window_hash(w[0], w[1], w[2], w[3]);
+    // two candidates per lane and round: their list entries and table buckets are fetched before either is examined
+    // (the walk is a chain of dependent loads; its latency, not its volume, is what the kernel waits for)
+    for (unsigned int c0 = lane; c0 < nc; c0 += 64) {
+        unsigned int hh[2];
+        int wr[2];
+        bool live[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const unsigned int c = c0 + 32u * (unsigned int)u;
+            live[u] = c < nc;
+            hh[u] = 0; wr[u] = 0;
+            if (!live[u]) continue;
+            if (!overflow) {
+                const uint2 cd = __ldg(list + c);
+                hh[u] = cd.x; wr[u] = (int)cd.y;
+            } else {
+                wr[u] = (int)(c * (unsigned int)K.stride);
+                const unsigned long long g = base + (unsigned long long)wr[u];
+                if (g + (unsigned long long)K.k > P.nbytes) { live[u] = false; continue; }   // a window inside an occurrence lies inside the batch
+                unsigned int w[4] = {0u, 0u, 0u, 0u};
+                for (int i = 0; i < K.k; ++i) w[i >> 2] |= (unsigned int)P.buf[g + i] << (8 * (i & 3));
+                hh[u] = window_hash(w[0], w[1], w[2], w[3]);
+            }
         }
-        if (!window_lookup(P, h, (long long)base + win_rel)) continue;
-        // local line of the occurrence = number of '\n' before the window (a pattern holds no '\n', so all of it
-        // lies on the line of its window)
-        int lo = 0, hi = n_tab;
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            if ((int)nl[mid] < win_rel) lo = mid + 1; else hi = mid;
+        uint4 kk[2], vv[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const unsigned int bkt = kmer_tile_bucket(hh[u], K.ht_mask);
+            kk[u] = __ldg(K.ht + 2 * (size_t)bkt); vv[u] = __ldg(K.ht + 2 * (size_t)bkt + 1);
         }
-        const unsigned long long line = lb + (unsigned long long)lo;
-        if ((int)(line & 3ull) != trole) continue;
-        const unsigned long long r = line >> 2;
-        if (r >= P.rec_cap) continue;
-        const unsigned int bit = 1u << (r & 31);
-        if (!(atomicOr(&P.hitbits[r >> 5], bit) & bit)) ++fresh;
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            if (!live[u]) continue;
+            // most candidates end here: no entry of the first bucket carries the hash and the bucket is not full
+            const bool maybe = kk[u].x == hh[u] || kk[u].y == hh[u] || kk[u].z == hh[u] || kk[u].w == hh[u] || vv[u].w != 0u;
+            if (!maybe) continue;
+            long long best_end = 0x7fffffffffffffffll;       // batch offset of the end of the first reported occurrence
+            unsigned long long best_low = ~0ull;
+            if (!window_lookup(P, hh[u], (long long)base + wr[u], P.rec_first ? &best_end : nullptr, &best_low)) continue;
+            // local line of the occurrence = number of '\n' before the window (a pattern holds no '\n', so all of it
+            // lies on the line of its window)
+            int lo = 0, hi = n_tab;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if ((int)nl[mid] < wr[u]) lo = mid + 1; else hi = mid;
+            }
+            const unsigned long long line = lb + (unsigned long long)lo;
+            if ((int)(line & 3ull) != trole) continue;
+            const unsigned long long r = line >> 2;
+            if (r >= P.rec_cap) continue;
+            const unsigned int bit = 1u << (r & 31);
+            if (!(atomicOr(&P.hitbits[r >> 5], bit) & bit)) ++fresh;
+            if (P.rec_first) {
+                // end offset relative to the start of the line (which may lie in an earlier tile)
+                const long long ls = lo >= 1 ? (long long)base + nl[lo - 1] + 1 : V.prev_nl(t, 1) + 1;
+                const unsigned long long end_rel = (unsigned long long)(best_end - ls);
+                atomicMin(&P.rec_first[r], ((end_rel < 0xffffffull ? end_rel : 0xffffffull) << 40) | (best_low & 0xffffffffffull));
+            }
+        }
     }
     fresh = __reduce_add_sync(0xffffffffu, fresh);
     if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
@@ -385,9 +438,10 @@ cudaError_t scan_launch_config(const void *func, int threads, size_t smem, int d
     return cudaSuccess;
 }
 
-void scan_geometry(int mode, int *tile_bytes, int *nl_stride, int *hit_words)
+void scan_geometry(int mode, int filter_log2_words, int *tile_bytes, int *nl_stride, int *hit_words)
 {
-    if (mode_is_kmer(mode)) { *tile_bytes = G32::kTileBytes; *nl_stride = G32::kMaxTileLines; *hit_words = G32::kHitWords; }
+    if (mode_is_kmer(mode) && filter_log2_words > 13) { *tile_bytes = G16D::kTileBytes; *nl_stride = G16D::kMaxTileLines; *hit_words = G16D::kHitWords; }
+    else if (mode_is_kmer(mode)) { *tile_bytes = G32::kTileBytes; *nl_stride = G32::kMaxTileLines; *hit_words = G32::kHitWords; }
     else { *tile_bytes = G24::kTileBytes; *nl_stride = G24::kMaxTileLines; *hit_words = G24::kHitWords; }
 }
 
@@ -465,6 +519,7 @@ struct CompactParams {
     fxg_run *runs;
     unsigned long long run_cap;
     int invert;
+    int *run_pid;                   // routing: every selected record is its own run; pattern id per run (P.rec_first)
 };
 constexpr int kCompactThreads = 1024;
 
@@ -492,7 +547,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_count_kernel(const Co
     const unsigned long long w = (unsigned long long)blockIdx.x * kCompactThreads + threadIdx.x;
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
-    unsigned int starts = s & ~((s << 1) | prev_msb);
+    unsigned int starts = C.run_pid ? s : s & ~((s << 1) | prev_msb);
     unsigned long long a = __popc(starts), b = __popc(s);
     for (int d = 16; d > 0; d >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, d); b += __shfl_xor_sync(0xffffffffu, b, d); }
     if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = b; }
@@ -543,8 +598,8 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
     unsigned int next_lsb = sel_word(C, w + 1, nrec) & 1u;
-    unsigned int starts = s & ~((s << 1) | prev_msb);
-    unsigned int ends = s & ~((s >> 1) | (next_lsb << 31));
+    unsigned int starts = C.run_pid ? s : s & ~((s << 1) | prev_msb);
+    unsigned int ends = C.run_pid ? s : s & ~((s >> 1) | (next_lsb << 31));
     unsigned long long n = __popc(starts), inc = n;
     for (int d = 1; d < 32; d <<= 1) { unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d); if ((threadIdx.x & 31) >= d) inc += o; }
     if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
@@ -560,7 +615,13 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
         m &= m - 1;
         unsigned long long rec = w * 32ull + b;
         if (starts & (1u << b)) {
-            if (opened < C.run_cap) C.runs[opened].off = offset_after_line(C.P, 4ll * (long long)rec - 1);
+            if (opened < C.run_cap) {
+                C.runs[opened].off = offset_after_line(C.P, 4ll * (long long)rec - 1);
+                if (C.run_pid) {
+                    const unsigned long long f = C.P.rec_first[rec];
+                    C.run_pid[opened] = f == ~0ull ? -1 : (int)(f & 0xffffffull);
+                }
+            }
             ++opened;
         }
         if (ends & (1u << b)) {
@@ -580,11 +641,11 @@ __global__ void compact_fixup_kernel(const CompactParams C)
 
 cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
-                           fxg_run *runs, unsigned long long run_cap, int invert, cudaStream_t stream, int *launches)
+                           fxg_run *runs, unsigned long long run_cap, int invert, int *run_pid, cudaStream_t stream, int *launches)
 {
     CompactParams C;
     C.hitbits = hitbits; C.P = P; C.ctr = ctr; C.block_sums = block_sums;
-    C.out_counts = out_counts; C.runs = runs; C.run_cap = run_cap; C.invert = invert;
+    C.out_counts = out_counts; C.runs = runs; C.run_cap = run_cap; C.invert = invert; C.run_pid = run_pid;
     unsigned long long words = (rec_cap + 31) / 32;
     unsigned int nblocks = (unsigned int)((words + kCompactThreads - 1) / kCompactThreads);
     if (nblocks == 0) nblocks = 1;

@@ -350,7 +350,7 @@ __device__ __forceinline__ unsigned long long exact_line_hash_tile(const ScanPar
     return exact_hash(ld, (long long)ks, (unsigned int)(ke - ks), stop, keylen);
 }
 // the same over global memory: line = batch bytes [a, e)
-__device__ __forceinline__ bool exact_line_global(const ScanParams &P, long long a, long long e)
+__device__ __forceinline__ bool exact_line_global(const ScanParams &P, long long a, long long e, int &pid)
 {
     long long ks = a, ke = e;
     bool stop = false;
@@ -361,7 +361,6 @@ __device__ __forceinline__ bool exact_line_global(const ScanParams &P, long long
         ks = sp;
     }
     if (ks > ke) ks = ke;
-    int pid;
     return exact_lookup_global(P.exact, P.buf + ks, (unsigned int)(ke - ks), stop, pid);
 }
 
@@ -398,7 +397,7 @@ __device__ __forceinline__ unsigned int class_bad(const ScanSmem<G> &S, const ui
 // guessed line phase turned out wrong (exact mode: also the tiles without anchor): those are re-evaluated with the
 // phase-free per-line path, exact-mode hashes under the true phase.
 template <class G, int MODE, bool REDO>
-__global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(const ScanParams P)
+__global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel(const ScanParams P)
 {
     constexpr int kTileBytes = G::kTileBytes, kThreads = G::kThreads, kChunks = G::kChunks, kWarps = G::kWarps;
     constexpr int kWarpChunks = G::kWarpChunks, kChunksPerThread = G::kChunksPerThread, kMaxTileLines = G::kMaxTileLines;
@@ -410,15 +409,25 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     constexpr int SB = KMER ? (1 << (MODE - kModeKmer)) : 16;          // probe stride in bytes
     constexpr int NPROBE = 16 / SB;
     constexpr bool HITS = LIT && !REDO;                                // this launch produces line-hit words
+    constexpr int kGroups = G::kGroups;
     typedef ScanSmem<G> Smem;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem &S = *reinterpret_cast<Smem *>(smem_raw);
-    unsigned int *filt = reinterpret_cast<unsigned int *>(smem_raw + sizeof(Smem));   // window filter (dynamic tail), or
-    LitSmem &LS = *reinterpret_cast<LitSmem *>(smem_raw + sizeof(Smem));              // the literal tables
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // a CTA is kGroups independent groups of kThreads threads: everything below -- tid, warp, S, the tile loop, the
+    // barriers -- is per group; only the matcher's filter behind the groups' blocks is shared
+    const int gid = kGroups > 1 ? (int)threadIdx.x / kThreads : 0;
+    Smem &S = reinterpret_cast<Smem *>(smem_raw)[gid];
+    unsigned int *filt = reinterpret_cast<unsigned int *>(smem_raw + kGroups * sizeof(Smem));   // window filter (dynamic tail), or
+    LitSmem &LS = *reinterpret_cast<LitSmem *>(smem_raw + kGroups * sizeof(Smem));              // the literal tables
+    const int tid = (int)threadIdx.x - gid * kThreads, lane = tid & 31, warp = tid >> 5;
     const LiteralTable *lit = P.lit;
     const unsigned long long n_work = REDO ? (unsigned long long)*P.redo_count : P.ntiles;
-    if ((unsigned long long)blockIdx.x >= n_work) return;
+    if ((unsigned long long)blockIdx.x * kGroups >= n_work) return;
+    const unsigned long long k_first = (unsigned long long)blockIdx.x * kGroups + gid, k_step = (unsigned long long)gridDim.x * kGroups;
+#define FXG_GROUP_SYNC()                                                                                                 \
+    do {                                                                                                                \
+        if (kGroups == 1) __syncthreads();                                                                              \
+        else asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "n"(kThreads) : "memory");                                 \
+    } while (0)
 #define FXG_TILE_OF(k) (REDO ? (unsigned long long)P.redo_list[(k)] : (unsigned long long)(k))
     // issue the bulk copy of tile `tt` into buffer `bf` (thread 0); in k-mer mode with the 16 bytes that follow it
     constexpr unsigned int kFetch = (unsigned int)kTileBytes + ((KMER && SB < 16) ? 16u : 0u);
@@ -438,8 +447,10 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     if (tid == 0) {
         mbar_init(&S.mbar[0], 1);
         mbar_init(&S.mbar[1], 1);
-        const unsigned long long t0 = FXG_TILE_OF(blockIdx.x);
-        FXG_ISSUE_TILE(t0, 0);
+        if (k_first < n_work) {
+            const unsigned long long t0 = FXG_TILE_OF(k_first);
+            FXG_ISSUE_TILE(t0, 0);
+        }
         reset_state(S.st[0]);
         reset_state(S.st[1]);
     }
@@ -460,17 +471,17 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         const int nw = 1 << P.kmer.filter_log2_words;
         const uint4 *src = reinterpret_cast<const uint4 *>(P.kmer.filter);
         uint4 *dst = reinterpret_cast<uint4 *>(filt);
-        for (int w = tid; w < nw / 4; w += kThreads) dst[w] = __ldg(src + w);
+        for (int w = (int)threadIdx.x; w < nw / 4; w += G::kCtaThreads) dst[w] = __ldg(src + w);
     }
     const unsigned int one = P.one;
     const unsigned int lt_mask = (1u << lane) - 1u;
     unsigned short *my_list = S.wl[warp];
     unsigned short *my_mask = S.wm[warp];
     const int trole = target_role(P.target);
-    __syncthreads();
+    __syncthreads();                     // the whole CTA: the filter is staged by every thread
 
     unsigned int it = 0;
-    for (unsigned long long k = blockIdx.x; k < n_work; k += gridDim.x, ++it) {
+    for (unsigned long long k = k_first; k < n_work; k += k_step, ++it) {
         const unsigned long long t = FXG_TILE_OF(k);
         const int cur = (int)(it & 1u);
         const uint4 *tile = S.tile[cur];
@@ -485,7 +496,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         //      previous iteration); reset the other copy of the per-tile scalars
         if (tid == 0) {
             if (it) reset_state(S.st[cur ^ 1]);
-            const unsigned long long kn = k + gridDim.x;
+            const unsigned long long kn = k + k_step;
             if (kn < n_work) {
                 const unsigned long long tn = FXG_TILE_OF(kn);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -501,7 +512,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                 }
                 S.tile[cur][b >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
             }
-            __syncthreads();
+            FXG_GROUP_SYNC();
         }
         if (bulk) mbar_wait(&S.mbar[cur], (it >> 1) & 1u);
 
@@ -561,14 +572,22 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                         const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h) | __funnelshift_l(0x00000101u, 0x00000101u, h >> 5);
                         if ((m & ~fw) == 0u) hits |= 1u << q;
                     }
-                    if (__any_sync(0xffffffffu, hits != 0u)) {        // filter hits are rare: listed for kmer_resolve_kernel
+                    // filter hits go to the tile's list for kmer_resolve_kernel: one shared-memory atomic per warp
+                    // and step (the slots of the step are dealt out by ballot rank); one vote when nothing hit
+                    if (__any_sync(0xffffffffu, hits != 0u)) {
+                        unsigned int bq[NPROBE], tot = 0;
+#pragma unroll
+                        for (int q = 0; q < NPROBE; ++q) { bq[q] = __ballot_sync(0xffffffffu, (hits >> q) & 1u); tot += __popc(bq[q]); }
+                        unsigned int slot = 0;
+                        if (lane == 0) slot = atomicAdd(&T.n_cand, tot);
+                        slot = __shfl_sync(0xffffffffu, slot, 0);
+                        uint2 *list = P.cand + t * (unsigned long long)P.cand_cap;
 #pragma unroll
                         for (int q = 0; q < NPROBE; ++q) {
-                            if (hits & (1u << q)) {
-                                const unsigned int slot = atomicAdd(&T.n_cand, 1u);
-                                if (slot < (unsigned int)P.cand_cap)
-                                    P.cand[t * (unsigned long long)P.cand_cap + slot] = make_uint2(hs[q], (unsigned int)((c << 4) + q * SB));
-                            }
+                            const unsigned int mine = slot + __popc(bq[q] & lt_mask);
+                            if (((hits >> q) & 1u) && mine < (unsigned int)P.cand_cap)
+                                list[mine] = make_uint2(hs[q], (unsigned int)((c << 4) + q * SB));
+                            slot += __popc(bq[q]);
                         }
                     }
                 }
@@ -589,7 +608,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
             cnt = __reduce_add_sync(0xffffffffu, cnt);
             if (lane == 0) S.wtot[cur][warp] = cnt;
         }
-        __syncthreads();
+        FXG_GROUP_SYNC();
 
         // ---- 3. (warp local) ordered '\n' position table
         unsigned int total;
@@ -637,7 +656,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
         }
         const int n_tab = total < (unsigned int)kMaxTileLines ? (int)total : kMaxTileLines;
         if (total > (unsigned int)kMaxTileLines && tid == 0) note_violation(T, FXG_V_DENSE_LINES);
-        __syncthreads();
+        FXG_GROUP_SYNC();
 
         // ---- 3b. phase anchor: the first line among local lines 1..31 that is exactly "+" (every warp looks
         //          for itself -- cheaper than a block-wide minimum and one more barrier)
@@ -758,7 +777,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
                 }
             }
         }
-        __syncthreads();
+        FXG_GROUP_SYNC();
 
         // ---- 6. publish the tile: count, violations / line-class flags, '\n' table, line hits.  No barrier
         //         after it: the next writers of anything read here (the bulk copy into this buffer, the table,
@@ -788,6 +807,7 @@ __global__ void __launch_bounds__(G::kThreads, G::kMinCtas) scan_tiles_kernel(co
     }
 #undef FXG_TILE_OF
 #undef FXG_ISSUE_TILE
+#undef FXG_GROUP_SYNC
 }
 
 // ---------------------------------------------------------------- launcher (one per instantiation)
@@ -798,13 +818,14 @@ cudaError_t scan_launch_config(const void *func, int threads, size_t smem, int d
 template <class G, int MODE, bool REDO>
 cudaError_t launch_scan_tiles(const ScanParams &P, size_t extra_smem, cudaStream_t stream, int dev, unsigned long long max_grid)
 {
-    const size_t smem = sizeof(ScanSmem<G>) + extra_smem;
+    const size_t smem = G::kGroups * sizeof(ScanSmem<G>) + extra_smem;
     int cap = 0;
-    cudaError_t e = scan_launch_config((const void *)scan_tiles_kernel<G, MODE, REDO>, G::kThreads, smem, dev, &cap);
+    cudaError_t e = scan_launch_config((const void *)scan_tiles_kernel<G, MODE, REDO>, G::kCtaThreads, smem, dev, &cap);
     if (e != cudaSuccess) return e;
-    unsigned long long grid = P.ntiles < (unsigned long long)cap ? P.ntiles : (unsigned long long)cap;
+    const unsigned long long want = (P.ntiles + G::kGroups - 1) / G::kGroups;
+    unsigned long long grid = want < (unsigned long long)cap ? want : (unsigned long long)cap;
     if (max_grid && grid > max_grid) grid = max_grid;
-    scan_tiles_kernel<G, MODE, REDO><<<(unsigned int)grid, G::kThreads, smem, stream>>>(P);
+    scan_tiles_kernel<G, MODE, REDO><<<(unsigned int)grid, G::kCtaThreads, smem, stream>>>(P);
     return cudaGetLastError();
 }
 

@@ -129,6 +129,7 @@ private:
 struct PoolConfig {
     int mode = FXG_MODE_LITERAL, target = FXG_TARGET_SEQ;
     bool invert = false, count_only = false, want_pattern_id = false;
+    bool route_runs = false;        // raw path: per-pattern output files (every selected record its own run + pattern id)
     size_t batch_bytes = 64u << 20;
     std::vector<int> devices;       // CUDA ordinals; batches go round-robin, results come back in order
 };
@@ -140,6 +141,7 @@ public:
     size_t capacity() const { return ctx_.size() * 2; }
     size_t inflight() const { return order_.size(); }
     size_t batch_bytes() const { return cfg_.batch_bytes; }
+    bool can_route() const;                                     // the raw path can name the pattern of every selected record
     void acquire(void **pinned, size_t *cap);                   // next device in turn
     void submit_fields(size_t nbytes, const uint32_t *off, uint32_t n);
     void submit_raw(size_t nbytes, bool is_last);

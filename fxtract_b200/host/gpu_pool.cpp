@@ -32,6 +32,7 @@ void DevicePool::create()
         c.device = dev; c.mode = cfg_.mode; c.target = cfg_.target;
         c.invert = cfg_.invert; c.count_only = cfg_.count_only; c.want_pattern_id = cfg_.want_pattern_id;
         c.batch_bytes = cfg_.batch_bytes;
+        c.route_runs = cfg_.route_runs;
         fxg_ctx *ctx = nullptr;
         if (fxg_create(&c, &ctx) != FXG_OK) fail(nullptr, "cannot open the GPU search path");
         if (fxg_set_patterns(ctx, (const uint8_t *)blob.data(), off.data(), (uint32_t)patterns_.size()) != FXG_OK)
@@ -39,6 +40,12 @@ void DevicePool::create()
         ctx_.push_back(ctx);
     }
     turn_ = 0; lent_ = -1;
+}
+
+bool DevicePool::can_route() const
+{
+    for (fxg_ctx *c : ctx_) if (!fxg_can_route(c)) return false;
+    return !ctx_.empty();
 }
 
 void DevicePool::destroy()

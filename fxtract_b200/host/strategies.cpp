@@ -295,13 +295,21 @@ private:
 
 struct RawPending { const uint8_t *host; uint64_t file_off; size_t nbytes; uint64_t window; };
 
-bool raw_path_allowed(const Job &job, const char *file2)
+// Which form of the raw path an input may take.  Per-pattern output files need the pattern that selected a
+// record -- but only where the reference looks it up: on_match2 returns before manager.find under -v and -c
+// (main.cpp:274-283), hash_search always calls it (main.cpp:315, side effects included), so exact look-ups with
+// files stay on the fields path when -v or -c is given.
+enum RawMode { RAW_NO, RAW_PLAIN, RAW_ROUTED };
+RawMode raw_mode(const Job &job, Strategy st, const char *file2)
 {
     const char *mode = getenv("FXTRACT_PATH");
-    if (mode && !strcmp(mode, "fields")) return false;
+    if (mode && !strcmp(mode, "fields")) return RAW_NO;
     const CliOptions &o = job.opt;
-    if (file2 || o.I || o.l) return false;           // mates and -l need per-pair rules: fields path
-    return job.router.all_stdout();                  // per-pattern output files need first-hit ids: fields path
+    if (file2 || o.I || o.l) return RAW_NO;          // mates and -l need per-pair rules: fields path
+    if (job.router.all_stdout()) return RAW_PLAIN;
+    if (st == S_MULTI && (o.v || o.c)) return RAW_PLAIN;
+    if ((st == S_MULTI || st == S_EXACT) && !o.v && !o.c) return RAW_ROUTED;
+    return RAW_NO;
 }
 
 int reader_threads_from_env()
@@ -340,7 +348,12 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
             if (!r.canonical_ok) { reroute_at = (int64_t)p.file_off; stats.rerouted++; }
             else {
                 if (o.c) job.matched_records += (long)r.n_selected;
-                else write_runs(p.host, r.runs, r.n_runs);
+                else if (r.run_pattern_id) {                          // per-pattern output files (main.cpp:285-287, :315-324)
+                    for (uint64_t k = 0; k < r.n_runs; ++k) {
+                        FILE *out = job.router.find(r.run_pattern_id[k]);
+                        if (out) fwrite(p.host + r.runs[k].off, 1, r.runs[k].len, out);
+                    }
+                } else write_runs(p.host, r.runs, r.n_runs);
                 stats.records += r.n_records;
                 stats.t_write += now_s() - t1;
             }
@@ -477,6 +490,8 @@ int run_input(Job &job, const char *file1, const char *file2)
     pc.mode = st == S_LITERAL ? FXG_MODE_LITERAL : (st == S_MULTI ? FXG_MODE_MULTI : FXG_MODE_EXACT);
     pc.target = fxg_target(o);
     pc.invert = o.v; pc.count_only = o.c; pc.want_pattern_id = st != S_LITERAL;
+    RawMode rm = raw_mode(job, st, file2);
+    pc.route_runs = st != S_LITERAL && !o.v && !o.c && !job.router.all_stdout();
     pc.batch_bytes = batch_bytes_from_env();
     pc.devices = devices_from_env();
     if (!job.pool) job.pool.reset(new DevicePool(pc, pats));     // strategy, flags and patterns are the same for every input
@@ -486,7 +501,8 @@ int run_input(Job &job, const char *file1, const char *file2)
     const auto t0 = std::chrono::steady_clock::now();
     uint64_t input_bytes = 0;
     bool done = false;
-    if (raw_path_allowed(job, file2)) {
+    if (rm == RAW_ROUTED && !pool.can_route()) rm = RAW_NO;       // pattern set not served by a fused matcher
+    if (rm != RAW_NO) {
         int fd = open(file1, O_RDONLY);
         if (fd >= 0) {
             int64_t next = run_raw(job, fd, pool, stats);

@@ -16,7 +16,7 @@ class FxgError(RuntimeError):
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("mode", C.c_int32), ("target", C.c_int32), ("invert", C.c_int32),
                 ("count_only", C.c_int32), ("want_pattern_id", C.c_int32), ("batch_bytes", C.c_uint64),
-                ("stream", C.c_void_p)]
+                ("stream", C.c_void_p), ("route_runs", C.c_int32), ("reserved", C.c_int32)]
 
 
 class Run(C.Structure):
@@ -27,7 +27,8 @@ class Result(C.Structure):
     _fields_ = [("n_records", C.c_uint64), ("n_matched", C.c_uint64), ("n_selected", C.c_uint64),
                 ("n_lines", C.c_uint64), ("consumed_bytes", C.c_uint64), ("canonical_ok", C.c_int32),
                 ("violation", C.c_uint32), ("first_bad_offset", C.c_uint64), ("n_runs", C.c_uint64),
-                ("runs", C.POINTER(Run)), ("flags", C.POINTER(C.c_uint8)), ("pattern_id", C.POINTER(C.c_int32))]
+                ("runs", C.POINTER(Run)), ("flags", C.POINTER(C.c_uint8)), ("pattern_id", C.POINTER(C.c_int32)),
+                ("run_pattern_id", C.POINTER(C.c_int32))]
 
 
 class SynthSpec(C.Structure):
@@ -40,7 +41,7 @@ class SynthSpec(C.Structure):
 EXPORTS = ["fxg_device_count", "fxg_create", "fxg_destroy", "fxg_last_error", "fxg_set_patterns",
            "fxg_acquire_buffer", "fxg_submit_raw", "fxg_submit_raw_from", "fxg_submit_fields", "fxg_collect",
            "fxg_count", "fxg_find_record_cut", "fxg_scan_device_async", "fxg_scan_device_finish",
-           "fxg_last_launch_count", "fxg_last_d2h_bytes", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
+           "fxg_can_route", "fxg_last_launch_count", "fxg_last_d2h_bytes", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
            "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free", "fxg_copy_to_host", "fxg_copy_to_device"]
 
 _lib = None
@@ -70,6 +71,7 @@ def load_library():
     lib.fxg_find_record_cut.restype = C.c_size_t
     lib.fxg_scan_device_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.fxg_scan_device_finish.argtypes = [C.c_void_p, C.POINTER(Result)]
+    lib.fxg_can_route.argtypes = [C.c_void_p]
     lib.fxg_last_launch_count.argtypes = [C.c_void_p]
     lib.fxg_last_d2h_bytes.argtypes = [C.c_void_p]
     lib.fxg_last_d2h_bytes.restype = C.c_uint64
@@ -130,10 +132,10 @@ class Context:
     """One fxg_ctx.  Thin: every method is one C-ABI call."""
 
     def __init__(self, mode, target=TARGET_SEQ, invert=False, count_only=False, want_pattern_id=False,
-                 device=0, batch_bytes=0, stream=None):
+                 device=0, batch_bytes=0, stream=None, route_runs=False):
         self.lib = load_library()
         cfg = Config(device, mode, target, int(invert), int(count_only), int(want_pattern_id), batch_bytes,
-                     C.c_void_p(stream) if stream else None)
+                     C.c_void_p(stream) if stream else None, int(route_runs), 0)
         self.h = C.c_void_p()
         rc = self.lib.fxg_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
@@ -158,6 +160,9 @@ class Context:
     def set_patterns(self, patterns):
         blob, off = pack_patterns(patterns)
         self._check(self.lib.fxg_set_patterns(self.h, blob, off, len(patterns)))
+
+    def can_route(self):
+        return bool(self.lib.fxg_can_route(self.h))
 
     # ---- host path
     def acquire(self):

@@ -67,6 +67,10 @@ typedef struct fxg_config {
     int32_t want_pattern_id;  /* fields path: also return first-hit pattern id per field */
     uint64_t batch_bytes;     /* capacity of each pinned staging buffer; 0 = 256 MiB */
     void *stream;             /* cudaStream_t to launch on; NULL = context-owned stream */
+    int32_t route_runs;       /* raw path, MULTI / EXACT, !invert, !count_only: per-pattern output routing
+                               * (on_match2 main.cpp:285-287, hash_search main.cpp:315-324): every selected record
+                               * is its own run and run_pattern_id[k] names the pattern that selected run k */
+    int32_t reserved;
 } fxg_config;
 
 typedef struct fxg_run { uint64_t off, len; } fxg_run;   /* selected byte range of the submitted batch */
@@ -84,6 +88,8 @@ typedef struct fxg_result {
     const fxg_run *runs;      /* selected byte ranges in input order; owned by ctx until next collect */
     const uint8_t *flags;     /* fields path: 1 byte per field, 1 = hit (NOT inverted) */
     const int32_t *pattern_id;/* fields path, want_pattern_id: first-hit pattern (sorted order) or -1 */
+    const int32_t *run_pattern_id; /* raw path, route_runs: pattern id per run (EXACT: the key; MULTI: the first
+                               * reported hit = smallest end offset, then longest pattern -- oracle/fxo_ac.h) */
 } fxg_result;
 
 /* ---- lifecycle ---------------------------------------------------------- */
@@ -128,6 +134,9 @@ size_t fxg_find_record_cut(const uint8_t *buf, size_t n);
  * otherwise) and readable for 16 bytes past nbytes (edge look-ups read whole aligned words). */
 int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes);
 int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res);
+/* 1 iff the context can serve cfg.route_runs on the raw path with the current pattern set (EXACT always; MULTI
+ * when the set is served by the fused window matcher); otherwise the caller keeps such inputs on the fields path. */
+int fxg_can_route(const fxg_ctx *ctx);
 /* Number of kernel launches the last *_async / submit_* call enqueued. */
 int fxg_last_launch_count(const fxg_ctx *ctx);
 /* Bytes the last collected / finished raw batch brought back to the host (counters + selected runs). */

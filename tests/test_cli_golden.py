@@ -94,6 +94,59 @@ def test_cli_raw_path_synthetic_all_strategies(cli, tmp_path):
         assert len(r1.stdout) > 0
 
 
+def test_cli_raw_path_per_pattern_output_files(cli, tmp_path):
+    """Pattern files with a second column (main.cpp:222-256) on canonical FASTQ: the raw path returns every selected
+    record as its own run with the pattern that selected it (exact: the key; multi: the first reported hit = smallest
+    end offset, then longest pattern) and the host routes it like FileManager::find (fileManager.cpp:171-202).
+    stdout and every output file must equal the reference binary's; FXTRACT_PATH=raw forbids the fields fallback."""
+    rng = random.Random(77)
+    wd = str(tmp_path)
+    pats = sorted(set(helpers.rand_dna(rng, rng.choice([20, 20, 24, 31])).encode() for _ in range(60)))
+    # nested / overlapping patterns: the first-hit rule decides which file a record goes to
+    pats += [pats[0][2:] + b"ACGTACGT", pats[1][:18] + b"GG", pats[2] + b"T"]
+    pats = sorted(set(pats))
+    recs = []
+    for i in range(30000):
+        n = rng.randint(60, 170)
+        seq = bytearray(helpers.rand_dna(rng, n).encode())
+        if i % 4 == 0:
+            for _ in range(rng.choice([1, 1, 2, 3])):
+                q = rng.choice(pats)
+                if len(q) <= n:
+                    o = rng.randint(0, n - len(q))
+                    seq[o:o + len(q)] = q
+        recs.append(b"@r%d c%d\n" % (i, i % 7) + bytes(seq) + b"\n+\n" + bytes(rng.randint(33, 73) for _ in range(n)) + b"\n")
+    open(os.path.join(wd, "in.fq"), "wb").write(b"".join(recs))
+    files = ["o_a.fq", "o_b.fq", "o_c.fq"]
+    with open(os.path.join(wd, "pf.txt"), "wb") as f:
+        for k, q in enumerate(pats):
+            f.write(q + (b"\t" + files[k % 4].encode() if k % 4 < 3 else b"") + b"\n")       # every 4th pattern: stdout
+    ids = [b"r%d" % i for i in range(0, 30000, 11)] + [b"nope"]
+    with open(os.path.join(wd, "ids.txt"), "wb") as f:
+        for k, q in enumerate(ids):
+            f.write(q + (b"\t" + files[k % 3].encode() if k % 5 else b"") + b"\n")
+    env = dict(cli)
+    env.update(FXTRACT_PATH="raw", FXTRACT_BATCH_MIB="1", FXTRACT_STATS="1")
+    for argv in (["-Sf", "pf.txt", "in.fq"], ["-Srf", "pf.txt", "in.fq"], ["-SHXf", "ids.txt", "in.fq"],
+                 ["-Svf", "pf.txt", "in.fq"], ["-Scf", "pf.txt", "in.fq"]):
+        for f in files:
+            if os.path.exists(os.path.join(wd, f)):
+                os.remove(os.path.join(wd, f))
+        r1 = subprocess.run([helpers.REF_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        want = {f: helpers.read_or_none(wd, f) for f in files}
+        for f in files:
+            if os.path.exists(os.path.join(wd, f)):
+                os.remove(os.path.join(wd, f))
+        r2 = subprocess.run([helpers.PRODUCT_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=600)
+        assert r2.returncode == 0, (argv, r2.stderr[-400:])
+        assert b"fields 0 B" in r2.stderr, r2.stderr[-300:]                  # everything went through the raw path
+        assert r1.stdout == r2.stdout, (argv, len(r1.stdout), len(r2.stdout))
+        got = {f: helpers.read_or_none(wd, f) for f in files}
+        assert got == want, (argv, {f: (len(want[f] or b""), len(got[f] or b"")) for f in files})
+        if argv[0] in ("-Sf", "-SHXf"):
+            assert all(want[f] for f in files) and len(r1.stdout) > 0
+
+
 def test_cli_reroutes_non_canonical_batches(cli, tmp_path):
     """A defect in the middle of an otherwise canonical file: the batches before it go through the
     raw path, the rest through the host reader; the output is still byte-identical."""
