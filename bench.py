@@ -51,11 +51,11 @@ PRODUCT_CLI = os.path.join(ROOT, "fxtract_b200", "_build", "fxtract")
 PATTERN_RECORD = 1234          # the single 20-mer of c2 is copied from this global record
 COMP = bytes.maketrans(b"ACGT", b"TGCA")
 KERNEL_NAMES = {
-    "c2": "fxg::scan_tiles_kernel<G24, literal fingerprint> (fxg_scan_kernel.cuh)",
-    "c3": "fxg::scan_tiles_kernel<G32, k-mer window matcher> (fxg_scan_kernel.cuh)",
-    "c4": "fxg::scan_tiles_kernel<G24, exact look-up> (fxg_scan_kernel.cuh)",
-    "c5v": "fxg::scan_tiles_kernel<G32, k-mer window matcher> (fxg_scan_kernel.cuh)",
-    "c5c": "fxg::scan_tiles_kernel<G32, k-mer window matcher> (fxg_scan_kernel.cuh)",
+    "c2": "fxg::scan_tiles_kernel<Geom<24576,384,3,1>, 9 (literal fingerprint), false> (fxg_scan_kernel.cuh)",
+    "c3": "fxg::scan_tiles_kernel<Geom<16384,512,1,2>, 19 (window matcher, 128 KiB filter, two groups), false> (fxg_scan_kernel.cuh)",
+    "c4": "fxg::scan_tiles_kernel<Geom<24576,384,3,1>, 30 (exact: key hash), false> (fxg_scan_kernel.cuh)",
+    "c5v": "fxg::scan_tiles_kernel<Geom<32768,512,2,1>, 19 (window matcher, 32 KiB filter), false> (fxg_scan_kernel.cuh)",
+    "c5c": "fxg::scan_tiles_kernel<Geom<32768,512,2,1>, 19 (window matcher, 32 KiB filter), false> (fxg_scan_kernel.cuh)",
 }
 
 

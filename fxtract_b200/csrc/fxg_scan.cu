@@ -315,10 +315,21 @@ __device__ __forceinline__ bool window_lookup(const ScanParams &P, unsigned int 
             const unsigned int m = __ldg(reinterpret_cast<const unsigned int *>(rec));
             const long long p = win - (long long)o;
             if (p < 0 || (unsigned long long)p + m > P.nbytes) continue;
-            const unsigned char *pb = reinterpret_cast<const unsigned char *>(rec) + 8;
+            // pattern bytes (8-byte aligned in the record) against the text, 8 bytes per step: three aligned text
+            // words, two funnel shifts by the occurrence's byte misalignment (the batch has 16 readable bytes of slack)
+            const unsigned long long *pw = reinterpret_cast<const unsigned long long *>(rec) + 1;
+            const unsigned int *tw = reinterpret_cast<const unsigned int *>(P.buf + (p & ~3ll));
+            const int sh = (int)(p & 3) * 8;
             bool eq = true;
-            for (unsigned int i = 0; i < m; ++i)
-                if (P.buf[p + i] != __ldg(pb + i)) { eq = false; break; }
+            unsigned int g0 = __ldg(tw);
+            for (unsigned int i = 0; i < m; i += 8, tw += 2) {
+                const unsigned int g1 = __ldg(tw + 1), g2 = __ldg(tw + 2);
+                unsigned long long w = (unsigned long long)__funnelshift_r(g0, g1, sh) | ((unsigned long long)__funnelshift_r(g1, g2, sh) << 32);
+                unsigned long long q = __ldg(pw + (i >> 3));
+                if (m - i < 8u) { const unsigned long long mk = (1ull << (8 * (m - i))) - 1ull; w &= mk; q &= mk; }
+                if (w != q) { eq = false; break; }
+                g0 = g2;
+            }
             if (!eq) continue;
             if (!best_end) return true;
             any = true;
@@ -341,8 +352,6 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
     if (!nc_raw) return;
     const KmerTile &K = P.kmer;
     const TileView V(P);
-    const unsigned long long lb = V.lbase(t);
-    const int n_tab = V.lines(t);
     const int trole = target_role(P.target);
     const unsigned long long base = t * (unsigned long long)P.tile_bytes;
     const unsigned short *nl = P.tile_nl + t * (unsigned long long)P.nl_stride;
@@ -351,16 +360,18 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
     const unsigned long long left = P.nbytes - base;
     const unsigned int tile_len = left < (unsigned long long)P.tile_bytes ? (unsigned int)left : (unsigned int)P.tile_bytes;
     const unsigned int nc = overflow ? (tile_len + (unsigned int)K.stride - 1u) / (unsigned int)K.stride : nc_raw;
+    const unsigned long long lb = V.lbase(t);
+    const int n_tab = V.lines(t);
     unsigned int fresh = 0;
     // two candidates per lane and round: their list entries and table buckets are fetched before either is examined
     // (the walk is a chain of dependent loads; its latency, not its volume, is what the kernel waits for)
-    for (unsigned int c0 = lane; c0 < nc; c0 += 64) {
+    for (unsigned int c0 = 0; c0 < nc; c0 += 64) {             // warp-uniform: the line look-up below is cooperative
         unsigned int hh[2];
         int wr[2];
         bool live[2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-            const unsigned int c = c0 + 32u * (unsigned int)u;
+            const unsigned int c = c0 + (unsigned int)lane + 32u * (unsigned int)u;
             live[u] = c < nc;
             hh[u] = 0; wr[u] = 0;
             if (!live[u]) continue;
@@ -376,39 +387,54 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
                 hh[u] = window_hash(w[0], w[1], w[2], w[3]);
             }
         }
-        uint4 kk[2], vv[2];
+        uint4 kk[2];
+        unsigned int full[2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-            const unsigned int bkt = kmer_tile_bucket(hh[u], K.ht_mask);
-            kk[u] = __ldg(K.ht + 2 * (size_t)bkt); vv[u] = __ldg(K.ht + 2 * (size_t)bkt + 1);
+            const uint4 *b = K.ht + 2 * (size_t)kmer_tile_bucket(hh[u], K.ht_mask);
+            kk[u] = __ldg(b); full[u] = __ldg(reinterpret_cast<const unsigned int *>(b + 1) + 3);
         }
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-            if (!live[u]) continue;
-            // most candidates end here: no entry of the first bucket carries the hash and the bucket is not full
-            const bool maybe = kk[u].x == hh[u] || kk[u].y == hh[u] || kk[u].z == hh[u] || kk[u].w == hh[u] || vv[u].w != 0u;
-            if (!maybe) continue;
+            bool hit = false;
             long long best_end = 0x7fffffffffffffffll;       // batch offset of the end of the first reported occurrence
             unsigned long long best_low = ~0ull;
-            if (!window_lookup(P, hh[u], (long long)base + wr[u], P.rec_first ? &best_end : nullptr, &best_low)) continue;
-            // local line of the occurrence = number of '\n' before the window (a pattern holds no '\n', so all of it
-            // lies on the line of its window)
-            int lo = 0, hi = n_tab;
-            while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                if ((int)nl[mid] < wr[u]) lo = mid + 1; else hi = mid;
-            }
-            const unsigned long long line = lb + (unsigned long long)lo;
-            if ((int)(line & 3ull) != trole) continue;
-            const unsigned long long r = line >> 2;
-            if (r >= P.rec_cap) continue;
-            const unsigned int bit = 1u << (r & 31);
-            if (!(atomicOr(&P.hitbits[r >> 5], bit) & bit)) ++fresh;
-            if (P.rec_first) {
-                // end offset relative to the start of the line (which may lie in an earlier tile)
-                const long long ls = lo >= 1 ? (long long)base + nl[lo - 1] + 1 : V.prev_nl(t, 1) + 1;
-                const unsigned long long end_rel = (unsigned long long)(best_end - ls);
-                atomicMin(&P.rec_first[r], ((end_rel < 0xffffffull ? end_rel : 0xffffffull) << 40) | (best_low & 0xffffffffffull));
+            // most candidates end here: no entry of the first bucket carries the hash and the bucket is not full
+            if (live[u] && (kk[u].x == hh[u] || kk[u].y == hh[u] || kk[u].z == hh[u] || kk[u].w == hh[u] || full[u] != 0u))
+                hit = window_lookup(P, hh[u], (long long)base + wr[u], P.rec_first ? &best_end : nullptr, &best_low);
+            // local line of a verified occurrence = number of '\n' before its window (a pattern holds no '\n', so all
+            // of it lies on the line of its window): counted by the whole warp, 32 table entries per step, instead
+            // of a binary search of dependent loads by the one lane that has the hit
+            unsigned int hb = __ballot_sync(0xffffffffu, hit);
+            while (hb) {
+                const int src = __ffs(hb) - 1;
+                hb &= hb - 1;
+                const int pos = __shfl_sync(0xffffffffu, wr[u], src);
+                // every lane counts eight table entries per step (one 16-byte load; the rows are 16-byte aligned)
+                int lo = 0;
+                for (int j = lane * 8; j < n_tab; j += 256) {
+                    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(nl + j));
+                    const unsigned int w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        lo += (j + 2 * q < n_tab && (int)(w[q] & 0xffffu) < pos) ? 1 : 0;
+                        lo += (j + 2 * q + 1 < n_tab && (int)(w[q] >> 16) < pos) ? 1 : 0;
+                    }
+                }
+                lo = (int)__reduce_add_sync(0xffffffffu, (unsigned int)lo);
+                if (lane != src) continue;
+                const unsigned long long line = lb + (unsigned long long)lo;
+                if ((int)(line & 3ull) != trole) continue;
+                const unsigned long long r = line >> 2;
+                if (r >= P.rec_cap) continue;
+                const unsigned int bit = 1u << (r & 31);
+                if (!(atomicOr(&P.hitbits[r >> 5], bit) & bit)) ++fresh;
+                if (P.rec_first) {
+                    // end offset relative to the start of the line (which may lie in an earlier tile)
+                    const long long ls = lo >= 1 ? (long long)base + __ldg(nl + lo - 1) + 1 : V.prev_nl(t, 1) + 1;
+                    const unsigned long long end_rel = (unsigned long long)(best_end - ls);
+                    atomicMin(&P.rec_first[r], ((end_rel < 0xffffffull ? end_rel : 0xffffffull) << 40) | (best_low & 0xffffffffffull));
+                }
             }
         }
     }

@@ -209,13 +209,13 @@ bool run_fields(Job &job, Strategy st, PairSource &src, bool paired, DevicePool 
 
 // ------------------------------------------------------------------ raw path
 // Host ingest of the raw path (hard part 5): the file is read in fixed windows by a team of
-// reader threads (pread of 8 MiB slices) straight into pinned buffers, several windows ahead of the GPU.  A window
+// reader threads (pread of 4 MiB slices) straight into pinned buffers, several windows ahead of the GPU.  A window
 // becomes a batch once the unconsumed tail of its predecessor (a partial record, copied into the pad in front of
 // the window) is known and the last record boundary inside it is found; batches go to the devices round-robin and
 // come back in order, and the selected byte runs are written from the pinned copy.
 class RawIngest {
 public:
-    static constexpr size_t kSlice = 8u << 20;
+    static constexpr size_t kSlice = 4u << 20;
     // `pad` = room in front of every window for the carried partial record
     RawIngest(int fd, uint64_t file_size, size_t window, size_t pad, int nbuf, int nthreads)
         : fd_(fd), size_(file_size), window_(window), pad_(pad), nbuf_(nbuf)
@@ -305,8 +305,9 @@ RawMode raw_mode(const Job &job, Strategy st, const char *file2)
     const char *mode = getenv("FXTRACT_PATH");
     if (mode && !strcmp(mode, "fields")) return RAW_NO;
     const CliOptions &o = job.opt;
-    if (file2 || o.I || o.l) return RAW_NO;          // mates and -l need per-pair rules: fields path
-    if (job.router.all_stdout()) return RAW_PLAIN;
+    if (file2 || o.I) return RAW_NO;                 // mates need per-pair rules: fields path
+    if (job.router.all_stdout()) return RAW_PLAIN;   // includes -l: the first batch with a match ends the input
+    if (o.l) return RAW_NO;                          // -l with output files: find()'s side effects need the pattern
     if (st == S_MULTI && (o.v || o.c)) return RAW_PLAIN;
     if ((st == S_MULTI || st == S_EXACT) && !o.v && !o.c) return RAW_ROUTED;
     return RAW_NO;
@@ -322,7 +323,7 @@ int reader_threads_from_env()
 
 // Returns: -1 = raw path not applicable (nothing consumed), otherwise the byte offset from which
 // the fields path has to continue (== file size when the raw path handled everything).
-int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
+int64_t run_raw(Job &job, Strategy st, const char *file1, int fd, DevicePool &pool, Stats &stats)
 {
     struct stat sb;
     if (fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode)) return -1;
@@ -332,10 +333,14 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
     const uint64_t file_size = (uint64_t)sb.st_size;
     const size_t pad = std::min<size_t>((size_t)1 << 20, pool.batch_bytes() / 4) & ~(size_t)63;
     const size_t window = pool.batch_bytes() - pad;                    // a batch = carried tail + one window <= batch_bytes
-    const int nbuf = (int)pool.capacity() + 2;                         // in flight on the devices + being filled / cut
+    const int nbuf = (int)pool.capacity() + 3;                         // in flight on the devices + being cut + two being filled
     RawIngest ingest(fd, file_size, window, pad, nbuf, reader_threads_from_env());
     std::deque<RawPending> pending;
     int64_t reroute_at = -1;
+    // -l (main.cpp:611-615, :439-444, :318-323): the first match prints the file name and ends the input; nothing else
+    // is ever printed or counted.  simple / exact search only get there without -v (:608, :316), multi always (:439).
+    const bool l_effective = o.l && (st == S_MULTI || !o.v);
+    bool l_stop = false;
     auto finish_oldest = [&]() {
         fxg_result r;
         const double t0 = now_s();
@@ -344,10 +349,12 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
         stats.t_gpu += t1 - t0;
         RawPending p = pending.front();
         pending.pop_front();
-        if (reroute_at < 0) {
+        if (reroute_at < 0 && !l_stop) {
             if (!r.canonical_ok) { reroute_at = (int64_t)p.file_off; stats.rerouted++; }
             else {
-                if (o.c) job.matched_records += (long)r.n_selected;
+                if (o.l) {
+                    if (l_effective && r.n_matched > 0) { printf("%s\n", file1); l_stop = true; }
+                } else if (o.c) job.matched_records += (long)r.n_selected;
                 else if (r.run_pattern_id) {                          // per-pattern output files (main.cpp:285-287, :315-324)
                     for (uint64_t k = 0; k < r.n_runs; ++k) {
                         FILE *out = job.router.find(r.run_pattern_id[k]);
@@ -363,8 +370,8 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
     const uint8_t *carry = nullptr;      // unconsumed tail of the previous window's batch (a partial record)
     size_t carry_n = 0;
     uint64_t consumed = 0;               // file offset up to which batches have been cut
-    for (uint64_t k = 0; k < ingest.windows() && reroute_at < 0; ++k) {
-        if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute_at >= 0) break; }
+    for (uint64_t k = 0; k < ingest.windows() && reroute_at < 0 && !l_stop; ++k) {
+        if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute_at >= 0 || l_stop) break; }
         size_t wlen;
         const double tw = now_s();
         uint8_t *w = ingest.wait_window(k, &wlen);
@@ -394,6 +401,7 @@ int64_t run_raw(Job &job, int fd, DevicePool &pool, Stats &stats)
         // released, which happens only when batch k has been collected -- at least one loop iteration later
     }
     while (!pending.empty()) finish_oldest();
+    if (l_stop) return (int64_t)file_size;
     if (reroute_at >= 0) {
         const char *mode = getenv("FXTRACT_PATH");
         if (mode && !strcmp(mode, "raw")) {
@@ -489,7 +497,7 @@ int run_input(Job &job, const char *file1, const char *file2)
     PoolConfig pc;
     pc.mode = st == S_LITERAL ? FXG_MODE_LITERAL : (st == S_MULTI ? FXG_MODE_MULTI : FXG_MODE_EXACT);
     pc.target = fxg_target(o);
-    pc.invert = o.v; pc.count_only = o.c; pc.want_pattern_id = st != S_LITERAL;
+    pc.invert = o.v; pc.count_only = o.c || o.l; pc.want_pattern_id = st != S_LITERAL;      // -l needs no runs either
     RawMode rm = raw_mode(job, st, file2);
     pc.route_runs = st != S_LITERAL && !o.v && !o.c && !job.router.all_stdout();
     pc.batch_bytes = batch_bytes_from_env();
@@ -505,7 +513,7 @@ int run_input(Job &job, const char *file1, const char *file2)
     if (rm != RAW_NO) {
         int fd = open(file1, O_RDONLY);
         if (fd >= 0) {
-            int64_t next = run_raw(job, fd, pool, stats);
+            int64_t next = run_raw(job, st, file1, fd, pool, stats);
             if (next >= 0) {
                 struct stat sb;
                 fstat(fd, &sb);

@@ -87,7 +87,10 @@ def test_cli_raw_path_synthetic_all_strategies(cli, tmp_path):
     for argv in (["-S", pat, "s.fq"], ["-Sr", pat, "s.fq"], ["-Sc", pat, "s.fq"], ["-Sv", pat, "s.fq"],
                  ["-Sf", "p.txt", "s.fq"], ["-Srf", "p.txt", "s.fq"], ["-Scf", "p.txt", "s.fq"], ["-Svcf", "p.txt", "s.fq"],
                  ["-SHXf", "ids.txt", "s.fq"], ["-SHXvcf", "ids.txt", "s.fq"], ["-SH", "FC:3:", "s.fq"],
-                 ["-SQc", "II", "s.fq"], ["-SCc", "1:N", "s.fq"], [pat, "s.fq"]):
+                 ["-SQc", "II", "s.fq"], ["-SCc", "1:N", "s.fq"], [pat, "s.fq"],
+                 # -l on the raw path: the first batch with a match prints the file name and ends the input
+                 ["-Sl", pat, "s.fq"], ["-Slf", "p.txt", "s.fq"], ["-SlHXf", "ids.txt", "s.fq"], ["-Slvf", "p.txt", "s.fq"],
+                 ["-Slc", pat, "s.fq"]):
         r1, r2 = _both(argv, wd, env)
         assert r2.returncode == 0, (argv, r2.stderr[-400:])
         assert hashlib.sha256(r1.stdout).hexdigest() == hashlib.sha256(r2.stdout).hexdigest(), (argv, len(r1.stdout), len(r2.stdout))
