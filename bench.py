@@ -348,9 +348,13 @@ def run_reference_arm(args):
         return 0
     w = workload_def(args.workload, args.records)
     nbytes_full = record_offset(w, 0, w["records"])
+    cfg = static_config(w, nbytes_full)
+    # the same keys as the GPU arm's config; what only a GPU run can fill stays None
+    cfg.update({"verified_against": None, "verify_records": None, "expected_selected": None, "selected_records": None,
+                "records": None, "runs_rank0": None})
     base = {"metric": METRIC, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u8", "data": "synthetic", "config": static_config(w, nbytes_full)}
+            "dtype": "u8", "data": "synthetic", "config": cfg}
     if not os.path.exists(REF_BIN) or not os.path.exists(FXSYNTH):
         base["unavailable"] = "oracle/_ref/fxtract or fxsynth not built (reference sources absent at build time)"
         print(json.dumps(base))

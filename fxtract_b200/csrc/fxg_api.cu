@@ -983,6 +983,7 @@ extern "C" size_t fxg_find_record_cut(const uint8_t *buf, size_t n)
 extern "C" int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes)
 {
     if (!ctx || (!d_buf && nbytes)) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    if (((uintptr_t)d_buf & 15) != 0) return set_error(ctx, FXG_ERR_ARG, "d_buf must be 16-byte aligned (the tiles are fetched with bulk copies)");
     cudaSetDevice(ctx->cfg.device);
     Slot &s = ctx->slots[2];
     int rc = enqueue_raw(ctx, (const uint8_t *)d_buf, (size_t)nbytes, s);

@@ -173,8 +173,7 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
             if (rec < P.rec_cap) {
                 if (P.rec_first) P.rec_first[rec] = (unsigned long long)(unsigned int)pid;
                 const unsigned int bit = 1u << (rec & 31);
-                const unsigned int old = atomicOr(&P.hitbits[rec >> 5], bit);
-                if (!(old & bit)) atomicAdd(&P.ctr->n_hits, 1ull);
+                atomicOr(&P.hitbits[rec >> 5], bit);
             }
         }
     }
@@ -184,21 +183,15 @@ __global__ void __launch_bounds__(256) tile_finalize_kernel(const ScanParams P)
         const int want = P.target == FXG_TARGET_SEQ ? 1 : (P.target == FXG_TARGET_QUAL ? 3 : 0);
         const unsigned int role_mask = 0x11111111u << ((want - r) & 3);     // 32 % 4 == 0: same mask for every word
         const unsigned int *hw = P.tile_hit + t * (unsigned long long)P.hit_words;
-        unsigned int fresh = 0;
         for (int w = 0; w * 32 <= n_tab; ++w) {
             unsigned int bits = hw[w] & role_mask;
             while (bits) {
                 const int b = __ffs(bits) - 1;
                 bits &= bits - 1;
                 const unsigned long long rec = (lb + (unsigned long long)(w * 32 + b)) >> 2;
-                if (rec < P.rec_cap) {
-                    const unsigned int bit = 1u << (rec & 31);
-                    const unsigned int old = atomicOr(&P.hitbits[rec >> 5], bit);
-                    if (!(old & bit)) ++fresh;
-                }
+                if (rec < P.rec_cap) atomicOr(&P.hitbits[rec >> 5], 1u << (rec & 31));
             }
         }
-        if (fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
     }
     if (t + 1 == P.ntiles) {
         P.ctr->n_lines = lb + ti.total;
@@ -256,40 +249,51 @@ __global__ void __launch_bounds__(256) tile_emit_kernel(const ScanParams P)
 // exact mode: one WARP per tile, one lane per line of the target's role; key hash from keyhash[], bucket probe,
 // and for a fingerprint match the key compared word by word against the batch text (replaces manager.find(*data),
 // main.cpp:315).  Line 0 of a tile (it may start in an earlier tile) is done by tile_finalize_kernel.
+constexpr int kExactLanesPerTile = 8;      // four tiles per warp: four chains of dependent loads per wait (see kmer_resolve_kernel)
 __global__ void __launch_bounds__(256) exact_resolve_kernel(const ScanParams P)
 {
-    const int lane = threadIdx.x & 31;
-    const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    constexpr int LPT = kExactLanesPerTile;
+    const int lane = (threadIdx.x & 31) % LPT;
+    const unsigned long long t = (((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / LPT) + (threadIdx.x & 31) / LPT;
     if (t >= P.ntiles) return;
     const TileView V(P);
     const unsigned long long lb = V.lbase(t);
     const int n_tab = V.lines(t);
     const int first = (target_role(P.target) - (int)(lb & 3ull)) & 3;
     const unsigned long long *kh = P.keyhash + t * (unsigned long long)(P.nl_stride / 4);
-    unsigned int fresh = 0;
-    for (int i = first + 4 * lane; i < n_tab; i += 128) {
-        if (i < 1) continue;
-        const unsigned long long h = __ldg(kh + (i >> 2));
-        int pid = -1;
-        if (P.target == FXG_TARGET_COMMENT) {              // the key starts behind the first ' ': found by the slow path
-            if (!exact_fingerprint_present(P.exact, h)) continue;
-            if (!exact_line_global(P, V.nl(t, i - 1) + 1, V.nl(t, i), pid)) continue;
-        } else {
-            if (P.exact.pre) {                             // pre-filter first: the line's bounds are only read for the few that pass
-                const unsigned int m = exact_pre_mask(h);
-                if ((__ldg(P.exact.pre + exact_pre_word(h, P.exact.pre_mask)) & m) != m) continue;
-            }
-            const bool name = P.target == FXG_TARGET_NAME;
-            if (!exact_verify_hashed(P.exact, h, P.buf, V.nl(t, i - 1) + 1 + (name ? 1 : 0), V.nl(t, i), name, pid)) continue;
+    // four lines per lane and round: their key hashes, then their pre-filter words, are fetched together; ~99 % of
+    // the lines end there
+    const bool use_pre = P.exact.pre != nullptr && P.target != FXG_TARGET_COMMENT;
+    for (int i0 = first + 4 * lane; i0 < n_tab; i0 += 16 * LPT) {
+        unsigned long long hv[4];
+        unsigned int pw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + 4 * LPT * u;
+            hv[u] = (i >= 1 && i < n_tab) ? __ldg(kh + (i >> 2)) : 0ull;
         }
-        const unsigned long long rec = (lb + (unsigned long long)i) >> 2;
-        if (rec >= P.rec_cap) continue;
-        if (P.rec_first) P.rec_first[rec] = (unsigned long long)(unsigned int)pid;
-        const unsigned int bit = 1u << (rec & 31);
-        if (!(atomicOr(&P.hitbits[rec >> 5], bit) & bit)) ++fresh;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) pw[u] = use_pre ? __ldg(P.exact.pre + exact_pre_word(hv[u], P.exact.pre_mask)) : 0xffffffffu;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + 4 * LPT * u;
+            if (i < 1 || i >= n_tab) continue;
+            const unsigned long long h = hv[u];
+            if (use_pre) { const unsigned int m = exact_pre_mask(h); if ((pw[u] & m) != m) continue; }
+            int pid = -1;
+            if (P.target == FXG_TARGET_COMMENT) {          // the key starts behind the first ' ': found by the slow path
+                if (!exact_fingerprint_present(P.exact, h)) continue;
+                if (!exact_line_global(P, V.nl(t, i - 1) + 1, V.nl(t, i), pid)) continue;
+            } else {
+                const bool name = P.target == FXG_TARGET_NAME;
+                if (!exact_verify_hashed(P.exact, h, P.buf, V.nl(t, i - 1) + 1 + (name ? 1 : 0), V.nl(t, i), name, pid)) continue;
+            }
+            const unsigned long long rec = (lb + (unsigned long long)i) >> 2;
+            if (rec >= P.rec_cap) continue;
+            if (P.rec_first) P.rec_first[rec] = (unsigned long long)(unsigned int)pid;
+            atomicOr(&P.hitbits[rec >> 5], 1u << (rec & 31));
+        }
     }
-    fresh = __reduce_add_sync(0xffffffffu, fresh);
-    if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
 }
 
 // window matcher: one WARP per tile, one lane per candidate {window hash, tile-relative offset of the window}:
@@ -343,10 +347,16 @@ __device__ __forceinline__ bool window_lookup(const ScanParams &P, unsigned int 
     }
 }
 
+// LPT = lanes per tile: 32 for pattern sets behind the 128 KiB filter (~90 false candidates per tile), 8 for the
+// small sets (a handful per tile): what the kernel waits for is the chain of dependent loads per tile, so a warp
+// that walks four tiles side by side gets four times the work out of each wait.
+template <int LPT>
 __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
 {
-    const int lane = threadIdx.x & 31;
-    const unsigned long long t = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    constexpr int kTilesPerWarp = 32 / LPT;
+    const int lane = threadIdx.x & 31, gl = lane % LPT, grp = lane / LPT;
+    const unsigned int gmask = LPT == 32 ? 0xffffffffu : (((1u << LPT) - 1u) << (grp * LPT));
+    const unsigned long long t = (((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kTilesPerWarp + (unsigned int)grp;
     if (t >= P.ntiles) return;
     const unsigned int nc_raw = P.tile_ncand[t];
     if (!nc_raw) return;
@@ -362,16 +372,14 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
     const unsigned int nc = overflow ? (tile_len + (unsigned int)K.stride - 1u) / (unsigned int)K.stride : nc_raw;
     const unsigned long long lb = V.lbase(t);
     const int n_tab = V.lines(t);
-    unsigned int fresh = 0;
     // two candidates per lane and round: their list entries and table buckets are fetched before either is examined
-    // (the walk is a chain of dependent loads; its latency, not its volume, is what the kernel waits for)
-    for (unsigned int c0 = 0; c0 < nc; c0 += 64) {             // warp-uniform: the line look-up below is cooperative
+    for (unsigned int c0 = 0; c0 < nc; c0 += 2 * LPT) {         // uniform over the tile's lanes: the line look-up below is cooperative
         unsigned int hh[2];
         int wr[2];
         bool live[2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-            const unsigned int c = c0 + (unsigned int)lane + 32u * (unsigned int)u;
+            const unsigned int c = c0 + (unsigned int)gl + (unsigned int)(LPT * u);
             live[u] = c < nc;
             hh[u] = 0; wr[u] = 0;
             if (!live[u]) continue;
@@ -403,16 +411,15 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
             if (live[u] && (kk[u].x == hh[u] || kk[u].y == hh[u] || kk[u].z == hh[u] || kk[u].w == hh[u] || full[u] != 0u))
                 hit = window_lookup(P, hh[u], (long long)base + wr[u], P.rec_first ? &best_end : nullptr, &best_low);
             // local line of a verified occurrence = number of '\n' before its window (a pattern holds no '\n', so all
-            // of it lies on the line of its window): counted by the whole warp, 32 table entries per step, instead
-            // of a binary search of dependent loads by the one lane that has the hit
-            unsigned int hb = __ballot_sync(0xffffffffu, hit);
+            // of it lies on the line of its window): counted by all lanes of the tile, eight table entries per lane
+            // and step, instead of a binary search of dependent loads by the one lane that has the hit
+            unsigned int hb = __ballot_sync(gmask, hit) & gmask;
             while (hb) {
                 const int src = __ffs(hb) - 1;
                 hb &= hb - 1;
-                const int pos = __shfl_sync(0xffffffffu, wr[u], src);
-                // every lane counts eight table entries per step (one 16-byte load; the rows are 16-byte aligned)
+                const int pos = __shfl_sync(gmask, wr[u], src);
                 int lo = 0;
-                for (int j = lane * 8; j < n_tab; j += 256) {
+                for (int j = gl * 8; j < n_tab; j += LPT * 8) {
                     const uint4 v = __ldg(reinterpret_cast<const uint4 *>(nl + j));
                     const unsigned int w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -421,14 +428,13 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
                         lo += (j + 2 * q + 1 < n_tab && (int)(w[q] >> 16) < pos) ? 1 : 0;
                     }
                 }
-                lo = (int)__reduce_add_sync(0xffffffffu, (unsigned int)lo);
+                lo = (int)__reduce_add_sync(gmask, (unsigned int)lo);
                 if (lane != src) continue;
                 const unsigned long long line = lb + (unsigned long long)lo;
                 if ((int)(line & 3ull) != trole) continue;
                 const unsigned long long r = line >> 2;
                 if (r >= P.rec_cap) continue;
-                const unsigned int bit = 1u << (r & 31);
-                if (!(atomicOr(&P.hitbits[r >> 5], bit) & bit)) ++fresh;
+                atomicOr(&P.hitbits[r >> 5], 1u << (r & 31));
                 if (P.rec_first) {
                     // end offset relative to the start of the line (which may lie in an earlier tile)
                     const long long ls = lo >= 1 ? (long long)base + __ldg(nl + lo - 1) + 1 : V.prev_nl(t, 1) + 1;
@@ -438,8 +444,31 @@ __global__ void __launch_bounds__(256) kmer_resolve_kernel(const ScanParams P)
             }
         }
     }
-    fresh = __reduce_add_sync(0xffffffffu, fresh);
-    if (lane == 0 && fresh) atomicAdd(&P.ctr->n_hits, (unsigned long long)fresh);
+}
+
+// matched_records (main.cpp:80): the records with a hit are counted from the finished bit set -- one pass over
+// 1 bit per record, one atomic per block -- instead of one same-address atomic per hit in the kernels that find them
+__global__ void __launch_bounds__(256) count_hits_kernel(const ScanParams P)
+{
+    __shared__ unsigned int wsum[8];
+    unsigned long long nrec = P.ctr->n_lines >> 2;
+    if (nrec > P.rec_cap) nrec = P.rec_cap;
+    const unsigned long long words = (nrec + 31) >> 5;
+    unsigned int n = 0;
+    for (unsigned long long w = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; w < words; w += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned int v = P.hitbits[w];
+        const unsigned long long left = nrec - w * 32ull;
+        if (left < 32ull) v &= (1u << left) - 1u;
+        n += __popc(v);
+    }
+    n = __reduce_add_sync(0xffffffffu, n);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int tot = 0;
+        for (int i = 0; i < 8; ++i) tot += wsum[i];
+        if (tot) atomicAdd(&P.ctr->n_hits, (unsigned long long)tot);
+    }
 }
 
 // ---------------------------------------------------------------- launch configuration cache
@@ -501,10 +530,15 @@ cudaError_t launch_scan_raw(const ScanParams &P, cudaStream_t stream, int *launc
     tile_finalize_kernel<<<(unsigned int)((P.ntiles + 255) / 256), 256, 0, stream>>>(P);
     if (launches) *launches += 6;
     if (kmer) {
-        kmer_resolve_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
+        if (P.kmer.filter_log2_words > 13) kmer_resolve_kernel<32><<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
+        else kmer_resolve_kernel<8><<<(unsigned int)((P.ntiles + 31) / 32), 256, 0, stream>>>(P);
         if (launches) *launches += 1;
     } else if (P.mode == kModeExact) {
-        exact_resolve_kernel<<<(unsigned int)((P.ntiles + 7) / 8), 256, 0, stream>>>(P);
+        exact_resolve_kernel<<<(unsigned int)((P.ntiles + 8 * (32 / kExactLanesPerTile) - 1) / (8 * (32 / kExactLanesPerTile))), 256, 0, stream>>>(P);
+        if (launches) *launches += 1;
+    }
+    if (P.mode != kModeIndex) {          // index-only: the field matcher that follows counts its own hits
+        count_hits_kernel<<<148 * 4, 256, 0, stream>>>(P);
         if (launches) *launches += 1;
     }
     if (P.fld_off) {

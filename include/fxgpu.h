@@ -130,8 +130,8 @@ size_t fxg_find_record_cut(const uint8_t *buf, size_t n);
 /* ---- device-resident path (inputs already in HBM) ------------------------ */
 /* Enqueues the raw scan over d_buf[0..nbytes) (whole records, ends in '\n') on the
  * context's stream; fxg_scan_device_finish() synchronises and fills res.
- * d_buf must be 16-byte aligned (the tiles are fetched with bulk copies; FXG_ERR_CUDA / misaligned address
- * otherwise) and readable for 16 bytes past nbytes (edge look-ups read whole aligned words). */
+ * d_buf must be 16-byte aligned (the tiles are fetched with bulk copies; FXG_ERR_ARG otherwise) and readable for
+ * 16 bytes past nbytes (edge look-ups and candidate verification read whole aligned words). */
 int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes);
 int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res);
 /* 1 iff the context can serve cfg.route_runs on the raw path with the current pattern set (EXACT always; MULTI

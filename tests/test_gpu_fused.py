@@ -225,6 +225,29 @@ def test_exact_fused_all_targets(fx, seed):
         assert cnt["n_selected"] == fxoracle.run(data, flag + "X", pattern_file=pf).count(b"\n") // 4
 
 
+def test_exact_fused_dense_hits(fx):
+    """Every read name is in the key list and the reads are short: ~200 look-up hits per 24 KiB tile, several rounds
+    of the resolve kernel's four-lines-per-lane walk, every lane on the verification path.  Same for sequence keys."""
+    rng = random.Random(4242)
+    recs, names, seqs = [], [], []
+    for i in range(12000):
+        n = rng.randint(20, 40)
+        name = b"k%d" % i
+        seq = helpers.rand_dna(rng, n).encode()
+        names.append(name); seqs.append(seq)
+        recs.append(b"@" + name + b" x\n" + seq + b"\n+\n" + bytes(rng.randint(33, 73) for _ in range(n)) + b"\n")
+    data = b"".join(recs)
+    for target, flag, pool in ((1, "H", names), (0, "", seqs)):
+        keys = sorted(set(pool[::1 if target == 1 else 2]) | {b"absent"})
+        pf = b"\n".join(keys) + b"\n"
+        for inv in (False, True):
+            want = fxoracle.run(data, flag + "X" + ("v" if inv else ""), pattern_file=pf)
+            got = run_raw(fx, data, fx.MODE_EXACT, keys, target=target, invert=inv)
+            assert got["ok"] == 1, got["violation"]
+            assert got["out"] == want, (target, inv, len(got["out"]), len(want))
+    assert len(fxoracle.run(data, "HX", pattern_file=b"\n".join(names) + b"\n")) == len(data)
+
+
 def test_exact_fused_long_reads_and_redo(fx):
     """Tiles without a "+" anchor (reads longer than a tile) and tiles whose guessed phase is wrong (1-base reads
     with "+" quality) take the REDO launch, which repeats the look-ups under the true phase."""
