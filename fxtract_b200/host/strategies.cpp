@@ -40,6 +40,7 @@ enum Strategy { S_LITERAL, S_MULTI, S_EXACT };
 struct Stats {
     uint64_t raw_bytes = 0, raw_batches = 0, field_bytes = 0, field_batches = 0, records = 0, rerouted = 0;
     double t_ingest = 0, t_gpu = 0, t_write = 0;      // raw path: main thread blocked on the readers / on the devices / writing
+    double t_submit = 0, t_setup = 0;                 // ... inside the submit calls (copy + kernel enqueue) / allocating the staging windows
 };
 
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
@@ -334,7 +335,9 @@ int64_t run_raw(Job &job, Strategy st, const char *file1, int fd, DevicePool &po
     const size_t pad = std::min<size_t>((size_t)1 << 20, pool.batch_bytes() / 4) & ~(size_t)63;
     const size_t window = pool.batch_bytes() - pad;                    // a batch = carried tail + one window <= batch_bytes
     const int nbuf = (int)pool.capacity() + 3;                         // in flight on the devices + being cut + two being filled
+    const double t_setup0 = now_s();
     RawIngest ingest(fd, file_size, window, pad, nbuf, reader_threads_from_env());
+    stats.t_setup += now_s() - t_setup0;
     std::deque<RawPending> pending;
     int64_t reroute_at = -1;
     // -l (main.cpp:611-615, :439-444, :318-323): the first match prints the file name and ends the input; nothing else
@@ -393,7 +396,9 @@ int64_t run_raw(Job &job, Strategy st, const char *file1, int fd, DevicePool &po
             break;
         }
         carry = batch + n; carry_n = have - n;
+        const double ts = now_s();
         pool.submit_raw_from(batch, n, last);
+        stats.t_submit += now_s() - ts;
         pending.push_back(RawPending{batch, consumed, n, k});
         consumed += n;
         stats.raw_bytes += n; stats.raw_batches++;
@@ -533,8 +538,9 @@ int run_input(Job &job, const char *file1, const char *file2)
     if (job.stats) {
         const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         if (stats.raw_batches)
-            fprintf(stderr, "[fxtract] raw path main thread: %.3f s waiting for the readers, %.3f s for the devices, %.3f s writing\n",
-                    stats.t_ingest, stats.t_gpu, stats.t_write);
+            fprintf(stderr, "[fxtract] raw path main thread: %.3f s waiting for the readers, %.3f s for the devices, %.3f s writing, "
+                            "%.3f s in submit calls, %.3f s allocating pinned windows\n",
+                    stats.t_ingest, stats.t_gpu, stats.t_write, stats.t_submit, stats.t_setup);
         fprintf(stderr, "[fxtract] %s: raw %llu B in %llu batches, fields %llu B in %llu batches, %llu records, %llu re-routed, "
                         "%.3f s%s\n", file1, (unsigned long long)stats.raw_bytes, (unsigned long long)stats.raw_batches,
                 (unsigned long long)stats.field_bytes, (unsigned long long)stats.field_batches,
