@@ -29,6 +29,8 @@ struct Slot {
     int kind = 0;                       // 0 raw, 1 fields
     size_t nbytes = 0; uint32_t nrec = 0; int is_last = 0;
     size_t runs_copied = 0;
+    int pair = 0;                       // raw batch of mates (fxg_submit_raw_interleaved_from / _pair_from)
+    uint64_t split = 0;                 // ... two files: bytes of file 1's part; 0 = interleaved
 };
 
 }  // namespace fxg
@@ -57,6 +59,7 @@ struct fxg_ctx {
     unsigned int *d_exact_pre = nullptr; unsigned int exact_pre_mask = 0;         // its Bloom pre-filter
     unsigned long long *d_keyhash = nullptr;                                      // exact mode: key hash per target line (scan -> resolve)
     unsigned long long *d_rec_first = nullptr;                                    // routing: first reported hit per record
+    unsigned int *d_pairsel = nullptr; size_t pairsel_cap = 0;                    // mates: selected bit per pair (scratch)
     uint2 *d_cand = nullptr; unsigned int *d_tile_ncand = nullptr;                // k-mer mode: filter hits per tile (scan -> resolve)
     unsigned long long *d_key_words = nullptr;
     // scan resources (shared; everything is ordered on one stream)
@@ -473,10 +476,11 @@ static bool routed(const fxg_ctx *ctx)
            (ctx->scan_mode == kModeExact || mode_is_kmer(ctx->scan_mode));
 }
 
-static int ensure_slot_runs(fxg_ctx *ctx, Slot &s)
+static int ensure_slot_runs(fxg_ctx *ctx, Slot &s, bool per_record)
 {
-    // plain: a run needs a selected record and an unselected one behind it; routed: every selected record is a run
-    size_t want = std::min<size_t>(routed(ctx) ? ctx->rec_cap + 2 : ctx->rec_cap / 2 + 2, (size_t)1 << 26);
+    // plain: a run needs a selected record and an unselected one behind it; routed / mates from two files: every
+    // selected record is a run
+    size_t want = std::min<size_t>(per_record ? ctx->rec_cap + 2 : ctx->rec_cap / 2 + 2, (size_t)1 << 26);
     cudaError_t e;
     if (s.d_runs_cap < want) {
         if ((e = dev_realloc(s.d_runs, want)) != cudaSuccess) return set_cuda_error(ctx, e, "alloc runs");
@@ -495,7 +499,7 @@ static int ensure_slot_runs(fxg_ctx *ctx, Slot &s)
 }
 
 // Enqueue the whole raw pipeline for one batch that is already in device memory.
-static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &s)
+static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &s, int pair = 0, uint64_t split = 0)
 {
     int rc;
     if (!ctx->have_patterns) return set_error(ctx, FXG_ERR_STATE, "fxg_set_patterns has not been called");
@@ -504,10 +508,11 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
     if ((rc = ensure_scan_capacity(ctx, nbytes)) != FXG_OK) return rc;
     if ((rc = ensure_slot_result(ctx, s)) != FXG_OK) return rc;
     const bool emit = !ctx->cfg.count_only;
-    if (emit && (rc = ensure_slot_runs(ctx, s)) != FXG_OK) return rc;
+    if (pair && split >= nbytes && nbytes) return set_error(ctx, FXG_ERR_ARG, "pair batch: the second file's part is empty");
+    if (emit && (rc = ensure_slot_runs(ctx, s, routed(ctx) || (pair && split))) != FXG_OK) return rc;
     cudaStream_t st = ctx->stream;
     ctx->last_launches = 0;
-    s.nbytes = nbytes; s.kind = 0; s.runs_copied = 0;
+    s.nbytes = nbytes; s.kind = 0; s.runs_copied = 0; s.pair = pair; s.split = pair ? split : 0;
     memset(s.h_ctr, 0, sizeof(ScanCounters)); s.h_counts[0] = s.h_counts[1] = 0;
     s.timed = false;
     if (nbytes == 0) { FXG_CUDA_OK(cudaEventRecord(s.done, st)); return FXG_OK; }
@@ -572,11 +577,26 @@ static int enqueue_raw(fxg_ctx *ctx, const uint8_t *d_buf, size_t nbytes, Slot &
         }
         ctx->last_launches += 1;
     }
+    if (pair) {
+        // mates: the strategy's pair rule (invert included) turns the hit bits into selected bits of both mates
+        if (ctx->pairsel_cap < words / 2 + 8) {
+            cudaError_t e = dev_realloc(ctx->d_pairsel, words / 2 + 8);
+            if (e != cudaSuccess) return set_cuda_error(ctx, e, "alloc pair selection");
+            ctx->pairsel_cap = words / 2 + 8;
+        }
+        PairRule rule;
+        rule.invert = ctx->cfg.invert ? 1 : 0;
+        rule.need_neither = ctx->cfg.mode == FXG_MODE_MULTI ? 1 : 0;
+        rule.all_match = (literal && ctx->h_lit.all_match) ? 1 : 0;
+        FXG_CUDA_OK(launch_pair_select(ctx->d_hitbits, ctx->d_pairsel, P, rec_cap, split, rule, st, &ctx->last_launches));
+    }
     if (emit) {
         int inv = ctx->cfg.invert ? 1 : 0;
         if (literal && ctx->h_lit.all_match) inv ^= 1;     // every record matches: hit bits stay 0
+        if (pair) inv = 0;                                 // the pair rule has applied it
         FXG_CUDA_OK(launch_compact(ctx->d_hitbits, P, ctx->d_ctr, rec_cap, ctx->d_block_sums, ctx->d_counts,
-                                   s.d_runs, s.d_runs_cap, inv, route ? s.d_run_pid : nullptr, st, &ctx->last_launches));
+                                   s.d_runs, s.d_runs_cap, inv, route ? s.d_run_pid : nullptr, (pair && split) ? 1 : 0,
+                                   st, &ctx->last_launches));
         if (ctx->profiling) { FXG_CUDA_OK(cudaEventRecord(s.ev[3], st)); s.timed = true; }
         FXG_CUDA_OK(cudaMemcpyAsync(s.h_counts, ctx->d_counts, 16, cudaMemcpyDeviceToHost, st));
         s.runs_copied = std::min<size_t>(kRunPrefix, s.d_runs_cap);
@@ -610,6 +630,10 @@ static int finish_raw(fxg_ctx *ctx, Slot &s, fxg_result *res)
     const bool literal = ctx->cfg.mode == FXG_MODE_LITERAL;
     res->n_matched = (literal && ctx->h_lit.all_match) ? res->n_records : c.n_hits;
     res->n_selected = ctx->cfg.invert ? res->n_records - res->n_matched : res->n_matched;
+    if (s.pair) {                                          // mates: the counts are in pairs
+        res->n_records >>= 1;
+        res->n_matched = res->n_selected = c.n_pair_sel;
+    }
     uint64_t d2h = sizeof(ScanCounters);
     if (!ctx->cfg.count_only && s.nbytes) {
         d2h += 16 + s.runs_copied * sizeof(fxg_run);
@@ -710,7 +734,7 @@ extern "C" void fxg_destroy(fxg_ctx *ctx)
         if (s.h2d_done) cudaEventDestroy(s.h2d_done);
         for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     }
-    void *dev[] = {ctx->d_rec_first, ctx->d_exact_pre, ctx->d_keyhash, ctx->d_cand, ctx->d_tile_ncand, ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
+    void *dev[] = {ctx->d_pairsel, ctx->d_rec_first, ctx->d_exact_pre, ctx->d_keyhash, ctx->d_cand, ctx->d_tile_ncand, ctx->d_ktfilter, ctx->d_ktht, ctx->d_ktrec, ctx->d_kfilter, ctx->d_kkey, ctx->d_kval, ctx->d_lit, ctx->d_pat, ctx->d_patoff, ctx->d_cls, ctx->d_next, ctx->d_out, ctx->d_bkt, ctx->d_key_words,
                    ctx->d_info, ctx->d_tile_nl, ctx->d_tile_hit, ctx->d_lbase, ctx->d_bsum, ctx->d_redo, ctx->d_ctr, ctx->d_hitbits, ctx->d_fld_off, ctx->d_block_sums, ctx->d_counts,
                    ctx->d_fld_len, ctx->d_flags, ctx->d_pid, ctx->d_off32};
     for (void *p : dev) if (p) cudaFree(p);
@@ -817,20 +841,23 @@ static int ensure_d_in(fxg_ctx *ctx, Slot &s, size_t n)
 // Host path, one batch: H2D on the copy stream into the slot's own device buffer, kernels on the compute stream
 // behind an event.  With two slots the copy of batch k+1 runs while the kernels of batch k do (the slot's buffer
 // is free: its previous batch has been collected).
-static int submit_raw_common(fxg_ctx *ctx, int si, const void *src, size_t nbytes, int is_last)
+static int submit_raw_common(fxg_ctx *ctx, int si, const void *src, size_t n1, int is_last, int pair = 0,
+                             const void *src2 = nullptr, size_t n2 = 0)
 {
     Slot &s = ctx->slots[si];
     int rc;
+    const size_t nbytes = n1 + n2;
     if (nbytes > ctx->cfg.batch_bytes) return set_error(ctx, FXG_ERR_ARG, "batch larger than batch_bytes");
     if (!ctx->have_patterns) return set_error(ctx, FXG_ERR_STATE, "fxg_set_patterns has not been called");
     if ((rc = ensure_d_in(ctx, s, nbytes)) != FXG_OK) return rc;
     if (nbytes) {
-        FXG_CUDA_OK(cudaMemcpyAsync(s.d_in, src, nbytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+        if (n1) FXG_CUDA_OK(cudaMemcpyAsync(s.d_in, src, n1, cudaMemcpyHostToDevice, ctx->copy_stream));
+        if (n2) FXG_CUDA_OK(cudaMemcpyAsync(s.d_in + n1, src2, n2, cudaMemcpyHostToDevice, ctx->copy_stream));
         FXG_CUDA_OK(cudaEventRecord(s.h2d_done, ctx->copy_stream));
         FXG_CUDA_OK(cudaStreamWaitEvent(ctx->stream, s.h2d_done, 0));
     }
     s.is_last = is_last;
-    if ((rc = enqueue_raw(ctx, s.d_in, nbytes, s)) != FXG_OK) return rc;
+    if ((rc = enqueue_raw(ctx, s.d_in, nbytes, s, pair, src2 ? (uint64_t)n1 : 0)) != FXG_OK) return rc;
     s.state = 2;
     ctx->inflight.push_back(si);
     return FXG_OK;
@@ -854,6 +881,26 @@ extern "C" int fxg_submit_raw_from(fxg_ctx *ctx, const void *host_buf, size_t nb
     int si = free_slot(ctx);
     if (si < 0) return set_error(ctx, FXG_ERR_STATE, "both slots are in flight: call fxg_collect first");
     return submit_raw_common(ctx, si, host_buf, nbytes, is_last);
+}
+
+extern "C" int fxg_submit_raw_interleaved_from(fxg_ctx *ctx, const void *host_buf, size_t nbytes, int is_last)
+{
+    if (!ctx || (!host_buf && nbytes)) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    cudaSetDevice(ctx->cfg.device);
+    for (int i = 0; i < 2; ++i) if (ctx->slots[i].state == 1) return set_error(ctx, FXG_ERR_STATE, "a buffer is lent out");
+    int si = free_slot(ctx);
+    if (si < 0) return set_error(ctx, FXG_ERR_STATE, "both slots are in flight: call fxg_collect first");
+    return submit_raw_common(ctx, si, host_buf, nbytes, is_last, 1);
+}
+
+extern "C" int fxg_submit_raw_pair_from(fxg_ctx *ctx, const void *host1, size_t n1, const void *host2, size_t n2, int is_last)
+{
+    if (!ctx || !host1 || !host2 || !n1 || !n2) return set_error(ctx, FXG_ERR_ARG, "null argument or empty part");
+    cudaSetDevice(ctx->cfg.device);
+    for (int i = 0; i < 2; ++i) if (ctx->slots[i].state == 1) return set_error(ctx, FXG_ERR_STATE, "a buffer is lent out");
+    int si = free_slot(ctx);
+    if (si < 0) return set_error(ctx, FXG_ERR_STATE, "both slots are in flight: call fxg_collect first");
+    return submit_raw_common(ctx, si, host1, n1, is_last, 1, host2, n2);
 }
 
 extern "C" int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *off, uint32_t nrec)
@@ -987,6 +1034,17 @@ extern "C" int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t n
     cudaSetDevice(ctx->cfg.device);
     Slot &s = ctx->slots[2];
     int rc = enqueue_raw(ctx, (const uint8_t *)d_buf, (size_t)nbytes, s);
+    if (rc == FXG_OK) s.state = 2;
+    return rc;
+}
+
+extern "C" int fxg_scan_device_pairs_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes, uint64_t split)
+{
+    if (!ctx || (!d_buf && nbytes)) return set_error(ctx, FXG_ERR_ARG, "null argument");
+    if (((uintptr_t)d_buf & 15) != 0) return set_error(ctx, FXG_ERR_ARG, "d_buf must be 16-byte aligned (the tiles are fetched with bulk copies)");
+    cudaSetDevice(ctx->cfg.device);
+    Slot &s = ctx->slots[2];
+    int rc = enqueue_raw(ctx, (const uint8_t *)d_buf, (size_t)nbytes, s, 1, split);
     if (rc == FXG_OK) s.state = 2;
     return rc;
 }

@@ -71,6 +71,7 @@ struct ScanCounters {
     unsigned long long first_bad;     // min offset of a violation (tile granularity)
     unsigned int violation;           // FXG_V_* bitmask
     unsigned int last_byte;           // last byte of the batch (must be '\n')
+    unsigned long long n_pair_sel;    // pair submissions: selected pairs (pair_select_kernel)
 };
 
 // ---------------------------------------------------------------- literal matcher tables
@@ -318,7 +319,13 @@ cudaError_t launch_scan_kmer(const ScanParams &P, cudaStream_t stream, int dev);
 cudaError_t launch_scan_kmer_redo(const ScanParams &P, cudaStream_t stream, int dev);
 cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
-                           fxg_run *runs, unsigned long long run_cap, int invert, int *run_pid, cudaStream_t stream, int *launches);
+                           fxg_run *runs, unsigned long long run_cap, int invert, int *run_pid, int per_record,
+                           cudaStream_t stream, int *launches);
+// mates (fx.cpp:58-77): per-record hit bits -> per-pair selection under the strategy's rule -> selected bits of both
+// mates, ready for launch_compact with invert = 0.  split = 0: interleaved; else byte offset of the second file's part.
+struct PairRule { int invert; int need_neither; int all_match; };
+cudaError_t launch_pair_select(unsigned int *hitbits, unsigned int *pairsel, const ScanParams &P, unsigned long long rec_cap,
+                               unsigned long long split, PairRule rule, cudaStream_t stream, int *launches);
 cudaError_t launch_fields_literal(const FieldSrc &src, unsigned long long n, const LiteralFieldParams &L,
                                   const FieldOut &O, cudaStream_t st);
 cudaError_t launch_fields_ac(const FieldSrc &src, unsigned long long n, const AcDevice &A, const FieldOut &O, cudaStream_t st);

@@ -579,7 +579,8 @@ struct CompactParams {
     fxg_run *runs;
     unsigned long long run_cap;
     int invert;
-    int *run_pid;                   // routing: every selected record is its own run; pattern id per run (P.rec_first)
+    int *run_pid;                   // routing: pattern id per run (P.rec_first); implies per_record
+    int per_record;                 // every selected record is its own run (routing; mates from two files)
 };
 constexpr int kCompactThreads = 1024;
 
@@ -607,7 +608,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_count_kernel(const Co
     const unsigned long long w = (unsigned long long)blockIdx.x * kCompactThreads + threadIdx.x;
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
-    unsigned int starts = C.run_pid ? s : s & ~((s << 1) | prev_msb);
+    unsigned int starts = C.per_record ? s : s & ~((s << 1) | prev_msb);
     unsigned long long a = __popc(starts), b = __popc(s);
     for (int d = 16; d > 0; d >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, d); b += __shfl_xor_sync(0xffffffffu, b, d); }
     if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = b; }
@@ -658,8 +659,8 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
     unsigned int next_lsb = sel_word(C, w + 1, nrec) & 1u;
-    unsigned int starts = C.run_pid ? s : s & ~((s << 1) | prev_msb);
-    unsigned int ends = C.run_pid ? s : s & ~((s >> 1) | (next_lsb << 31));
+    unsigned int starts = C.per_record ? s : s & ~((s << 1) | prev_msb);
+    unsigned int ends = C.per_record ? s : s & ~((s >> 1) | (next_lsb << 31));
     unsigned long long n = __popc(starts), inc = n;
     for (int d = 1; d < 32; d <<= 1) { unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d); if ((threadIdx.x & 31) >= d) inc += o; }
     if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
@@ -701,11 +702,13 @@ __global__ void compact_fixup_kernel(const CompactParams C)
 
 cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, const ScanCounters *ctr,
                            unsigned long long rec_cap, unsigned long long *block_sums, unsigned long long *out_counts,
-                           fxg_run *runs, unsigned long long run_cap, int invert, int *run_pid, cudaStream_t stream, int *launches)
+                           fxg_run *runs, unsigned long long run_cap, int invert, int *run_pid, int per_record,
+                           cudaStream_t stream, int *launches)
 {
     CompactParams C;
     C.hitbits = hitbits; C.P = P; C.ctr = ctr; C.block_sums = block_sums;
     C.out_counts = out_counts; C.runs = runs; C.run_cap = run_cap; C.invert = invert; C.run_pid = run_pid;
+    C.per_record = (per_record || run_pid) ? 1 : 0;
     unsigned long long words = (rec_cap + 31) / 32;
     unsigned int nblocks = (unsigned int)((words + kCompactThreads - 1) / kCompactThreads);
     if (nblocks == 0) nblocks = 1;
@@ -714,6 +717,126 @@ cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, con
     compact_write_kernel<<<nblocks, kCompactThreads, 0, stream>>>(C);
     compact_fixup_kernel<<<148, 256, 0, stream>>>(C);
     if (launches) *launches += 4;
+    return cudaGetLastError();
+}
+
+// ================================================================= mates: per-record hits -> per-pair selection
+// Fxstream::read (fx.cpp:58-77) hands the strategies one pair at a time; what they do with the two mates' hits
+// (m1, m2) reduces, for everything but -l, to one selection bit per pair:
+//   simple_string_search (main.cpp:599-648)   select = -v ? !m1 : m1 | m2          (-v never looks at read 2, :618-619)
+//   hash_search          (main.cpp:311-346)   select = -v ? !m1 : m1 | m2          (a read-2 hit prints even under -v, :331-337)
+//   multipattern_search  (main.cpp:388-446)   select = -v ? !(m1 | m2) : m1 | m2   (:427-438)
+// pair_select_kernel evaluates that rule 32 pairs per thread from the finished per-record hit bit set and counts the
+// selected pairs; pair_spread_kernel writes the selection back as one bit per RECORD (both mates of a selected
+// pair), so that the compaction emits their byte runs in input order.  Layouts: interleaved -- mates are records
+// 2i, 2i+1; two files -- the batch is file 1's R records followed by file 2's R records, mates are i and R + i.
+struct PairParams {
+    unsigned int *hitbits;          // in: hit bit per record; out (pair_spread_kernel): selected bit per record
+    unsigned int *pairsel;          // scratch: selected bit per pair
+    ScanParams P;
+    unsigned long long rec_cap;
+    unsigned long long split;       // two files: byte offset of the second part; 0 = interleaved
+    PairRule rule;
+};
+
+__device__ __forceinline__ unsigned int even_bits(unsigned int x)     // bits 0,2,4,... of x -> bits 0..15
+{
+    x &= 0x55555555u;
+    x = (x | (x >> 1)) & 0x33333333u;
+    x = (x | (x >> 2)) & 0x0f0f0f0fu;
+    x = (x | (x >> 4)) & 0x00ff00ffu;
+    return (x | (x >> 8)) & 0xffffu;
+}
+__device__ __forceinline__ unsigned int twice_bits(unsigned int x)    // bit i of x (i < 16) -> bits 2i and 2i+1
+{
+    x = (x | (x << 8)) & 0x00ff00ffu;
+    x = (x | (x << 4)) & 0x0f0f0f0fu;
+    x = (x | (x << 2)) & 0x33333333u;
+    x = (x | (x << 1)) & 0x55555555u;
+    return x | (x << 1);
+}
+// 32 bits of a bit set starting at bit `first` (the set is readable one word past its end)
+__device__ __forceinline__ unsigned int bits_at(const unsigned int *set, unsigned long long first)
+{
+    const unsigned long long q = first >> 5;
+    return __funnelshift_r(set[q], set[q + 1], (unsigned int)(first & 31ull));
+}
+
+__global__ void __launch_bounds__(256) pair_select_kernel(const PairParams C)
+{
+    __shared__ unsigned int wsum[8];
+    unsigned long long nrec = C.P.ctr->n_lines >> 2;
+    if (nrec > C.rec_cap) nrec = C.rec_cap;
+    const unsigned long long npairs = nrec >> 1;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        // whole pairs only; two files: the second part starts exactly where record `npairs` starts
+        bool bad = (nrec & 1ull) != 0ull;
+        if (!bad && C.split && offset_after_line(C.P, 4ll * (long long)npairs - 1) != C.split) bad = true;
+        if (bad) atomicOr(&C.P.ctr->violation, (unsigned int)FXG_V_PAIRING);
+    }
+    const unsigned long long words = (npairs + 31) >> 5;
+    unsigned int n = 0;
+    for (unsigned long long w = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; w < words; w += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned int a, b;
+        if (C.rule.all_match) a = b = 0xffffffffu;
+        else if (C.split) { a = C.hitbits[w]; b = bits_at(C.hitbits, npairs + w * 32ull); }
+        else {
+            const unsigned int h0 = C.hitbits[2 * w], h1 = C.hitbits[2 * w + 1];
+            a = even_bits(h0) | (even_bits(h1) << 16);
+            b = even_bits(h0 >> 1) | (even_bits(h1 >> 1) << 16);
+        }
+        unsigned int sel = C.rule.invert ? (C.rule.need_neither ? ~(a | b) : ~a) : (a | b);
+        const unsigned long long left = npairs - w * 32ull;
+        if (left < 32ull) sel &= (1u << left) - 1u;
+        C.pairsel[w] = sel;
+        n += __popc(sel);
+    }
+    // one zero word behind the set: pair_spread_kernel reads one word past the last
+    if (blockIdx.x == 0 && threadIdx.x == 0) C.pairsel[words] = 0u;
+    n = __reduce_add_sync(0xffffffffu, n);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int tot = 0;
+        for (int i = 0; i < 8; ++i) tot += wsum[i];
+        if (tot) atomicAdd(&C.P.ctr->n_pair_sel, (unsigned long long)tot);
+    }
+}
+
+__global__ void __launch_bounds__(256) pair_spread_kernel(const PairParams C)
+{
+    unsigned long long nrec = C.P.ctr->n_lines >> 2;
+    if (nrec > C.rec_cap) nrec = C.rec_cap;
+    const unsigned long long npairs = nrec >> 1;
+    const unsigned long long words = (nrec + 31) >> 5;       // an odd last record (rejected batch) stays unselected
+    for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < words; k += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned int out;
+        if (!C.split) out = twice_bits((C.pairsel[k >> 1] >> ((unsigned int)(k & 1ull) * 16u)) & 0xffffu);
+        else {
+            const unsigned long long first = k * 32ull;       // records first .. first + 31
+            out = 0u;
+            if (first < npairs) {                              // file 1's part: pair i is record i
+                out = C.pairsel[k];
+                const unsigned long long left = npairs - first;
+                if (left < 32ull) out &= (1u << left) - 1u;
+            }
+            if (first + 32ull > npairs) {                      // file 2's part: pair i is record npairs + i
+                if (first >= npairs) out |= bits_at(C.pairsel, first - npairs);
+                else out |= C.pairsel[0] << (unsigned int)(npairs - first);
+            }
+        }
+        C.hitbits[k] = out;
+    }
+}
+
+cudaError_t launch_pair_select(unsigned int *hitbits, unsigned int *pairsel, const ScanParams &P, unsigned long long rec_cap,
+                               unsigned long long split, PairRule rule, cudaStream_t stream, int *launches)
+{
+    PairParams C;
+    C.hitbits = hitbits; C.pairsel = pairsel; C.P = P; C.rec_cap = rec_cap; C.split = split; C.rule = rule;
+    pair_select_kernel<<<148 * 2, 256, 0, stream>>>(C);
+    pair_spread_kernel<<<148 * 2, 256, 0, stream>>>(C);
+    if (launches) *launches += 2;
     return cudaGetLastError();
 }
 

@@ -83,6 +83,7 @@ public:
     // returns non-zero like Fxstream::open (second file + interleaved)
     int open(const char *file1, const char *file2, bool interleaved);
     void open_fd_at(int fd, uint64_t offset, const char *name);
+    void open_fds_at(int fd1, uint64_t off1, const char *name1, int fd2, uint64_t off2, const char *name2, bool interleaved);
     // appends pairs until `max_pairs` / `max_arena` is reached or the stream ends
     void read_batch(PairBatch &b, size_t max_pairs, size_t max_arena);
     const std::string &name1() const { return name1_; }
@@ -146,6 +147,8 @@ public:
     void submit_fields(size_t nbytes, const uint32_t *off, uint32_t n);
     void submit_raw(size_t nbytes, bool is_last);
     void submit_raw_from(const void *host, size_t nbytes, bool is_last);   // caller-owned pinned memory, next device in turn
+    // mates on the raw path: host2 == nullptr: interleaved (records 2i, 2i+1); else n1 bytes of file 1 + n2 bytes of file 2
+    void submit_raw_pairs_from(const void *host1, size_t n1, const void *host2, size_t n2, bool is_last);
     void collect(fxg_result *res);                              // oldest submitted batch
     void grow(size_t batch_bytes);                              // re-create the contexts with larger buffers (idle only)
 private:

@@ -97,6 +97,16 @@ void DevicePool::submit_raw_from(const void *host, size_t nbytes, bool is_last)
     turn_ = (turn_ + 1) % (int)ctx_.size();
 }
 
+void DevicePool::submit_raw_pairs_from(const void *host1, size_t n1, const void *host2, size_t n2, bool is_last)
+{
+    fxg_ctx *c = ctx_[turn_];
+    const int rc = host2 ? fxg_submit_raw_pair_from(c, host1, n1, host2, n2, is_last ? 1 : 0)
+                         : fxg_submit_raw_interleaved_from(c, host1, n1, is_last ? 1 : 0);
+    if (rc != FXG_OK) fail(c, "fxg_submit_raw_pair_from");
+    order_.push_back(turn_);
+    turn_ = (turn_ + 1) % (int)ctx_.size();
+}
+
 void DevicePool::collect(fxg_result *res)
 {
     if (order_.empty()) { fprintf(stderr, "fxtract: internal error: collect() with nothing in flight\n"); exit(1); }

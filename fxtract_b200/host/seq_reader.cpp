@@ -245,6 +245,19 @@ void PairSource::open_fd_at(int fd, uint64_t offset, const char *name)
     in1_.open_fd_at(fd, offset);
 }
 
+// raw-path re-route of mates: continue at a record boundary of both streams (fd2 < 0: interleaved, one stream)
+void PairSource::open_fds_at(int fd1, uint64_t off1, const char *name1, int fd2, uint64_t off2, const char *name2, bool interleaved)
+{
+    name1_ = name1 ? name1 : "";
+    in1_.open_fd_at(fd1, off1);
+    if (fd2 >= 0) {
+        name2_ = name2 ? name2 : "";
+        in2_.open_fd_at(fd2, off2);
+        have2_ = true;
+    }
+    interleaved_ = interleaved;
+}
+
 void PairSource::read_batch(PairBatch &b, size_t max_pairs, size_t max_arena)
 {
     while (!done_ && b.first.size() < max_pairs && b.arena.size() < max_arena) {

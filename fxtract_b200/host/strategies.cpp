@@ -26,6 +26,9 @@
 #include <sys/stat.h>
 #include <sys/uio.h>
 #include <unistd.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 #ifndef REG_BASIC
 #define REG_BASIC 0
@@ -209,6 +212,36 @@ bool run_fields(Job &job, Strategy st, PairSource &src, bool paired, DevicePool 
 }
 
 // ------------------------------------------------------------------ raw path
+// '\n' count of a slice (mates on the raw path: the host cuts both streams at the same record count, and canonical
+// FASTQ -- which the GPU predicate verifies -- has four lines per record)
+uint64_t count_newlines(const uint8_t *p, size_t n)
+{
+    uint64_t cnt = 0;
+    size_t i = 0;
+#if defined(__SSE2__)
+    const __m128i nl = _mm_set1_epi8('\n');
+    for (; i + 64 <= n; i += 64) {
+        const unsigned m0 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i)), nl));
+        const unsigned m1 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i + 16)), nl));
+        const unsigned m2 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i + 32)), nl));
+        const unsigned m3 = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i *)(p + i + 48)), nl));
+        cnt += (uint64_t)__builtin_popcountll((unsigned long long)m0 | ((unsigned long long)m1 << 16) |
+                                              ((unsigned long long)m2 << 32) | ((unsigned long long)m3 << 48));
+    }
+#endif
+    for (; i < n; ++i) cnt += p[i] == '\n';
+    return cnt;
+}
+
+// offset just behind the `skip`-th '\n' counted backwards from the end of buf[0, n) after dropping what follows the
+// last one: with L '\n' in the buffer, skip = L - K gives the offset behind the K-th.  (K >= 1.)
+size_t offset_behind_newline_from_end(const uint8_t *buf, size_t n, uint64_t skip)
+{
+    const uint8_t *e = (const uint8_t *)memrchr(buf, '\n', n);
+    while (e && skip--) e = (e > buf) ? (const uint8_t *)memrchr(buf, '\n', (size_t)(e - buf)) : nullptr;
+    return e ? (size_t)(e - buf) + 1 : 0;
+}
+
 // Host ingest of the raw path (hard part 5): the file is read in fixed windows by a team of
 // reader threads (pread of 4 MiB slices) straight into pinned buffers, several windows ahead of the GPU.  A window
 // becomes a batch once the unconsumed tail of its predecessor (a partial record, copied into the pad in front of
@@ -218,10 +251,12 @@ class RawIngest {
 public:
     static constexpr size_t kSlice = 4u << 20;
     // `pad` = room in front of every window for the carried partial record
-    RawIngest(int fd, uint64_t file_size, size_t window, size_t pad, int nbuf, int nthreads)
-        : fd_(fd), size_(file_size), window_(window), pad_(pad), nbuf_(nbuf)
+    // `nwin` > 0: that many windows (the ones past the end of the file are empty) -- mates from two files advance
+    // through both inputs in step
+    RawIngest(int fd, uint64_t file_size, size_t window, size_t pad, int nbuf, int nthreads, bool count_nl = false, uint64_t nwin = 0)
+        : fd_(fd), size_(file_size), window_(window), pad_(pad), nbuf_(nbuf), count_nl_(count_nl)
     {
-        nwin_ = (size_ + window_ - 1) / window_;
+        nwin_ = nwin ? nwin : (size_ + window_ - 1) / window_;
         bufs_.resize(nbuf_);
         for (Buf &b : bufs_) {
             void *p = nullptr;
@@ -229,6 +264,7 @@ public:
             b.mem = (uint8_t *)p;
         }
         done_.assign(nwin_, 0);
+        nl_.assign(nwin_, 0);
         for (int t = 0; t < nthreads; ++t) threads_.emplace_back([this] { work(); });
     }
     ~RawIngest()
@@ -239,6 +275,7 @@ public:
         for (Buf &b : bufs_) fxg_host_free(b.mem);
     }
     uint64_t windows() const { return nwin_; }
+    uint64_t window_lines(uint64_t k) const { return nl_[k]; }       // '\n' count of window k (count_nl; after wait_window)
     // blocks until window k is in memory; returns its first byte (`pad` bytes lie in front of it) and length
     uint8_t *wait_window(uint64_t k, size_t *len)
     {
@@ -257,7 +294,7 @@ public:
     }
 private:
     struct Buf { uint8_t *mem = nullptr; };
-    size_t win_len(uint64_t k) const { const uint64_t o = k * window_; return (size_t)std::min<uint64_t>(window_, size_ - o); }
+    size_t win_len(uint64_t k) const { const uint64_t o = k * window_; return o >= size_ ? 0 : (size_t)std::min<uint64_t>(window_, size_ - o); }
     size_t slices_in(uint64_t k) const { return (win_len(k) + kSlice - 1) / kSlice; }
     void work()
     {
@@ -265,7 +302,10 @@ private:
             uint64_t k; size_t s;
             {
                 std::unique_lock<std::mutex> l(mu_);
-                cv_.wait(l, [&] { return stop_ || failed_ || (next_win_ < nwin_ && next_win_ < low_ + (uint64_t)nbuf_); });
+                cv_.wait(l, [&] {
+                    while (next_win_ < nwin_ && slices_in(next_win_) == 0) ++next_win_;     // empty windows need no reader
+                    return stop_ || failed_ || (next_win_ < nwin_ && next_win_ < low_ + (uint64_t)nbuf_);
+                });
                 if (stop_ || failed_) return;
                 k = next_win_; s = next_slice_;
                 if (++next_slice_ >= slices_in(k)) { next_slice_ = 0; ++next_win_; }
@@ -279,12 +319,14 @@ private:
                 if (got <= 0) { bad = true; break; }          // the file shrank under us, or an I/O error
                 have += (size_t)got;
             }
-            { std::lock_guard<std::mutex> l(mu_); if (bad) failed_ = true; ++done_[k]; }
+            const uint64_t lines = (count_nl_ && !bad) ? count_newlines(dst, want) : 0;
+            { std::lock_guard<std::mutex> l(mu_); if (bad) failed_ = true; nl_[k] += lines; ++done_[k]; }
             cv_.notify_all();
         }
     }
-    int fd_; uint64_t size_; size_t window_, pad_; int nbuf_;
+    int fd_; uint64_t size_; size_t window_, pad_; int nbuf_; bool count_nl_;
     uint64_t nwin_ = 0;
+    std::vector<uint64_t> nl_;
     std::vector<Buf> bufs_;
     std::vector<size_t> done_;
     std::vector<std::thread> threads_;
@@ -306,7 +348,10 @@ RawMode raw_mode(const Job &job, Strategy st, const char *file2)
     const char *mode = getenv("FXTRACT_PATH");
     if (mode && !strcmp(mode, "fields")) return RAW_NO;
     const CliOptions &o = job.opt;
-    if (file2 || o.I) return RAW_NO;                 // mates need per-pair rules: fields path
+    // mates: the device applies the strategy's pair rule (run_raw_pairs); -l keeps its per-pair quirks (which file
+    // name is printed, main.cpp:427-435) on the fields path
+    if ((file2 || o.I) && o.l) return RAW_NO;
+    if ((file2 || o.I) && st == S_MULTI && o.Q) return RAW_NO;     // read 2 is searched in its SEQUENCE under -Q (main.cpp:416)
     if (job.router.all_stdout()) return RAW_PLAIN;   // includes -l: the first batch with a match ends the input
     if (o.l) return RAW_NO;                          // -l with output files: find()'s side effects need the pattern
     if (st == S_MULTI && (o.v || o.c)) return RAW_PLAIN;
@@ -418,6 +463,187 @@ int64_t run_raw(Job &job, Strategy st, const char *file1, int fd, DevicePool &po
     return (int64_t)file_size;
 }
 
+// ------------------------------------------------------------------ raw path, mates (two files / -I)
+// Fxstream::read (fx.cpp:58-77) pairs record i of file 1 with record i of file 2 (or records 2i, 2i+1 of one
+// interleaved file) and ends at the first failed read of either.  Both streams are read in windows like run_raw;
+// the reader threads also count the '\n' of every slice, so the host can cut both streams at the same number of
+// whole records (four lines each -- verified on the device, which raises FXG_V_PAIRING otherwise) without parsing.
+struct MateStream {
+    std::unique_ptr<RawIngest> in;
+    size_t pad = 0;
+    const uint8_t *carry = nullptr; size_t carry_n = 0; uint64_t carry_lines = 0;
+    uint64_t consumed = 0;                 // file offset where the next batch starts
+    uint8_t *batch = nullptr; size_t have = 0; uint64_t lines = 0;
+    // carried tail + window k -> batch / have / lines; false: the carry does not fit in front of the window
+    bool load(uint64_t k, double &t_wait)
+    {
+        size_t wlen;
+        const double t0 = now_s();
+        uint8_t *w = in->wait_window(k, &wlen);
+        t_wait += now_s() - t0;
+        if (carry_n > pad) return false;
+        batch = w - carry_n;
+        if (carry_n) memmove(batch, carry, carry_n);
+        have = carry_n + wlen;
+        lines = carry_lines + in->window_lines(k);
+        return true;
+    }
+    // keep the first `recs` records for this batch, carry the rest; returns the batch's byte length
+    size_t cut(uint64_t recs)
+    {
+        const size_t n = recs ? offset_behind_newline_from_end(batch, have, lines - 4 * recs) : 0;
+        carry = batch + n; carry_n = have - n; carry_lines = lines - 4 * recs;
+        return n;
+    }
+};
+
+struct MatePending { const uint8_t *host1, *host2; size_t n1; uint64_t off1, off2, window; };
+
+// Returns false when the raw path is not applicable (nothing consumed); else `next1` / `next2` are the offsets from
+// which the fields path has to continue (== file sizes when everything was handled here).
+bool run_raw_pairs(Job &job, Strategy st, int fd1, int fd2, DevicePool &pool, Stats &stats, uint64_t &next1, uint64_t &next2, bool &finished)
+{
+    const bool two = fd2 >= 0;
+    struct stat sb1, sb2;
+    if (fstat(fd1, &sb1) != 0 || !S_ISREG(sb1.st_mode)) return false;
+    if (two && (fstat(fd2, &sb2) != 0 || !S_ISREG(sb2.st_mode))) return false;
+    unsigned char magic = 0;
+    if (pread(fd1, &magic, 1, 0) < 1 || magic != '@') return false;
+    if (two && (pread(fd2, &magic, 1, 0) < 1 || magic != '@')) return false;
+    const CliOptions &o = job.opt;
+    const uint64_t size1 = (uint64_t)sb1.st_size, size2 = two ? (uint64_t)sb2.st_size : 0;
+    const size_t pad = std::min<size_t>((size_t)1 << 20, pool.batch_bytes() / 8) & ~(size_t)63;
+    const int nstreams = two ? 2 : 1;
+    if (pool.batch_bytes() < (size_t)nstreams * pad + 4096) return false;
+    const size_t usable = pool.batch_bytes() - (size_t)nstreams * pad - 128;
+    const uint64_t nwin = std::max<uint64_t>(1, (size1 + size2 + usable - 1) / usable);
+    const int nbuf = (int)pool.capacity() + 3;
+    const int readers = std::max(1, reader_threads_from_env() / nstreams);
+    MateStream ms[2];
+    const double t_setup0 = now_s();
+    for (int i = 0; i < nstreams; ++i) {
+        const uint64_t size = i ? size2 : size1;
+        const size_t window = (size_t)((((size + nwin - 1) / nwin) + 63) & ~(uint64_t)63);
+        ms[i].pad = pad;
+        ms[i].in.reset(new RawIngest(i ? fd2 : fd1, size, std::max<size_t>(window, 64), pad, nbuf, readers, true, nwin));
+    }
+    stats.t_setup += now_s() - t_setup0;
+    std::deque<MatePending> pending;
+    bool reroute = false;
+    uint64_t re1 = 0, re2 = 0;
+    std::vector<struct iovec> iov;
+    auto finish_oldest = [&]() {
+        fxg_result r;
+        const double t0 = now_s();
+        pool.collect(&r);
+        const double t1 = now_s();
+        stats.t_gpu += t1 - t0;
+        MatePending p = pending.front();
+        pending.pop_front();
+        if (!reroute) {
+            if (!r.canonical_ok) { reroute = true; re1 = p.off1; re2 = p.off2; stats.rerouted++; }
+            else {
+                if (o.c) job.matched_records += (long)r.n_selected;
+                else if (!two && !r.run_pattern_id) write_runs(p.host1, r.runs, r.n_runs);      // interleaved: a pair is one byte range
+                else {
+                    // one run per record: interleaved -- mates are runs 2k, 2k+1; two files -- runs k and n/2 + k,
+                    // the second with its offset relative to the concatenation of both parts
+                    const uint64_t np = r.n_runs / 2;
+                    auto mate = [&](uint64_t k, int which, const uint8_t *&ptr, size_t &len, int &pid) {
+                        const uint64_t idx = two ? (which ? np + k : k) : 2 * k + (uint64_t)which;
+                        const fxg_run &run = r.runs[idx];
+                        ptr = (two && which) ? p.host2 + (run.off - p.n1) : p.host1 + run.off;
+                        len = (size_t)run.len;
+                        pid = r.run_pattern_id ? r.run_pattern_id[idx] : -1;
+                    };
+                    if (r.run_pattern_id) {                                 // per-pattern output files: read 1's pattern if it
+                        for (uint64_t k = 0; k < np; ++k) {                 // has one, else read 2's (main.cpp:408-435, :315-337)
+                            const uint8_t *a, *b; size_t la, lb; int pa, pb;
+                            mate(k, 0, a, la, pa); mate(k, 1, b, lb, pb);
+                            FILE *out = job.router.find(pa >= 0 ? pa : pb);
+                            if (out) { fwrite(a, 1, la, out); fwrite(b, 1, lb, out); }
+                        }
+                    } else {
+                        fflush(stdout);
+                        constexpr size_t kIov = 512;
+                        for (uint64_t k0 = 0; k0 < np; k0 += kIov / 2) {
+                            iov.clear();
+                            size_t want = 0;
+                            for (uint64_t k = k0; k < np && k < k0 + kIov / 2; ++k)
+                                for (int which = 0; which < 2; ++which) {
+                                    const uint8_t *ptr; size_t len; int pid;
+                                    mate(k, which, ptr, len, pid);
+                                    iov.push_back({const_cast<uint8_t *>(ptr), len});
+                                    want += len;
+                                }
+                            size_t first = 0;
+                            while (want) {
+                                ssize_t got = writev(STDOUT_FILENO, iov.data() + first, (int)(iov.size() - first));
+                                if (got < 0) { if (errno == EINTR) continue; perror("fxtract: write"); exit(1); }
+                                want -= (size_t)got;
+                                while (got > 0 && first < iov.size()) {
+                                    if ((size_t)got >= iov[first].iov_len) { got -= (ssize_t)iov[first].iov_len; ++first; }
+                                    else { iov[first].iov_base = (uint8_t *)iov[first].iov_base + got; iov[first].iov_len -= (size_t)got; got = 0; }
+                                }
+                            }
+                        }
+                    }
+                }
+                stats.records += r.n_records;
+                stats.t_write += now_s() - t1;
+            }
+        }
+        for (int i = 0; i < nstreams; ++i) ms[i].in->release_window(p.window);
+    };
+    auto drain = [&]() { while (!pending.empty()) finish_oldest(); };
+    auto reroute_here = [&]() {
+        drain();
+        if (!reroute) { reroute = true; re1 = ms[0].consumed; re2 = ms[1].consumed; }
+    };
+    for (uint64_t k = 0; k < nwin && !reroute; ++k) {
+        if (pool.inflight() == pool.capacity()) { finish_oldest(); if (reroute) break; }
+        bool fits = true;
+        for (int i = 0; i < nstreams; ++i) fits = ms[i].load(k, stats.t_ingest) && fits;
+        if (!fits) { reroute_here(); break; }                       // a carried tail longer than the pad
+        const bool last = k + 1 == nwin;
+        if (last) {
+            // a last line without '\n' or a record cut short is the tokenizer's business (kseq.hpp:120-164)
+            bool whole = true;
+            for (int i = 0; i < nstreams; ++i)
+                if (ms[i].have && (ms[i].batch[ms[i].have - 1] != '\n' || (ms[i].lines & 3))) whole = false;
+            if (!whole) { reroute_here(); break; }
+        }
+        uint64_t recs = ms[0].lines / 4;
+        if (two) recs = std::min<uint64_t>(recs, ms[1].lines / 4);
+        else recs &= ~1ull;                                          // whole pairs; an odd last record has no mate (fx.cpp:64-69)
+        if (recs == 0) {
+            if (last) break;                                         // one stream has no record left: the pair stream ends
+            reroute_here();                                          // no whole pair in a whole window
+            break;
+        }
+        const size_t n1 = ms[0].cut(recs), n2 = two ? ms[1].cut(recs) : 0;
+        if (n1 == 0 || (two && n2 == 0)) { reroute_here(); break; }
+        const double ts = now_s();
+        pool.submit_raw_pairs_from(ms[0].batch, n1, two ? ms[1].batch : nullptr, n2, last);
+        stats.t_submit += now_s() - ts;
+        pending.push_back(MatePending{ms[0].batch, two ? ms[1].batch : nullptr, n1, ms[0].consumed, ms[1].consumed, k});
+        ms[0].consumed += n1; ms[1].consumed += n2;
+        stats.raw_bytes += n1 + n2; stats.raw_batches++;
+    }
+    drain();
+    finished = !reroute;
+    if (reroute) {
+        const char *mode = getenv("FXTRACT_PATH");
+        if (mode && !strcmp(mode, "raw")) {
+            fprintf(stderr, "fxtract: FXTRACT_PATH=raw but the mates are not canonical FASTQ at bytes %llu / %llu\n",
+                    (unsigned long long)re1, (unsigned long long)re2);
+            exit(1);
+        }
+        next1 = re1; next2 = re2;
+    } else { next1 = size1; next2 = size2; }
+    return true;
+}
+
 // ------------------------------------------------------------------ POSIX regex (outside the graft; CPU, main.cpp:462-514)
 int run_regex(Job &job, PairSource &src, bool paired, regex_t *re)
 {
@@ -515,7 +741,27 @@ int run_input(Job &job, const char *file1, const char *file2)
     uint64_t input_bytes = 0;
     bool done = false;
     if (rm == RAW_ROUTED && !pool.can_route()) rm = RAW_NO;       // pattern set not served by a fused matcher
-    if (rm != RAW_NO) {
+    if (rm != RAW_NO && paired) {
+        const int fd1 = open(file1, O_RDONLY), fd2 = file2 ? open(file2, O_RDONLY) : -1;
+        if (fd1 >= 0 && (!file2 || fd2 >= 0)) {
+            uint64_t next1 = 0, next2 = 0;
+            bool finished = false;
+            if (run_raw_pairs(job, st, fd1, fd2, pool, stats, next1, next2, finished)) {
+                struct stat sb;
+                fstat(fd1, &sb);
+                input_bytes = (uint64_t)sb.st_size;
+                if (fd2 >= 0) { fstat(fd2, &sb); input_bytes += (uint64_t)sb.st_size; }
+                if (!finished) {
+                    PairSource rest;                             // both streams stand at a FASTQ record boundary
+                    rest.open_fds_at(fd1, next1, file1, fd2, next2, file2, o.I);
+                    run_fields(job, st, rest, true, pool, stats);
+                }
+                done = true;
+            }
+        }
+        if (fd1 >= 0) close(fd1);
+        if (fd2 >= 0) close(fd2);
+    } else if (rm != RAW_NO) {
         int fd = open(file1, O_RDONLY);
         if (fd >= 0) {
             int64_t next = run_raw(job, st, file1, fd, pool, stats);

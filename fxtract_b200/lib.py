@@ -39,7 +39,8 @@ class SynthSpec(C.Structure):
 
 
 EXPORTS = ["fxg_device_count", "fxg_create", "fxg_destroy", "fxg_last_error", "fxg_set_patterns",
-           "fxg_acquire_buffer", "fxg_submit_raw", "fxg_submit_raw_from", "fxg_submit_fields", "fxg_collect",
+           "fxg_acquire_buffer", "fxg_submit_raw", "fxg_submit_raw_from", "fxg_submit_raw_interleaved_from",
+           "fxg_submit_raw_pair_from", "fxg_scan_device_pairs_async", "fxg_submit_fields", "fxg_collect",
            "fxg_count", "fxg_find_record_cut", "fxg_scan_device_async", "fxg_scan_device_finish",
            "fxg_can_route", "fxg_last_launch_count", "fxg_last_d2h_bytes", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
            "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free", "fxg_copy_to_host", "fxg_copy_to_device"]
@@ -64,6 +65,9 @@ def load_library():
     lib.fxg_acquire_buffer.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
     lib.fxg_submit_raw.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
     lib.fxg_submit_raw_from.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+    lib.fxg_submit_raw_interleaved_from.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+    lib.fxg_submit_raw_pair_from.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int]
+    lib.fxg_scan_device_pairs_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64]
     lib.fxg_submit_fields.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_uint32), C.c_uint32]
     lib.fxg_collect.argtypes = [C.c_void_p, C.POINTER(Result)]
     lib.fxg_count.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
@@ -180,6 +184,12 @@ class Context:
     def submit_raw_from(self, ptr, nbytes, is_last=False):
         self._check(self.lib.fxg_submit_raw_from(self.h, C.c_void_p(ptr), nbytes, int(is_last)))
 
+    def submit_raw_interleaved_from(self, ptr, nbytes, is_last=False):
+        self._check(self.lib.fxg_submit_raw_interleaved_from(self.h, C.c_void_p(ptr), nbytes, int(is_last)))
+
+    def submit_raw_pair_from(self, ptr1, n1, ptr2, n2, is_last=False):
+        self._check(self.lib.fxg_submit_raw_pair_from(self.h, C.c_void_p(ptr1), n1, C.c_void_p(ptr2), n2, int(is_last)))
+
     def submit_fields(self, fields):
         p, cap = self.acquire()
         blob = b"".join(fields)
@@ -201,6 +211,9 @@ class Context:
     # ---- device-resident path
     def scan_device_async(self, dptr, nbytes):
         self._check(self.lib.fxg_scan_device_async(self.h, C.c_void_p(dptr), nbytes))
+
+    def scan_device_pairs_async(self, dptr, nbytes, split):
+        self._check(self.lib.fxg_scan_device_pairs_async(self.h, C.c_void_p(dptr), nbytes, split))
 
     def scan_device_finish(self):
         r = Result()

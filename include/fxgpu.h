@@ -54,7 +54,9 @@ enum { FXG_V_BYTE_RANGE = 1,      /* byte outside {'\n'} U [0x20,0x7e] */
        FXG_V_QUAL_LEN = 64,       /* |qual| != |seq| (kseq.hpp:161) */
        FXG_V_HEADER_SPACE = 128,  /* header separator would not round-trip (kseq.cpp:35-37) */
        FXG_V_DENSE_LINES = 256,   /* pathological newline density */
-       FXG_V_TRUNCATED = 512 };   /* line count not a multiple of 4 / no final newline */
+       FXG_V_TRUNCATED = 512,     /* line count not a multiple of 4 / no final newline */
+       FXG_V_PAIRING = 1024 };    /* pair submissions: the mates do not pair up inside the batch (odd record
+                                   * count, or the two files' parts do not hold the same number of records) */
 
 typedef struct fxg_ctx fxg_ctx;
 
@@ -115,6 +117,23 @@ int fxg_submit_raw(fxg_ctx *ctx, size_t nbytes, int is_last);
  * fxg_host_alloc): copied straight from there, no staging copy.  nbytes must be
  * <= cfg.batch_bytes; the memory must stay valid until the batch is collected. */
 int fxg_submit_raw_from(fxg_ctx *ctx, const void *host_buf, size_t nbytes, int is_last);
+/* Mates on the raw path (Fxstream::read, fx.cpp:58-77; the pair rules of simple_string_search main.cpp:599-648,
+ * hash_search main.cpp:311-346 and multipattern_search main.cpp:388-446).  Both calls take caller-owned (ideally
+ * pinned) memory like fxg_submit_raw_from and are collected with fxg_collect.  The per-strategy rule is applied on
+ * the device: a pair is selected when either mate has a hit; under cfg.invert when read 1 has none (LITERAL, EXACT:
+ * main.cpp:618-619, :331-343) or when neither mate has one (MULTI: main.cpp:427-438).  In the result n_records,
+ * n_matched and n_selected count PAIRS (n_matched == n_selected), and a batch whose mates do not pair up raises
+ * FXG_V_PAIRING (canonical_ok = 0: the caller re-routes it like any other rejected batch).  route_runs: every
+ * record of a selected pair carries the first-hit pattern id of that record (-1 when the record itself has none);
+ * the pair's file is read 1's pattern if it has one, else read 2's (main.cpp:408-435, :315-337).
+ *   interleaved (-I): mates are records 2i and 2i+1 of the batch, which must hold whole pairs.  Runs as in
+ *     fxg_submit_raw_from (a selected pair is 8 consecutive lines).
+ *   two files: the batch is n1 bytes of file 1 and n2 bytes of file 2 (n1 + n2 <= cfg.batch_bytes), each made of
+ *     the same number of whole records; mate i of file 1 pairs with mate i of file 2.  Every selected record is
+ *     its own run: the first n_runs / 2 runs are the selected records of file 1 (offsets into host1), the second
+ *     half their mates in the same order, with offsets relative to the concatenation (off - n1 indexes host2). */
+int fxg_submit_raw_interleaved_from(fxg_ctx *ctx, const void *host_buf, size_t nbytes, int is_last);
+int fxg_submit_raw_pair_from(fxg_ctx *ctx, const void *host1, size_t n1, const void *host2, size_t n2, int is_last);
 /* Fields path: the acquired buffer holds nrec target fields back to back
  * (nbytes total); off[nrec+1] are their offsets; asynchronous. */
 int fxg_submit_fields(fxg_ctx *ctx, size_t nbytes, const uint32_t *off, uint32_t nrec);
@@ -133,6 +152,9 @@ size_t fxg_find_record_cut(const uint8_t *buf, size_t n);
  * d_buf must be 16-byte aligned (the tiles are fetched with bulk copies; FXG_ERR_ARG otherwise) and readable for
  * 16 bytes past nbytes (edge look-ups and candidate verification read whole aligned words). */
 int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes);
+/* The same for mates already in HBM: split == 0: interleaved; else d_buf[0..split) holds file 1's records and
+ * d_buf[split..nbytes) their mates (see fxg_submit_raw_pair_from). */
+int fxg_scan_device_pairs_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes, uint64_t split);
 int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res);
 /* 1 iff the context can serve cfg.route_runs on the raw path with the current pattern set (EXACT always; MULTI
  * when the set is served by the fused window matcher); otherwise the caller keeps such inputs on the fields path. */

@@ -25,6 +25,7 @@ struct fxg_ctx {
     uint8_t *flags[2]; int32_t *pid[2]; uint64_t nrec[2], nhit[2]; int raw[2];
     int fifo[2]; int nfifo;
     const uint8_t *rawp[2]; size_t rawn[2]; fxg_run *runs[2];   /* FXSHIM_RAW=1: a plain CPU walk over canonical FASTQ */
+    int pair[2]; const uint8_t *rawp2[2]; size_t rawn2[2];      /* mates: 1 interleaved, 2 two files */
 };
 
 static const char *g_err = "";
@@ -98,11 +99,44 @@ int fxg_submit_raw_from(fxg_ctx *c, const void *h, size_t n, int l)
     (void)l;
     for (int i = 0; i < 2; ++i) if (c->state[i] == 0) {
         c->raw[i] = n ? 1 : 2; c->state[i] = 2; c->fifo[c->nfifo++] = i;
-        c->rawp[i] = (const uint8_t *)h; c->rawn[i] = n;
+        c->rawp[i] = (const uint8_t *)h; c->rawn[i] = n; c->pair[i] = 0;
         return FXG_OK;
     }
     g_err = "both slots are in flight";
     return FXG_ERR_STATE;
+}
+int fxg_submit_raw_interleaved_from(fxg_ctx *c, const void *h, size_t n, int l)
+{
+    int rc = fxg_submit_raw_from(c, h, n, l);
+    if (rc == FXG_OK) c->pair[c->fifo[c->nfifo - 1]] = 1;
+    return rc;
+}
+int fxg_submit_raw_pair_from(fxg_ctx *c, const void *h1, size_t n1, const void *h2, size_t n2, int l)
+{
+    int rc = fxg_submit_raw_from(c, h1, n1, l);
+    if (rc == FXG_OK) { int s = c->fifo[c->nfifo - 1]; c->pair[s] = 2; c->rawp2[s] = (const uint8_t *)h2; c->rawn2[s] = n2; }
+    return rc;
+}
+
+/* FXSHIM_RAW: records of a part of whole 4-line records; returns the record count or -1 */
+static long shim_walk(fxg_ctx *c, const uint8_t *b, size_t n, size_t base, uint8_t **hits, fxg_run **recs, long have)
+{
+    size_t pos = 0;
+    while (pos < n) {
+        size_t e[4], q = pos;
+        for (int k = 0; k < 4; ++k) {
+            const uint8_t *nl = (const uint8_t *)memchr(b + q, '\n', n - q);
+            if (!nl) return -1;
+            e[k] = (size_t)(nl - b); q = e[k] + 1;
+        }
+        if (b[pos] != '@') return -1;
+        int hit = 0;
+        for (uint32_t p = 0; p < c->n && p < 2 && !hit; ++p)
+            hit = find_bytes(b + e[0] + 1, e[1] - e[0] - 1, c->blob + c->off[p], c->off[p + 1] - c->off[p]) != NULL;
+        (*hits)[have] = (uint8_t)hit; (*recs)[have].off = base + pos; (*recs)[have].len = q - pos;
+        ++have; pos = q;
+    }
+    return have;
 }
 int fxg_host_alloc(void **p, size_t n) { *p = malloc(n); return *p ? FXG_OK : FXG_ERR_NOMEM; }
 int fxg_host_free(void *p) { free(p); return FXG_OK; }
@@ -150,7 +184,41 @@ int fxg_collect(fxg_ctx *c, fxg_result *r)
     int s = c->fifo[0];
     c->fifo[0] = c->fifo[1]; c->nfifo--;
     memset(r, 0, sizeof *r);
-    if (c->raw[s] == 1 && getenv("FXSHIM_RAW") && c->cfg.mode == FXG_MODE_LITERAL && c->cfg.target == FXG_TARGET_SEQ) {
+    if (c->raw[s] == 1 && c->pair[s] && getenv("FXSHIM_RAW") && c->cfg.mode == FXG_MODE_LITERAL && c->cfg.target == FXG_TARGET_SEQ) {
+        /* mates (host-ingest tests): literal rule select = -v ? !m1 : m1 | m2; counts in pairs */
+        const size_t cap = (c->rawn[s] + (c->pair[s] == 2 ? c->rawn2[s] : 0)) / 8 + 2;
+        uint8_t *hits = (uint8_t *)malloc(cap); fxg_run *recs = (fxg_run *)malloc(sizeof(fxg_run) * cap);
+        long n1 = shim_walk(c, c->rawp[s], c->rawn[s], 0, &hits, &recs, 0), nrec = n1;
+        if (n1 >= 0 && c->pair[s] == 2) nrec = shim_walk(c, c->rawp2[s], c->rawn2[s], c->rawn[s], &hits, &recs, n1);
+        r->canonical_ok = nrec >= 0 && (nrec & 1) == 0 && (c->pair[s] == 1 || nrec == 2 * n1);
+        if (!r->canonical_ok) { r->violation = FXG_V_PAIRING; free(hits); free(recs); c->state[s] = 0; return FXG_OK; }
+        const long np = nrec / 2;
+        free(c->runs[s]); c->runs[s] = (fxg_run *)malloc(sizeof(fxg_run) * (size_t)(nrec + 2));
+        uint8_t *sel = (uint8_t *)calloc((size_t)np + 1, 1);
+        for (long i = 0; i < np; ++i) {
+            const int m1 = c->pair[s] == 1 ? hits[2 * i] : hits[i], m2 = c->pair[s] == 1 ? hits[2 * i + 1] : hits[np + i];
+            sel[i] = (uint8_t)(c->cfg.invert ? !m1 : (m1 | m2));
+            r->n_selected += sel[i];
+        }
+        r->n_records = (uint64_t)np; r->n_matched = r->n_selected;
+        if (!c->cfg.count_only) {
+            if (c->pair[s] == 1) {                       /* merged runs of consecutive selected pairs */
+                for (long i = 0; i < np; ++i) {
+                    if (!sel[i]) continue;
+                    const uint64_t off = recs[2 * i].off, len = recs[2 * i].len + recs[2 * i + 1].len;
+                    if (r->n_runs && c->runs[s][r->n_runs - 1].off + c->runs[s][r->n_runs - 1].len == off && i && sel[i - 1])
+                        c->runs[s][r->n_runs - 1].len += len;
+                    else { c->runs[s][r->n_runs].off = off; c->runs[s][r->n_runs++].len = len; }
+                }
+            } else {                                     /* one run per record: file 1's, then their mates */
+                for (int which = 0; which < 2; ++which)
+                    for (long i = 0; i < np; ++i) if (sel[i]) c->runs[s][r->n_runs++] = recs[which * np + i];
+            }
+        }
+        r->runs = c->runs[s];
+        r->consumed_bytes = c->rawn[s] + (c->pair[s] == 2 ? c->rawn2[s] : 0);
+        free(sel); free(hits); free(recs);
+    } else if (c->raw[s] == 1 && !c->pair[s] && getenv("FXSHIM_RAW") && c->cfg.mode == FXG_MODE_LITERAL && c->cfg.target == FXG_TARGET_SEQ) {
         /* host-ingest tests: the batch must be whole 4-line records; literal search on the sequence line, runs of
          * consecutive selected records (NOT the product's algorithm, and no validation beyond the line count) */
         const uint8_t *b = c->rawp[s]; size_t n = c->rawn[s], pos = 0, run_start = 0; int in_run = 0;

@@ -107,3 +107,37 @@ def test_raw_ingest_windows_and_carry(shim_env, tmp_path):
             assert r2.returncode == 0, (argv, r2.stderr[-300:])
             assert r1.stdout == r2.stdout, (mib, readers, devs, argv, len(r1.stdout), len(r2.stdout), r2.stderr[-300:])
             assert b"raw 0 B" not in r2.stderr and b"0 re-routed" in r2.stderr, r2.stderr
+
+
+def test_raw_ingest_mates(shim_env, tmp_path):
+    """Mates on the raw path (strategies.cpp, run_raw_pairs): two files cut at equal record counts from the reader
+    threads' newline counts, interleaved input cut at whole pairs, carried tails, unequal files, an odd record, a
+    truncated last record (re-routed to the fields path).  The shim applies the literal pair rule on the CPU
+    (FXSHIM_RAW=1); the kernels are not under test here."""
+    if not os.path.exists(helpers.REF_CLI):
+        pytest.skip("oracle/_ref/fxtract not built")
+    rng = random.Random(9)
+    wd = str(tmp_path)
+    a = helpers.make_fastq(rng, 30000, seqlen=(30, 300), name_prefix="a")
+    b = helpers.make_fastq(rng, 30000, seqlen=(20, 120), name_prefix="b")
+    recs_b = b.split(b"\n@b")
+    short_b = b"\n@b".join(recs_b[:25000]) + b"\n"
+    files = {"a.fq": a, "b.fq": b, "bs.fq": short_b, "odd.fq": b"\n@a".join(a.split(b"\n@a")[:20001]) + b"\n",
+             "cut.fq": a[:len(a) - 7]}
+    for name, data in files.items():
+        open(os.path.join(wd, name), "wb").write(data)
+    pat = helpers.pick_substring(rng, a, 5, 6).decode()
+    cases_ = ([pat, "a.fq", "b.fq"], ["-v", pat, "a.fq", "b.fq"], ["-c", pat, "a.fq", "b.fq"], ["-cv", pat, "b.fq", "a.fq"],
+              [pat, "a.fq", "bs.fq"], [pat, "bs.fq", "a.fq"], ["-I", pat, "a.fq"], ["-Iv", pat, "a.fq"], ["-Ic", pat, "odd.fq"],
+              ["-I", pat, "odd.fq"], [pat, "cut.fq", "b.fq"], ["-I", pat, "cut.fq"], ["-c", pat, "a.fq", "b.fq", "b.fq", "a.fq"])
+    for mib, readers, devs in (("1", "2", "0"), ("2", "6", "0,0,0"), ("64", "4", "0,0")):
+        env = dict(shim_env, FXSHIM_RAW="1", FXTRACT_BATCH_MIB=mib, FXTRACT_READERS=readers, FXTRACT_DEVICES=devs, FXTRACT_STATS="1")
+        for argv in cases_:
+            r1 = subprocess.run([helpers.REF_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+            r2 = subprocess.run([helpers.PRODUCT_CLI] + argv, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=120)
+            assert r2.returncode == 0, (argv, r2.stderr[-300:])
+            assert r1.stdout == r2.stdout, (mib, readers, devs, argv, len(r1.stdout), len(r2.stdout), r2.stderr[-400:])
+            if "cut.fq" not in argv or mib != "64":        # one window: the truncated record sends all of it to the fields path
+                assert b"raw 0 B" not in r2.stderr, (argv, r2.stderr)
+            if "cut.fq" not in argv and "bs.fq" not in argv:
+                assert b" 0 re-routed" in r2.stderr, (argv, r2.stderr)
