@@ -50,8 +50,8 @@ template <class G> struct __align__(128) ScanSmem {
     unsigned short wm[G::kWarps][G::kWarpChunks];     // per entry of wl: 16-bit mask of the bytes < 0x20 of that chunk
     unsigned int wtot[2][G::kWarps];                  // '\n' count of each warp's 2 KiB segment (by tile parity)
     unsigned int below[17];                           // interleaved-layout mask of the bytes < p of a chunk
-    unsigned int sbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x41 (not a sequence letter)
-    unsigned int qbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x21 (not a quality char)
+    __align__(16) unsigned int sbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x41 (not a sequence letter)
+    __align__(16) unsigned int qbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x21 (not a quality char)
     unsigned int linehit[G::kHitWords];               // bit i: local line i has a (phase-conditional) match
     unsigned long long mbar[2];                       // bulk-copy completion barriers
     // per-tile scalars, double buffered by tile parity: the copy of the previous tile is reset by
@@ -522,22 +522,38 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
         unsigned int wcount = 0;
         {
             unsigned int hi_acc = 0;
+#if defined(FXG_VAR_ROWS128)
+            unsigned int sb_all[kChunksPerThread], qb_all[kChunksPerThread];
+#endif
 #pragma unroll
             for (int j = 0; j < kChunksPerThread; ++j) {
                 const int c = warp * kWarpChunks + j * 32 + lane;
                 const uint4 x = tile[c];
-                hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);     // bytes >= 0x7f anywhere
+                // bytes >= 0x7f anywhere: bit 7 of (byte + 1).  Only a byte 0xff escapes this sum (it wraps to 0 and
+                // carries into its neighbour) -- and every 0xff is caught on another way: + 0x5f and + 0x60 wrap as
+                // well, so it is listed as a '\n' candidate, enters the position table as a byte < 0x20, and the
+                // per-line check "the byte at a line end is '\n'" (step 4) raises FXG_V_BYTE_RANGE for it.
+#if defined(FXG_VAR_OLDRANGE)
+                hi_acc |= x.x | fma_add(x.x, one, 0x01010101u);
                 hi_acc |= x.y | fma_add(x.y, one, 0x01010101u);
                 hi_acc |= x.z | fma_add(x.z, one, 0x01010101u);
                 hi_acc |= x.w | fma_add(x.w, one, 0x01010101u);
+#else
+                hi_acc |= fma_add(x.x, one, 0x01010101u) | fma_add(x.y, one, 0x01010101u);
+                hi_acc |= fma_add(x.z, one, 0x01010101u) | fma_add(x.w, one, 0x01010101u);
+#endif
                 const bool s_any = ((fma_add(x.x, one, kAdd41) & fma_add(x.y, one, kAdd41) & fma_add(x.z, one, kAdd41) &
                                      fma_add(x.w, one, kAdd41)) & kHi) != kHi;
                 const bool q_any = ((fma_add(x.x, one, kAdd21) & fma_add(x.y, one, kAdd21) & fma_add(x.z, one, kAdd21) &
                                      fma_add(x.w, one, kAdd21)) & kHi) != kHi;
                 const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
                 const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
+#if defined(FXG_VAR_ROWS128)
+                sb_all[j] = sb; qb_all[j] = qb;
+#else
                 S.sbits[c >> 5] = sb;                                 // warp-uniform address and value: every lane stores
                 S.qbits[c >> 5] = qb;
+#endif
                 if (q_any) my_list[wcount + __popc(qb & lt_mask)] = (unsigned short)c;
                 wcount += __popc(qb);
                 if (LIT8 && !REDO) {
@@ -592,6 +608,13 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
                     }
                 }
             }
+#if defined(FXG_VAR_ROWS128)
+            if (lane == 0) {
+                static_assert(kChunksPerThread == 4, "one 16-byte store per row");
+                *reinterpret_cast<uint4 *>(&S.sbits[warp * kChunksPerThread]) = make_uint4(sb_all[0], sb_all[1], sb_all[2], sb_all[3]);
+                *reinterpret_cast<uint4 *>(&S.qbits[warp * kChunksPerThread]) = make_uint4(qb_all[0], qb_all[1], qb_all[2], qb_all[3]);
+            }
+#endif
             if (__any_sync(0xffffffffu, (hi_acc & kHi) != 0) && lane == 0) note_violation(T, FXG_V_BYTE_RANGE);
         }
 

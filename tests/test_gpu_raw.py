@@ -173,6 +173,41 @@ def test_non_canonical_is_rejected(fx, data, name):
         assert got["ok"] == 0, (name, got)
 
 
+def test_stray_bytes_are_rejected_wherever_they_sit(fx):
+    """Bytes kseq drops, stops at or reads as EOF (0x7f in a sequence, 0x80..0xff anywhere: kseq.hpp:138-144, :167-181)
+    must reject the batch on every line role and at every position inside a 4-byte word / 16-byte chunk: the range
+    check of the main pass is a SWAR sum whose carries cross byte lanes (0xff is caught through the line-end check)."""
+    rng = random.Random(11)
+    clean = helpers.make_fastq(rng, 400, seqlen=(100, 160))
+    lines = clean.split(b"\n")
+    starts = []
+    o = 0
+    for ln in lines[:-1]:
+        starts.append(o)
+        o += len(ln) + 1
+    ok = run_raw(fx, clean, fx.MODE_LITERAL, [b"ACGTACGTACGTACGTAC"], count_only=True)
+    assert ok["ok"] == 1
+    blobs = []
+    for bad in (0x7f, 0x80, 0x9f, 0xa0, 0xa1, 0xc0, 0xfe, 0xff, 0x01, 0x1f):
+        for role in (0, 1, 3):
+            for k in range(17):
+                li = 4 * rng.randrange(5, 390) + role
+                pos = starts[li] + 2 + ((k + rng.randrange(0, 4) * 16) % (len(lines[li]) - 3))
+                b = bytearray(clean)
+                b[pos] = bad
+                if k % 5 == 0 and pos + 1 < starts[li] + len(lines[li]) - 1:
+                    b[pos + 1] = 0x7e                     # the neighbour a carry would land on
+                blobs.append((bad, role, pos, bytes(b)))
+    from fxtract_b200 import lib
+    ctx = fx.Context(fx.MODE_LITERAL, count_only=True, batch_bytes=max(len(clean), 1 << 20))
+    ctx.set_patterns([b"ACGTACGTACGTACGTAC"])
+    for bad, role, pos, blob in blobs:
+        ctx.submit_raw_bytes(blob, True)
+        r = ctx.collect()
+        assert r.canonical_ok == 0, (hex(bad), role, pos, pos & 15, r.violation)
+    ctx.close()
+
+
 def test_canonical_edge_shapes(fx):
     # shortest records, '@'/'+' opening quality lines, names without comments, long lines across tiles
     recs = [b"@\nA\n+\nI\n", b"@a\nAC\n+\n@+\n", b"@x y z\nACGTN\n+\n+@+@+\n"]
