@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1120,5 +1121,119 @@ extern "C" int fxg_copy_to_host(fxg_ctx *ctx, void *host_dst, const void *d_src,
     cudaSetDevice(ctx->cfg.device);
     FXG_CUDA_OK(cudaMemcpyAsync(host_dst, d_src, n, cudaMemcpyDeviceToHost, ctx->stream));
     FXG_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    return FXG_OK;
+}
+
+// ================================================================= allocation-free literal count (fxg_count_device_noalloc)
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops).  Every scratch table the raw scan needs lives in ONE
+// file-scope __device__ array, carved below for the largest batch the entry point accepts.  In host code the name
+// `g_noalloc_scratch` is only a host-side stand-in for the symbol, never a device address: its address is taken
+// once per device with cudaGetSymbolAddress (that device current) and the kernels get pointers derived from it.
+namespace fxg {
+
+constexpr size_t na_align(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr size_t kNaMaxBytes = FXG_NOALLOC_MAX_BYTES;
+constexpr size_t kNaTiles = (kNaMaxBytes + G24::kTileBytes - 1) / G24::kTileBytes;
+constexpr size_t kNaRecCap = kNaTiles * (size_t)(G24::kMaxTileLines / 4) + 64;
+constexpr size_t kNaWords = (kNaRecCap + 31) / 32 + 4;
+// offsets of the tables inside the array (each 256-byte aligned)
+constexpr size_t kNaOffCtr = 0;
+constexpr size_t kNaOffInfo = kNaOffCtr + na_align(sizeof(ScanCounters));
+constexpr size_t kNaOffLbase = kNaOffInfo + na_align(kNaTiles * sizeof(TileInfo));
+constexpr size_t kNaOffBsum = kNaOffLbase + na_align((kNaTiles + 1) * sizeof(unsigned long long));
+constexpr size_t kNaOffRedo = kNaOffBsum + na_align((kNaTiles / 4096 + 2) * sizeof(unsigned long long));
+constexpr size_t kNaOffHitbits = kNaOffRedo + na_align((kNaTiles + 1) * sizeof(unsigned int));
+constexpr size_t kNaOffTileHit = kNaOffHitbits + na_align(kNaWords * sizeof(unsigned int));
+constexpr size_t kNaOffTileNl = kNaOffTileHit + na_align(kNaTiles * (size_t)G24::kHitWords * sizeof(unsigned int));
+constexpr size_t kNaScratchBytes = kNaOffTileNl + na_align(kNaTiles * (size_t)G24::kMaxTileLines * sizeof(unsigned short));
+static_assert(kNaScratchBytes < (2u << 20), "the no-alloc scratch is meant to stay modest (< 2 MiB per GPU)");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaScratchBytes];
+
+// counters -> the caller's result record (what finish_raw does on the host for the ordinary path)
+__global__ void noalloc_publish_kernel(const ScanCounters *ctr, unsigned long long nbytes, int all_match, fxg_noalloc_counts *out)
+{
+    if (blockIdx.x || threadIdx.x) return;
+    fxg_noalloc_counts r;
+    r.n_lines = ctr->n_lines;
+    r.n_records = ctr->n_lines >> 2;
+    unsigned int viol = ctr->violation;
+    if (nbytes && (ctr->last_byte != '\n' || (ctr->n_lines & 3ull))) viol |= FXG_V_TRUNCATED;
+    r.n_matched = all_match ? r.n_records : ctr->n_hits;
+    r.first_bad_offset = ctr->first_bad;
+    r.violation = viol;
+    r.canonical_ok = viol == 0u ? 1u : 0u;
+    *out = r;
+}
+
+// device address of the scratch array on `dev` (looked up once per device, with that device current)
+static int noalloc_scratch_base(fxg_ctx *ctx, int dev, unsigned char **base)
+{
+    static std::mutex mu;
+    static unsigned char *ptr[64];
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev < 0 || dev >= 64) return set_error(ctx, FXG_ERR_ARG, "fxg_count_device_noalloc: device ordinal out of range");
+    if (!ptr[dev]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return set_cuda_error(ctx, e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+        if (!p || ((uintptr_t)p & 255) != 0) return set_error(ctx, FXG_ERR_CUDA, "fxg_count_device_noalloc: scratch symbol has no usable device address");
+        ptr[dev] = (unsigned char *)p;
+    }
+    *base = ptr[dev];
+    return FXG_OK;
+}
+
+}  // namespace fxg
+
+extern "C" int fxg_count_device_noalloc(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes, fxg_noalloc_counts *d_out)
+{
+    if (!ctx || !d_out || (!d_buf && nbytes)) return set_error(ctx, FXG_ERR_ARG, "fxg_count_device_noalloc: null argument");
+    if (nbytes > kNaMaxBytes)
+        return set_error(ctx, FXG_ERR_ARG, "fxg_count_device_noalloc: batch of " + std::to_string(nbytes) + " bytes exceeds FXG_NOALLOC_MAX_BYTES (" +
+                                               std::to_string(kNaMaxBytes) + "); use fxg_scan_device_async or smaller batches");
+    if (((uintptr_t)d_buf & 15) != 0) return set_error(ctx, FXG_ERR_ARG, "d_buf must be 16-byte aligned (the tiles are fetched with bulk copies)");
+    if (!ctx->have_patterns) return set_error(ctx, FXG_ERR_STATE, "fxg_set_patterns has not been called");
+    if (ctx->cfg.mode != FXG_MODE_LITERAL)
+        return set_error(ctx, FXG_ERR_UNSUPPORTED, "fxg_count_device_noalloc serves FXG_MODE_LITERAL contexts only");
+    if (ctx->tile_bytes != G24::kTileBytes || ctx->nl_stride != G24::kMaxTileLines || ctx->hit_words != G24::kHitWords)
+        return set_error(ctx, FXG_ERR_STATE, "fxg_count_device_noalloc: unexpected scan geometry");
+    FXG_CUDA_OK(cudaSetDevice(ctx->cfg.device));
+    unsigned char *base = nullptr;
+    int rc = noalloc_scratch_base(ctx, ctx->cfg.device, &base);
+    if (rc != FXG_OK) return rc;
+    cudaStream_t st = ctx->stream;
+    ScanCounters *ctr = reinterpret_cast<ScanCounters *>(base + kNaOffCtr);
+    unsigned int *hitbits = reinterpret_cast<unsigned int *>(base + kNaOffHitbits);
+    unsigned int *redo = reinterpret_cast<unsigned int *>(base + kNaOffRedo);
+    const size_t ntiles = ((size_t)nbytes + G24::kTileBytes - 1) / G24::kTileBytes;
+    const size_t rec_cap = ntiles * (size_t)(G24::kMaxTileLines / 4) + 64;
+    const size_t words = (rec_cap + 31) / 32;
+    // the array keeps the previous call's contents: everything the kernels accumulate into starts at zero again
+    FXG_CUDA_OK(cudaMemsetAsync(ctr, 0, sizeof(ScanCounters), st));
+    FXG_CUDA_OK(cudaMemsetAsync(&ctr->first_bad, 0xff, 8, st));
+    FXG_CUDA_OK(cudaMemsetAsync(hitbits, 0, (words + 4) * sizeof(unsigned int), st));
+    FXG_CUDA_OK(cudaMemsetAsync(redo + kNaTiles, 0, sizeof(unsigned int), st));
+    ctx->last_launches = 0;
+    if (nbytes) {
+        ScanParams P;
+        memset(&P, 0, sizeof P);
+        P.buf = (const uint8_t *)d_buf; P.nbytes = nbytes; P.ntiles = ntiles;
+        P.tile_bytes = G24::kTileBytes; P.nl_stride = G24::kMaxTileLines; P.hit_words = G24::kHitWords;
+        P.info = reinterpret_cast<TileInfo *>(base + kNaOffInfo);
+        P.tile_nl = reinterpret_cast<unsigned short *>(base + kNaOffTileNl);
+        P.tile_hit = reinterpret_cast<unsigned int *>(base + kNaOffTileHit);
+        P.lbase = reinterpret_cast<unsigned long long *>(base + kNaOffLbase);
+        P.bsum = reinterpret_cast<unsigned long long *>(base + kNaOffBsum);
+        P.ctr = ctr; P.hitbits = hitbits; P.rec_cap = rec_cap; P.one = 1; P.l2_evict_first = 1;
+        P.redo_list = redo; P.redo_count = redo + kNaTiles;
+        P.lit = ctx->d_lit; P.pat_bytes = ctx->d_pat; P.target = ctx->cfg.target;
+        P.mode = ctx->scan_mode; P.match_enabled = mode_is_literal(P.mode); P.lit_unit = ctx->h_lit.unit;
+        FXG_CUDA_OK(launch_scan_raw(P, st, &ctx->last_launches, nullptr));
+    }
+    noalloc_publish_kernel<<<1, 32, 0, st>>>(ctr, nbytes, ctx->h_lit.all_match ? 1 : 0, d_out);
+    ctx->last_launches += 1;
+    FXG_CUDA_OK(cudaGetLastError());
     return FXG_OK;
 }

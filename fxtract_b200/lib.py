@@ -31,6 +31,14 @@ class Result(C.Structure):
                 ("run_pattern_id", C.POINTER(C.c_int32))]
 
 
+NOALLOC_MAX_BYTES = 8 << 20
+
+
+class NoAllocCounts(C.Structure):
+    _fields_ = [("n_lines", C.c_uint64), ("n_records", C.c_uint64), ("n_matched", C.c_uint64),
+                ("first_bad_offset", C.c_uint64), ("violation", C.c_uint32), ("canonical_ok", C.c_uint32)]
+
+
 class SynthSpec(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("first_record", C.c_uint64), ("n_records", C.c_uint64),
                 ("read_len", C.c_uint32), ("plant_mode", C.c_uint32), ("pattern_seed", C.c_uint64),
@@ -42,7 +50,7 @@ EXPORTS = ["fxg_device_count", "fxg_create", "fxg_destroy", "fxg_last_error", "f
            "fxg_acquire_buffer", "fxg_submit_raw", "fxg_submit_raw_from", "fxg_submit_raw_interleaved_from",
            "fxg_submit_raw_pair_from", "fxg_scan_device_pairs_async", "fxg_submit_fields", "fxg_collect",
            "fxg_count", "fxg_find_record_cut", "fxg_scan_device_async", "fxg_scan_device_finish",
-           "fxg_can_route", "fxg_last_launch_count", "fxg_last_d2h_bytes", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
+           "fxg_count_device_noalloc", "fxg_can_route", "fxg_last_launch_count", "fxg_last_d2h_bytes", "fxg_set_profiling", "fxg_last_kernel_ms", "fxg_synth_bytes", "fxg_synth_record_offset", "fxg_synth_host",
            "fxg_synth_device", "fxg_synth_pattern", "fxg_synth_name", "fxg_host_alloc", "fxg_host_free", "fxg_copy_to_host", "fxg_copy_to_device"]
 
 _lib = None
@@ -75,6 +83,7 @@ def load_library():
     lib.fxg_find_record_cut.restype = C.c_size_t
     lib.fxg_scan_device_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.fxg_scan_device_finish.argtypes = [C.c_void_p, C.POINTER(Result)]
+    lib.fxg_count_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     lib.fxg_can_route.argtypes = [C.c_void_p]
     lib.fxg_last_launch_count.argtypes = [C.c_void_p]
     lib.fxg_last_d2h_bytes.argtypes = [C.c_void_p]
@@ -214,6 +223,14 @@ class Context:
 
     def scan_device_pairs_async(self, dptr, nbytes, split):
         self._check(self.lib.fxg_scan_device_pairs_async(self.h, C.c_void_p(dptr), nbytes, split))
+
+    def count_device_noalloc(self, dptr, nbytes, d_out):
+        """Enqueues the allocation-free literal count; d_out = device address of one NoAllocCounts.  Returns the raw
+        status (0 = ok) so that callers can look at refusals; fxg_last_error() has the text."""
+        return self.lib.fxg_count_device_noalloc(self.h, C.c_void_p(dptr), nbytes, C.c_void_p(d_out))
+
+    def last_error(self):
+        return self.lib.fxg_last_error(self.h).decode()
 
     def scan_device_finish(self):
         r = Result()

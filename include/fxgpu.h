@@ -156,6 +156,32 @@ int fxg_scan_device_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes);
  * d_buf[split..nbytes) their mates (see fxg_submit_raw_pair_from). */
 int fxg_scan_device_pairs_async(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes, uint64_t split);
 int fxg_scan_device_finish(fxg_ctx *ctx, fxg_result *res);
+/* ---- allocation-free count over a device-resident batch ------------------ */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The literal search of fxg_scan_device_async (FXG_MODE_LITERAL contexts only; invert / count_only / route_runs
+ * are ignored: counts only) over d_buf[0..nbytes), with every scratch table of the scan -- per-tile line tables,
+ * prefix sums, line-hit words, hit bit set, counters: about 1.6 MB -- in a file-scope __device__ array of the
+ * library instead of cudaMalloc'ed memory.  Every GPU that loads the library holds that array until the process
+ * exits.  The call allocates nothing on the device (no cudaMalloc / cudaFree, no allocating library routine); it
+ * only enqueues memsets and kernels on the context's stream and returns without synchronising.  The result is
+ * written to d_out, a caller-owned DEVICE buffer of one fxg_noalloc_counts, in stream order.
+ *   limit : nbytes <= FXG_NOALLOC_MAX_BYTES (8 MiB); larger batches are refused with FXG_ERR_ARG and a message.
+ *   d_buf : 16-byte aligned, readable for 16 bytes past nbytes (like fxg_scan_device_async).
+ *   sharing: all calls on one GPU -- from any context -- share the one scratch array.  What must start at zero is
+ *            cleared by the call itself (stream-ordered), but two calls that overlap on the GPU (different streams,
+ *            or different contexts with their own streams) RACE on it: serialise them. */
+#define FXG_NOALLOC_MAX_BYTES (8u << 20)
+typedef struct fxg_noalloc_counts {
+    uint64_t n_lines;         /* '\n' count */
+    uint64_t n_records;       /* n_lines / 4 */
+    uint64_t n_matched;       /* records with >= 1 hit (before invert) */
+    uint64_t first_bad_offset;/* as in fxg_result (all ones: none) */
+    uint32_t violation;       /* FXG_V_* bitmask; 0 = the batch satisfies the canonical-FASTQ predicate */
+    uint32_t canonical_ok;
+} fxg_noalloc_counts;
+int fxg_count_device_noalloc(fxg_ctx *ctx, const void *d_buf, uint64_t nbytes, fxg_noalloc_counts *d_out);
+
 /* 1 iff the context can serve cfg.route_runs on the raw path with the current pattern set (EXACT always; MULTI
  * when the set is served by the fused window matcher); otherwise the caller keeps such inputs on the fields path. */
 int fxg_can_route(const fxg_ctx *ctx);
