@@ -41,7 +41,11 @@ template <int TILE_BYTES, int THREADS, int MIN_CTAS, int GROUPS = 1> struct Geom
     static_assert(TILE_BYTES % (THREADS * 16) == 0 && TILE_BYTES <= 65536, "tile = whole 16-byte chunks per thread; u16 positions");
     static_assert(kWarps % 4 == 0, "every line role has its own warps");
 };
+#if defined(FXG_VAR_G24_TILE)          // geometry experiments (scripts/build_variant.sh): -DFXG_VAR_G24_TILE=16384 -DFXG_VAR_G24_THREADS=256 -DFXG_VAR_G24_CTAS=4
+typedef Geom<FXG_VAR_G24_TILE, FXG_VAR_G24_THREADS, FXG_VAR_G24_CTAS> G24;
+#else
 typedef Geom<24576, 384, 3> G24;
+#endif
 typedef Geom<32768, 512, 2> G32;
 typedef Geom<16384, 512, 1, 2> G16D;
 typedef Geom<16384, 512, 2> G16;

@@ -54,8 +54,8 @@ template <class G> struct __align__(128) ScanSmem {
     __align__(16) unsigned int qbits[G::kChunks / 32];              // bit c: chunk c has a byte < 0x21 (not a quality char)
     unsigned int linehit[G::kHitWords];               // bit i: local line i has a (phase-conditional) match
     unsigned long long mbar[2];                       // bulk-copy completion barriers
-    // per-tile scalars, double buffered by tile parity: the copy of the previous tile is reset by
-    // thread 0 while the current one is in use (no extra barrier between "last read" and "first write")
+    // per-tile scalars, double buffered by tile parity: a tile's copy is reset by the thread that publishes it, behind
+    // the tile's last barrier, and next used two tiles on (no extra barrier between "last read" and "first write")
     TileState st[2];
 };
 
@@ -494,9 +494,8 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
         const int bulk = tile_len & ~15;
 
         // ---- prefetch the next tile of this CTA into the other buffer (free since the end of the
-        //      previous iteration); reset the other copy of the per-tile scalars
+        //      previous iteration)
         if (tid == 0) {
-            if (it) reset_state(S.st[cur ^ 1]);
             const unsigned long long kn = k + k_step;
             if (kn < n_work) {
                 const unsigned long long tn = FXG_TILE_OF(kn);
@@ -845,23 +844,31 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
         {
             uint4 *dst = reinterpret_cast<uint4 *>(P.tile_nl + t * (unsigned long long)kMaxTileLines);
             const uint4 *src = reinterpret_cast<const uint4 *>(S.nlpos);
-            for (int q = tid; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
+            // the duties of this step start on different warps -- table copy: warp 4, scalars and hit words: warp 8;
+            // thread 0 keeps the prefetch of the next tile -- so that no single warp enters the next tile's main pass
+            // late by the sum of them: the whole group waits for its last warp at the next barrier (c2 + 1.9 %, c4
+            // + 2.5 %).  All three are header-role warps, which have the least to do in step 4 in every mode.
+            const int tid_nl = tid >= 128 ? tid - 128 : tid + kThreads - 128;
+            const int tid_hit = tid >= 257 ? tid - 257 : tid + kThreads - 257;
+            const int tid_info = 256;
+            for (int q = tid_nl; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
             if (HITS) {
                 unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
                 const int nw = (n_tab >> 5) + 1;               // local line indices 0..n_tab
-                for (int w = tid; w < nw; w += kThreads) {
+                for (int w = tid_hit; w < nw; w += kThreads) {
                     const unsigned int v = S.linehit[w];
                     hd[w] = v;
                     if (v) S.linehit[w] = 0;
                 }
             }
-            if (tid == 0) {
+            if (tid == tid_info) {
                 if (KMER && !REDO) P.tile_ncand[t] = T.n_cand <= (unsigned int)P.cand_cap ? T.n_cand : ((unsigned int)P.cand_cap | kCandOverflow);
                 // the REDO launch re-checks structure only: the hit words of the first launch stand, and so does their flag
                 const unsigned int kept = REDO ? (P.info[t].viol & kTileHasHit) : 0u;
                 const TileInfo ti = {total, kept | T.viol | (plus_idx != 0xffffffffu ? (((2u - plus_idx) & 3u) + 1u) << 16 : 0u),
                                      {(unsigned short)T.cls[0], (unsigned short)T.cls[1], (unsigned short)T.cls[2], (unsigned short)T.cls[3]}};
                 P.info[t] = ti;
+                reset_state(T);                                // next used two tiles on, behind that tile's barriers
             }
         }
     }
