@@ -410,6 +410,7 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
     constexpr int NPROBE = 16 / SB;
     constexpr bool HITS = LIT && !REDO;                                // this launch produces line-hit words
     constexpr int kGroups = G::kGroups;
+    constexpr bool ROLEMIX = EXACT || (KMER && G::kGroups == 1);        // see step 4
     constexpr bool KDEFER = KMER && G::kGroups == 1;                   // window matcher: filter test deferred by one step
     typedef ScanSmem<G> Smem;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -738,7 +739,11 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
             // One thread per LINE, one line role per warp (role = warp & 3), so no lane of a warp diverges from
             // its neighbours and the longest dependent chain of this step is one class check.
             const int r = (int)((2u - plus_idx) & 3u);
-            const int role = warp & 3;                        // 0 header, 1 sequence, 2 plus, 3 quality
+            // 0 header, 1 sequence, 2 plus, 3 quality.  Warp w issues on scheduler w % 4, so with role = w % 4 each
+            // role's work always lands on one scheduler; ROLEMIX rotates the roles from one group of four warps to
+            // the next (measured: exact + 4.4 % -- the key hashing no longer sits on one scheduler --, small-filter
+            // window matcher + 1.1 %, literal - 0.4 %, two-group window matcher - 5 %: those keep w % 4)
+            const int role = ROLEMIX ? (warp + (warp >> 2)) & 3 : warp & 3;
             const int first = (role - r) & 3;                 // smallest local line index with that role
             unsigned int viol = 0;
             for (int i = first + 4 * ((warp >> 2) * 32 + lane); i <= n_tab; i += 4 * (kWarps / 4) * 32) {
@@ -848,9 +853,10 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
             // thread 0 keeps the prefetch of the next tile -- so that no single warp enters the next tile's main pass
             // late by the sum of them: the whole group waits for its last warp at the next barrier (c2 + 1.9 %, c4
             // + 2.5 %).  All three are header-role warps, which have the least to do in step 4 in every mode.
-            const int tid_nl = tid >= 128 ? tid - 128 : tid + kThreads - 128;
-            const int tid_hit = tid >= 257 ? tid - 257 : tid + kThreads - 257;
-            const int tid_info = 256;
+            constexpr int kNlBase = ROLEMIX ? 224 : 128, kInfoTid = ROLEMIX ? 320 : 256;   // header-role warps: 0, 4, 8 / 0, 7, 10
+            const int tid_nl = tid >= kNlBase ? tid - kNlBase : tid + kThreads - kNlBase;
+            const int tid_hit = tid > kInfoTid ? tid - kInfoTid - 1 : tid + kThreads - kInfoTid - 1;
+            const int tid_info = kInfoTid;
             for (int q = tid_nl; q * 8 < n_tab; q += kThreads) dst[q] = src[q];
             if (HITS) {
                 unsigned int *hd = P.tile_hit + t * (unsigned long long)kHitWords;
