@@ -133,7 +133,9 @@ struct KmerTile {
     int k, stride;                         // stride in {4, 8, 16}
     int filter_log2_words;                 // 13 (32 KiB, 2 CTAs / SM) or 15 (128 KiB, 1 CTA of 32 warps / SM)
 };
-// hash of a window given as four little-endian words (bytes past the window masked off); identical on host and device
+// hash of a window given as four little-endian words (bytes past the window masked off); identical on host and device.
+// (Measured and dropped: folding the masks into left-shifted multipliers saves two LOP3 per probe, but the last
+// bytes of the window then only reach the top bits of the hash -- more filter hits, config 3 resolve + 10 %.)
 constexpr unsigned int kWinMul0 = 0x9E3779B1u, kWinMul1 = 0x85EBCA77u, kWinMul2 = 0xC2B2AE3Du, kWinMul3 = 0x27D4EB2Fu;
 __host__ __device__ inline unsigned int window_hash(unsigned int w0, unsigned int w1, unsigned int w2, unsigned int w3)
 {
@@ -141,9 +143,17 @@ __host__ __device__ inline unsigned int window_hash(unsigned int w0, unsigned in
 }
 __host__ __device__ inline unsigned int kmer_tile_filter_word(unsigned int h, int log2_words) { return h >> (32 - log2_words); }
 // four bits of one filter word per window: {r, r + 16} and {s, s + 8} (mod 32), r = h & 31, s = (h >> 5) & 31
+// (Which hash bits give the two rotation counts was measured: 0 / 5 as here; 5 / 10, 7 / 12 cost one more shift per
+// probe and gain nothing; 10 / 15 and 12 / 17 overlap the bits that pick the filter WORD, so all entries of a word
+// share their rotations and 13 % of the probes pass -- config 3 at a third of its speed.)
+#ifndef FXG_FILT_SHIFT_R
+#define FXG_FILT_SHIFT_R 0
+#define FXG_FILT_SHIFT_S 5
+#endif
+constexpr int kFiltShiftR = FXG_FILT_SHIFT_R, kFiltShiftS = FXG_FILT_SHIFT_S;
 __host__ __device__ inline unsigned int kmer_tile_filter_mask(unsigned int h)
 {
-    const unsigned int r = h & 31u, s = (h >> 5) & 31u;
+    const unsigned int r = (h >> kFiltShiftR) & 31u, s = (h >> kFiltShiftS) & 31u;
     return ((0x00010001u << r) | (0x00010001u >> ((32u - r) & 31u))) | ((0x00000101u << s) | (0x00000101u >> ((32u - s) & 31u)));
 }
 __host__ __device__ inline unsigned int kmer_tile_bucket(unsigned int h, unsigned int mask) { return ((h * 0x9E3779B1u) >> 9) & mask; }

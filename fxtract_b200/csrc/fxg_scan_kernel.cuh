@@ -525,12 +525,15 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
             unsigned int hi_acc = 0;
             unsigned int pr0 = 0, pr1 = 0, pf0 = 1, pf1 = 1;
             unsigned int khs[NPROBE], kfw[NPROBE];
+#if defined(FXG_VAR_KBATCH)
+            unsigned int ahs[NPROBE * kChunksPerThread], ahits = 0;
+#endif
             auto kmer_eval = [&](const unsigned int (&eh)[NPROBE], const unsigned int (&ef)[NPROBE], int ec) {
                 unsigned int hits = 0;
 #pragma unroll
                 for (int q = 0; q < NPROBE; ++q) {
                     const unsigned int h = eh[q];
-                    const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h) | __funnelshift_l(0x00000101u, 0x00000101u, h >> 5);
+                    const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h >> kFiltShiftR) | __funnelshift_l(0x00000101u, 0x00000101u, h >> kFiltShiftS);
                     if ((m & ~ef[q]) == 0u) hits |= 1u << q;
                 }
                 if (__any_sync(0xffffffffu, hits != 0u)) {
@@ -628,12 +631,39 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
                         const unsigned int h = window_hash(wd[o], wd[o + 1], wd[o + 2] & wmask2, wd[o + 3] & wmask3);
                         hs[q] = h;
                         const unsigned int fw = filt[h >> fshift];
-                        const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h) | __funnelshift_l(0x00000101u, 0x00000101u, h >> 5);
+                        const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h >> kFiltShiftR) | __funnelshift_l(0x00000101u, 0x00000101u, h >> kFiltShiftS);
                         if ((m & ~fw) == 0u) hits |= 1u << q;
                     }
+#if defined(FXG_VAR_KBATCH)
+                    // large filter (4.5 % of the probes pass: nearly every step of a warp has a hit): the hits of all
+                    // steps of the segment are pushed together -- one vote, one atomic, one slot hand-out per tile
+#pragma unroll
+                    for (int q = 0; q < NPROBE; ++q) ahs[j * NPROBE + q] = hs[q];
+                    ahits |= hits << (j * NPROBE);
+                    if (j == kChunksPerThread - 1 && __any_sync(0xffffffffu, ahits != 0u)) {
+                        constexpr int NP = NPROBE * kChunksPerThread;
+                        unsigned int bq[NP], tot = 0;
+#pragma unroll
+                        for (int q = 0; q < NP; ++q) { bq[q] = __ballot_sync(0xffffffffu, (ahits >> q) & 1u); tot += __popc(bq[q]); }
+                        unsigned int slot = 0;
+                        if (lane == 0) slot = atomicAdd(&T.n_cand, tot);
+                        slot = __shfl_sync(0xffffffffu, slot, 0);
+                        uint2 *list = P.cand + t * (unsigned long long)P.cand_cap;
+                        const int c0 = warp * kWarpChunks + lane;
+#pragma unroll
+                        for (int q = 0; q < NP; ++q) {
+                            const unsigned int mine = slot + __popc(bq[q] & lt_mask);
+                            if (((ahits >> q) & 1u) && mine < (unsigned int)P.cand_cap)
+                                list[mine] = make_uint2(ahs[q], (unsigned int)(((c0 + (q / NPROBE) * 32) << 4) + (q % NPROBE) * SB));
+                            slot += __popc(bq[q]);
+                        }
+                    }
+                    if (false) {
+#else
                     // filter hits go to the tile's list for kmer_resolve_kernel: one shared-memory atomic per warp
                     // and step (the slots of the step are dealt out by ballot rank); one vote when nothing hit
                     if (__any_sync(0xffffffffu, hits != 0u)) {
+#endif
                         unsigned int bq[NPROBE], tot = 0;
 #pragma unroll
                         for (int q = 0; q < NPROBE; ++q) { bq[q] = __ballot_sync(0xffffffffu, (hits >> q) & 1u); tot += __popc(bq[q]); }

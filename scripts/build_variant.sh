@@ -10,5 +10,7 @@ nvcc $NV $FLAGS -c -o $B/var/obj_$NAME/fxg_scan.o $C/fxg_scan.cu &
 if [ -n "$KMER" ]; then nvcc $NV $FLAGS -c -o $B/var/obj_$NAME/fxg_scan_kmer.o $C/fxg_scan_kmer.cu & fi
 wait
 K=$B/fxg_scan_kmer.o; [ -n "$KMER" ] && K=$B/var/obj_$NAME/fxg_scan_kmer.o
-nvcc $NV -shared -o $B/var/$NAME.so $B/var/obj_$NAME/fxg_scan.o $K $B/fxg_fields.o $B/fxg_synth.o $B/fxg_api.o
+A=$B/fxg_api.o
+if [ -n "$API" ]; then nvcc $NV $FLAGS -c -o $B/var/obj_$NAME/fxg_api.o $C/fxg_api.cu; A=$B/var/obj_$NAME/fxg_api.o; fi   # API=1: host tables depend on the flags too
+nvcc $NV -shared -o $B/var/$NAME.so $B/var/obj_$NAME/fxg_scan.o $K $B/fxg_fields.o $B/fxg_synth.o $A
 echo built $B/var/$NAME.so
