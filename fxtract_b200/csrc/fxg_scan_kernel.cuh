@@ -525,6 +525,112 @@ __global__ void __launch_bounds__(G::kCtaThreads, G::kMinCtas) scan_tiles_kernel
             unsigned int hi_acc = 0;
             unsigned int pr0 = 0, pr1 = 0, pf0 = 1, pf1 = 1;
             unsigned int khs[NPROBE], kfw[NPROBE];
+            auto kmer_eval = [&](const unsigned int (&eh)[NPROBE], const unsigned int (&ef)[NPROBE], int ec) {
+                unsigned int hits = 0;
+#pragma unroll
+                for (int q = 0; q < NPROBE; ++q) {
+                    const unsigned int h = eh[q];
+                    const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h >> kFiltShiftR) | __funnelshift_l(0x00000101u, 0x00000101u, h >> kFiltShiftS);
+                    if ((m & ~ef[q]) == 0u) hits |= 1u << q;
+                }
+                if (__any_sync(0xffffffffu, hits != 0u)) {
+                    unsigned int bq[NPROBE], tot = 0;
+#pragma unroll
+                    for (int q = 0; q < NPROBE; ++q) { bq[q] = __ballot_sync(0xffffffffu, (hits >> q) & 1u); tot += __popc(bq[q]); }
+                    unsigned int slot = 0;
+                    if (lane == 0) slot = atomicAdd(&T.n_cand, tot);
+                    slot = __shfl_sync(0xffffffffu, slot, 0);
+                    uint2 *list = P.cand + t * (unsigned long long)P.cand_cap;
+#pragma unroll
+                    for (int q = 0; q < NPROBE; ++q) {
+                        const unsigned int mine = slot + __popc(bq[q] & lt_mask);
+                        if (((hits >> q) & 1u) && mine < (unsigned int)P.cand_cap)
+                            list[mine] = make_uint2(eh[q], (unsigned int)((ec << 4) + q * SB));
+                        slot += __popc(bq[q]);
+                    }
+                }
+            };
+#pragma unroll
+            for (int j = 0; j < kChunksPerThread; ++j) {
+                const int c = warp * kWarpChunks + j * 32 + lane;
+                const uint4 x = tile[c];
+                // bytes >= 0x7f anywhere: bit 7 of (byte + 1).  Only a byte 0xff escapes this sum (it wraps to 0 and
+                // carries into its neighbour) -- and every 0xff is caught on another way: + 0x5f and + 0x60 wrap as
+                // well, so it is listed as a '\n' candidate, enters the position table as a byte < 0x20, and the
+                // per-line check "the byte at a line end is '\n'" (step 4) raises FXG_V_BYTE_RANGE for it.
+                hi_acc |= fma_add(x.x, one, 0x01010101u) | fma_add(x.y, one, 0x01010101u);
+                hi_acc |= fma_add(x.z, one, 0x01010101u) | fma_add(x.w, one, 0x01010101u);
+                const bool s_any = ((fma_add(x.x, one, kAdd41) & fma_add(x.y, one, kAdd41) & fma_add(x.z, one, kAdd41) &
+                                     fma_add(x.w, one, kAdd41)) & kHi) != kHi;
+                const bool q_any = ((fma_add(x.x, one, kAdd21) & fma_add(x.y, one, kAdd21) & fma_add(x.z, one, kAdd21) &
+                                     fma_add(x.w, one, kAdd21)) & kHi) != kHi;
+                const unsigned int sb = __ballot_sync(0xffffffffu, s_any);
+                const unsigned int qb = __ballot_sync(0xffffffffu, q_any);
+                S.sbits[c >> 5] = sb;                                 // warp-uniform address and value: every lane stores
+                S.qbits[c >> 5] = qb;
+                if (q_any) my_list[wcount + __popc(qb & lt_mask)] = (unsigned short)c;
+                wcount += __popc(qb);
+                if (LIT8 && !REDO) {
+                    const unsigned int r0 = MODE == kModeLit9 ? x.x + x.y * lit_mul2 : x.x * lit_mul1 + x.y * lit_mul2;
+                    const unsigned int r1 = MODE == kModeLit9 ? x.z + x.w * lit_mul2 : x.z * lit_mul1 + x.w * lit_mul2;
+                    // the table words of this step are compared one step later: their latency hides behind the next
+                    // step's class sums instead of stalling the warp in front of the vote
+                    const unsigned int f0 = LS.fp[r0 >> lit_shift], f1 = LS.fp[r1 >> lit_shift];
+                    if (j > 0) {
+                        const bool c0 = pf0 == pr0, c1 = pf1 == pr1;
+                        if (__any_sync(0xffffffffu, c0 || c1)) {
+                            if (c0) push_candidate(LS, T, (c - 32) << 4, LS.masks[pr0 >> lit_shift]);
+                            if (c1) push_candidate(LS, T, ((c - 32) << 4) + 8, LS.masks[pr1 >> lit_shift]);
+                        }
+                    }
+                    pr0 = r0; pr1 = r1; pf0 = f0; pf1 = f1;
+                    if (j == kChunksPerThread - 1) {
+                        const bool c0 = pf0 == pr0, c1 = pf1 == pr1;
+                        if (__any_sync(0xffffffffu, c0 || c1)) {
+                            if (c0) push_candidate(LS, T, c << 4, LS.masks[pr0 >> lit_shift]);
+                            if (c1) push_candidate(LS, T, (c << 4) + 8, LS.masks[pr1 >> lit_shift]);
+                        }
+                    }
+                } else if (MODE == kModeLitSmall && !REDO) {
+                    if ((c << 4) < tile_len) filter_small_units(LS, T, x.x, x.y, x.z, x.w, c << 4, lit_unit, lit_nkeys);
+                } else if (KMER && !REDO) {
+                    // windows of k bytes that start at byte 0, SB, 2 SB, ... of the lane's chunk; what lies past the
+                    // chunk comes from the head of the next one (same shared-memory row; behind the tile's last chunk
+                    // lie the 16 bytes staged after the tile)
+                    unsigned int wd[7] = {x.x, x.y, x.z, x.w, 0u, 0u, 0u};
+                    if (SB == 8) {
+                        const uint2 n = *reinterpret_cast<const uint2 *>(&tile[c + 1]);
+                        wd[4] = n.x; wd[5] = n.y;
+                    } else if (SB == 4) {
+                        const uint4 n = tile[c + 1];
+                        wd[4] = n.x; wd[5] = n.y; wd[6] = n.z;
+                    }
+                    // small filter (two CTAs per SM): the filter words fetched in this step are tested one step later,
+                    // their latency hides behind the next step's sums and hashes (c5c + 1 %; the two-group kernel of
+                    // the large filter lost 1 % with it and tests at once)
+                    if (KDEFER) {
+                    unsigned int hs[NPROBE], fws[NPROBE];
+#pragma unroll
+                    for (int q = 0; q < NPROBE; ++q) {
+                        const int o = q * (SB / 4);                   // first word of the window
+                        hs[q] = window_hash(wd[o], wd[o + 1], wd[o + 2] & wmask2, wd[o + 3] & wmask3);
+                        fws[q] = filt[hs[q] >> fshift];
+                    }
+                    if (j > 0) kmer_eval(khs, kfw, c - 32);
+#pragma unroll
+                    for (int q = 0; q < NPROBE; ++q) { khs[q] = hs[q]; kfw[q] = fws[q]; }
+                    if (j == kChunksPerThread - 1) kmer_eval(khs, kfw, c);
+                    } else {
+                    unsigned int hs[NPROBE], hits = 0;
+#pragma unroll
+                    for (int q = 0; q < NPROBE; ++q) {
+                        const int o = q * (SB / 4);                   // first word of the window
+                        const unsigned int h = window_hash(wd[o], wd[o + 1], wd[o + 2] & wmask2, wd[o + 3] & wmask3);
+                        hs[q] = h;
+                        const unsigned int fw = filt[h >> fshift];
+                        const unsigned int m = __funnelshift_l(0x00010001u, 0x00010001u, h >> kFiltShiftR) | __funnelshift_l(0x00000101u, 0x00000101u, h >> kFiltShiftS);
+                        if ((m & ~fw) == 0u) hits |= 1u << q;
+                    }
                     // filter hits go to the tile's list for kmer_resolve_kernel: one shared-memory atomic per warp
                     // and step (the slots of the step are dealt out by ballot rank); one vote when nothing hit
                     if (__any_sync(0xffffffffu, hits != 0u)) {
