@@ -581,6 +581,7 @@ struct CompactParams {
     int invert;
     int *run_pid;                   // routing: pattern id per run (P.rec_first); implies per_record
     int per_record;                 // every selected record is its own run (routing; mates from two files)
+    unsigned int nblocks;           // blocks of 1024 hit words the batch's record capacity covers (bounds every walk)
 };
 constexpr int kCompactThreads = 1024;
 
@@ -599,13 +600,10 @@ __global__ void __launch_bounds__(kCompactThreads) compact_count_kernel(const Co
 {
     __shared__ unsigned long long red[2][kCompactThreads / 32];
     const unsigned long long nrec = C.ctr->n_lines >> 2;
-    // the grid covers the record capacity of the batch (bytes / smallest record); blocks past the records that
-    // exist leave at once
-    if ((unsigned long long)blockIdx.x * kCompactThreads * 32ull >= nrec) {
-        if (threadIdx.x == 0) C.block_sums[blockIdx.x] = 0ull;
-        return;
-    }
-    const unsigned long long w = (unsigned long long)blockIdx.x * kCompactThreads + threadIdx.x;
+    // a fixed grid walks the blocks of 1024 hit words that hold records (the record CAPACITY of a batch -- bytes /
+    // smallest record -- is 7 x what 150-base reads fill: one CTA per capacity block cost 40 us in empty CTAs)
+    for (unsigned long long vb = blockIdx.x; vb < C.nblocks && vb * kCompactThreads * 32ull < nrec; vb += gridDim.x) {
+    const unsigned long long w = vb * kCompactThreads + threadIdx.x;
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
     unsigned int starts = C.per_record ? s : s & ~((s << 1) | prev_msb);
@@ -616,8 +614,10 @@ __global__ void __launch_bounds__(kCompactThreads) compact_count_kernel(const Co
     if (threadIdx.x == 0) {
         unsigned long long ta = 0, tb2 = 0;
         for (int i = 0; i < kCompactThreads / 32; ++i) { ta += red[0][i]; tb2 += red[1][i]; }
-        C.block_sums[blockIdx.x] = ta;
+        C.block_sums[vb] = ta;
         if (tb2) atomicAdd(&C.out_counts[1], tb2);
+    }
+    __syncthreads();
     }
 }
 
@@ -654,8 +654,8 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
 {
     __shared__ unsigned long long wsum[kCompactThreads / 32];
     const unsigned long long nrec = C.ctr->n_lines >> 2;
-    if ((unsigned long long)blockIdx.x * kCompactThreads * 32ull >= nrec) return;   // no record, no run (block-uniform)
-    const unsigned long long w = (unsigned long long)blockIdx.x * kCompactThreads + threadIdx.x;
+    for (unsigned long long vb = blockIdx.x; vb < C.nblocks && vb * kCompactThreads * 32ull < nrec; vb += gridDim.x) {
+    const unsigned long long w = vb * kCompactThreads + threadIdx.x;
     unsigned int s = sel_word(C, w, nrec);
     unsigned int prev_msb = (w > 0) ? (sel_word(C, w - 1, nrec) >> 31) : 0u;
     unsigned int next_lsb = sel_word(C, w + 1, nrec) & 1u;
@@ -667,7 +667,7 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
     __syncthreads();
     unsigned long long woff = 0;
     for (int k = 0; k < (int)(threadIdx.x >> 5); ++k) woff += wsum[k];
-    unsigned long long excl = C.block_sums[blockIdx.x] + woff + inc - n;   // run starts before this word
+    unsigned long long excl = C.block_sums[vb] + woff + inc - n;   // run starts before this word
     // a run that is open at the start of this word has index excl-1
     unsigned int m = starts | ends;
     unsigned long long opened = excl;
@@ -689,6 +689,8 @@ __global__ void __launch_bounds__(kCompactThreads) compact_write_kernel(const Co
             unsigned long long r = opened - 1;
             if (r < C.run_cap) C.runs[r].len = offset_after_line(C.P, 4ll * (long long)rec + 3);   // end offset; fixed up below
         }
+    }
+    __syncthreads();                 // wsum is reused by the next block of words
     }
 }
 
@@ -712,9 +714,11 @@ cudaError_t launch_compact(const unsigned int *hitbits, const ScanParams &P, con
     unsigned long long words = (rec_cap + 31) / 32;
     unsigned int nblocks = (unsigned int)((words + kCompactThreads - 1) / kCompactThreads);
     if (nblocks == 0) nblocks = 1;
-    compact_count_kernel<<<nblocks, kCompactThreads, 0, stream>>>(C);
+    C.nblocks = nblocks;
+    const unsigned int grid = nblocks < 148u * 16u ? nblocks : 148u * 16u;   // enough CTAs to hide the look-ups of run-dense batches
+    compact_count_kernel<<<grid, kCompactThreads, 0, stream>>>(C);
     compact_scan_kernel<<<1, 1024, 0, stream>>>(C, nblocks);
-    compact_write_kernel<<<nblocks, kCompactThreads, 0, stream>>>(C);
+    compact_write_kernel<<<grid, kCompactThreads, 0, stream>>>(C);
     compact_fixup_kernel<<<148, 256, 0, stream>>>(C);
     if (launches) *launches += 4;
     return cudaGetLastError();
