@@ -56,6 +56,8 @@ KERNEL_NAMES = {
     "c4": "fxg::scan_tiles_kernel<Geom<24576,384,3,1>, 30 (exact: key hash), false> (fxg_scan_kernel.cuh)",
     "c5v": "fxg::scan_tiles_kernel<Geom<32768,512,2,1>, 19 (window matcher, 32 KiB filter), false> (fxg_scan_kernel.cuh)",
     "c5c": "fxg::scan_tiles_kernel<Geom<32768,512,2,1>, 19 (window matcher, 32 KiB filter), false> (fxg_scan_kernel.cuh)",
+    "ms": "fxg::scan_tiles_kernel<Geom<32768,512,2,1>, 18..20 (window matcher, 32 KiB filter), false> (fxg_scan_kernel.cuh)",
+    "hf": "fxg::scan_tiles_kernel<Geom<24576,384,3,1>, 0 (index pass), false> (fxg_scan_kernel.cuh); the matcher is fields_ac_kernel (fxg_fields.cu), inside pipeline_ms",
 }
 
 
@@ -87,6 +89,16 @@ def workload_def(name, records):
                  invert=1 if name == "c5v" else 0, count_only=1 if name == "c5c" else 0,
                  desc="-f 1000 20-mers %s over synthetic %d-read FASTQ" % ("-v" if name == "c5v" else "-c", records),
                  cli=["-v"] if name == "c5v" else ["-c"])
+    elif name == "ms":
+        # the reference's own speed-test pattern set (speed_test/random_1000_patterns_minus_small.txt, committed under
+        # tests/golden/patterns/): 1000 patterns of 16..60 bytes, not planted -- measures the filter, not the hits
+        w.update(mode=1, pattern_source=os.path.join(ROOT, "tests", "golden", "patterns", "random_1000_patterns_minus_small.txt"),
+                 desc="-f random_1000_patterns_minus_small.txt over synthetic %d-read FASTQ" % records, cli=[])
+    elif name == "hf":
+        # multi-pattern search on the read NAME (-H -f): 1000 name fragments ":x:y:" -- served by the index pass + the
+        # Aho-Corasick field matcher (DFA in shared memory), not by the window matcher
+        w.update(mode=1, target=1, name_fragments=1000,
+                 desc="-H -f 1000 name fragments over synthetic %d-record FASTQ" % records, cli=["-H"])
     else:
         raise SystemExit("unknown workload %s" % name)
     return w
@@ -118,6 +130,16 @@ def workload_pattern_file(w, total_records, directory):
         seq = open(one, "rb").read().split(b"\n")[1]
         os.remove(one)
         return None, [seq[37:57]]
+    if w.get("pattern_source"):
+        shutil.copyfile(w["pattern_source"], path)
+        return path, sorted(set(l for l in open(path, "rb").read().split(b"\n") if l))
+    if w.get("name_fragments"):
+        n = min(w["name_fragments"], total_records)
+        fxsynth("names", spec_string(w, 0, 1), max(1, total_records // n), n, path)
+        frags = sorted(set(b":" + b":".join(l.split(b":")[4:6]) + b":" for l in open(path, "rb").read().split(b"\n") if l))
+        with open(path, "wb") as f:
+            f.write(b"\n".join(frags) + b"\n")
+        return path, frags
     if w["mode"] == 1:
         fxsynth("patterns", spec_string(w, 0, 1), path)
         base = set(l for l in open(path, "rb").read().split(b"\n") if l)
